@@ -1,0 +1,286 @@
+// Dense PS update: gradient push (peer loads) + mean + optimizer apply + parameter pull
+// (peer stores) in one kernel, and the cross-rank flag barrier.  SURVEY.md §8a A12-A14.
+//
+// HBM-bound.  Algorithmic bytes per parameter on the owner: 4*n_grads read (remote over
+// NVLink when n_gpus > 1) + 4 read var (+4 accum) + 4 written per pull destination
+// (+4 accum).  Single GPU, SGD: 12 B/param; momentum: 20 B/param.
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace tfg {
+
+constexpr int kApplyThreads = 256;
+constexpr int kChunk = 4096;            // elements per work chunk = 4 float4 per thread
+
+struct ApplyArgs {
+  const float* grads[TFG_MAX_REPLICAS];
+  float* pull[TFG_MAX_GPUS];
+  const float* loss_src[TFG_MAX_REPLICAS];
+  float* var;
+  float* accum;
+  float* loss_dst;
+  const Segment* segs;   // NULL: the single inline segment `seg0`
+  Segment seg0;
+  int n_segs;
+  int n_grads, n_pull, n_loss, kind;
+  long long n_chunks;
+  float divisor, lr, mu;
+};
+
+__device__ __forceinline__ float4 ld_stream(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+
+// One optimizer update, written with explicit round-to-nearest ops so that nvcc cannot
+// contract mul+add into FMA: TF 1.3's Eigen expressions round every product.
+template <int KIND>
+__device__ __forceinline__ void update1(float g, float& v, float& a, float lr, float mu) {
+  if (KIND == TFG_OPT_SGD) {
+    v = __fsub_rn(v, __fmul_rn(g, lr));
+  } else if (KIND == TFG_OPT_MOMENTUM) {
+    a = __fadd_rn(__fmul_rn(a, mu), g);
+    v = __fsub_rn(v, __fmul_rn(a, lr));
+  } else {
+    a = __fadd_rn(__fmul_rn(a, mu), g);
+    v = __fsub_rn(v, __fadd_rn(__fmul_rn(g, lr), __fmul_rn(__fmul_rn(a, mu), lr)));
+  }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kApplyThreads)
+push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
+  // mean loss over replicas, replica order (the step's scalar result)
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.n_loss > 0) {
+    float s = a.loss_src[0][0];
+    for (int r = 1; r < a.n_loss; ++r) s = __fadd_rn(s, a.loss_src[r][0]);
+    a.loss_dst[0] = __fdiv_rn(s, (float)a.n_loss);
+  }
+  constexpr int kVecPerThread = kChunk / 4 / kApplyThreads;  // 4
+  for (long long c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
+    Segment sg = a.seg0;
+    if (a.segs) {  // few segments: binary search on the first chunk index
+      int lo = 0, hi = a.n_segs - 1;
+      while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (a.segs[mid].chunk0 <= c) lo = mid; else hi = mid - 1;
+      }
+      sg = a.segs[lo];
+    }
+    const long long base = sg.off + (c - sg.chunk0) * (long long)kChunk;
+    const long long end = sg.off + sg.cnt;
+    float4 g[kVecPerThread];
+    long long idx[kVecPerThread];
+#pragma unroll
+    for (int u = 0; u < kVecPerThread; ++u) {
+      idx[u] = base + 4ll * (threadIdx.x + u * kApplyThreads);
+      g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (idx[u] < end) g[u] = ld_stream(a.grads[0] + idx[u]);
+    }
+    for (int r = 1; r < a.n_grads; ++r) {
+      float4 t[kVecPerThread];
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u)
+        if (idx[u] < end) t[u] = ld_stream(a.grads[r] + idx[u]);
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u)
+        if (idx[u] < end) {
+          g[u].x = __fadd_rn(g[u].x, t[u].x); g[u].y = __fadd_rn(g[u].y, t[u].y);
+          g[u].z = __fadd_rn(g[u].z, t[u].z); g[u].w = __fadd_rn(g[u].w, t[u].w);
+        }
+    }
+    float4 v[kVecPerThread], m[kVecPerThread];
+#pragma unroll
+    for (int u = 0; u < kVecPerThread; ++u)
+      if (idx[u] < end) {
+        v[u] = *reinterpret_cast<const float4*>(a.var + idx[u]);
+        if (KIND != TFG_OPT_SGD) m[u] = *reinterpret_cast<const float4*>(a.accum + idx[u]);
+      }
+#pragma unroll
+    for (int u = 0; u < kVecPerThread; ++u)
+      if (idx[u] < end) {
+        float4 gg = g[u];
+        gg.x = __fdiv_rn(gg.x, a.divisor); gg.y = __fdiv_rn(gg.y, a.divisor);
+        gg.z = __fdiv_rn(gg.z, a.divisor); gg.w = __fdiv_rn(gg.w, a.divisor);
+        update1<KIND>(gg.x, v[u].x, m[u].x, a.lr, a.mu);
+        update1<KIND>(gg.y, v[u].y, m[u].y, a.lr, a.mu);
+        update1<KIND>(gg.z, v[u].z, m[u].z, a.lr, a.mu);
+        update1<KIND>(gg.w, v[u].w, m[u].w, a.lr, a.mu);
+        if (KIND != TFG_OPT_SGD) *reinterpret_cast<float4*>(a.accum + idx[u]) = m[u];
+        if (a.var) *reinterpret_cast<float4*>(a.var + idx[u]) = v[u];
+        for (int p = 0; p < a.n_pull; ++p) *reinterpret_cast<float4*>(a.pull[p] + idx[u]) = v[u];
+      }
+  }
+}
+
+// scalar path for caller buffers whose length or alignment rules out float4
+template <int KIND>
+__global__ void __launch_bounds__(kApplyThreads)
+apply_scalar_kernel(const __grid_constant__ ApplyArgs a, long long count) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+       i += (long long)gridDim.x * blockDim.x) {
+    float g = a.grads[0][i];
+    for (int r = 1; r < a.n_grads; ++r) g = __fadd_rn(g, a.grads[r][i]);
+    g = __fdiv_rn(g, a.divisor);
+    float v = a.var[i], m = (KIND != TFG_OPT_SGD) ? a.accum[i] : 0.f;
+    update1<KIND>(g, v, m, a.lr, a.mu);
+    if (KIND != TFG_OPT_SGD) a.accum[i] = m;
+    a.var[i] = v;
+    for (int p = 0; p < a.n_pull; ++p) a.pull[p][i] = v;
+  }
+}
+
+static int grid_for(long long n_chunks) {
+  long long g = n_chunks < (long long)kNumSMs * 8 ? n_chunks : (long long)kNumSMs * 8;
+  return (int)(g < 1 ? 1 : g);
+}
+
+template <typename K>
+static cudaError_t launch_kind(int kind, K&& f) {
+  switch (kind) {
+    case TFG_OPT_SGD: f(std::integral_constant<int, TFG_OPT_SGD>()); break;
+    case TFG_OPT_MOMENTUM: f(std::integral_constant<int, TFG_OPT_MOMENTUM>()); break;
+    default: f(std::integral_constant<int, TFG_OPT_NESTEROV>()); break;
+  }
+  return cudaGetLastError();
+}
+
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
+  ApplyArgs a = {};
+  if (summed_local) {
+    a.grads[0] = j->grads[0];
+    a.n_grads = 1;
+    a.divisor = (float)n_summed;
+    a.var = j->params;
+    a.n_pull = 0;
+    a.n_loss = 0;
+  } else {
+    for (int r = 0; r < j->n_replicas; ++r) a.grads[r] = j->peer_grads[r];
+    a.n_grads = j->n_replicas;
+    a.divisor = (float)j->n_replicas;
+    a.var = j->params;
+    a.n_pull = 0;
+    for (int g = 0; g < j->n_gpus; ++g)
+      if (g != j->gpu_rank) a.pull[a.n_pull++] = j->peer_params[g];
+    a.n_loss = j->model ? j->n_replicas : 0;
+    for (int r = 0; r < a.n_loss; ++r) a.loss_src[r] = j->peer_loss[r % j->n_gpus] + r;
+  }
+  a.loss_dst = j->loss + TFG_MAX_REPLICAS;
+  a.accum = j->accum;
+  a.segs = j->d_segs;
+  a.n_segs = (int)j->segs.size();
+  a.n_chunks = j->n_chunks;
+  a.kind = j->opt_kind;
+  a.lr = j->lr;
+  a.mu = j->mu;
+  if (a.n_segs == 0 && a.n_loss == 0) return TFG_OK;  // this rank owns nothing
+  int grid = grid_for(a.n_chunks);
+  cudaStream_t s = j->stream;
+  cudaError_t e = launch_kind(j->opt_kind, [&](auto k) {
+    push_apply_pull_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(a);
+  });
+  j->launches++;
+  if (e != cudaSuccess) return fail_cuda(j, e, "push_apply_pull_kernel");
+  return TFG_OK;
+}
+
+int launch_dense_apply(int kind, float* var, float* accum, const float* const* grads, int n_grads,
+                       float divisor, int64_t count, float lr, float mu, float* const* pull,
+                       int n_pull, cudaStream_t s) {
+  ApplyArgs a = {};
+  bool aligned = ((uintptr_t)var % 16 == 0) && (!accum || (uintptr_t)accum % 16 == 0);
+  for (int r = 0; r < n_grads; ++r) {
+    if (!grads[r]) return fail(nullptr, TFG_EINVAL, "NULL gradient pointer");
+    a.grads[r] = grads[r];
+    aligned = aligned && ((uintptr_t)grads[r] % 16 == 0);
+  }
+  for (int p = 0; p < n_pull; ++p) {
+    if (!pull[p]) return fail(nullptr, TFG_EINVAL, "NULL pull pointer");
+    a.pull[p] = pull[p];
+    aligned = aligned && ((uintptr_t)pull[p] % 16 == 0);
+  }
+  a.n_grads = n_grads;
+  a.n_pull = n_pull;
+  a.var = var;
+  a.accum = accum;
+  a.kind = kind;
+  a.divisor = divisor;
+  a.lr = lr;
+  a.mu = mu;
+  a.n_loss = 0;
+  cudaError_t e = cudaSuccess;
+  int64_t vec_count = aligned ? (count / 4) * 4 : 0;
+  if (vec_count > 0) {
+    a.segs = nullptr;
+    a.seg0 = Segment{0, vec_count, 0};
+    a.n_segs = 1;
+    a.n_chunks = (vec_count + kChunk - 1) / kChunk;
+    int grid = grid_for(a.n_chunks);
+    e = launch_kind(kind, [&](auto k) {
+      push_apply_pull_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(a);
+    });
+    if (e != cudaSuccess) return fail_cuda(nullptr, e, "push_apply_pull_kernel");
+  }
+  if (vec_count < count) {
+    ApplyArgs t = a;
+    for (int r = 0; r < n_grads; ++r) t.grads[r] = a.grads[r] + vec_count;
+    for (int p = 0; p < n_pull; ++p) t.pull[p] = a.pull[p] + vec_count;
+    t.var = var + vec_count;
+    t.accum = accum ? accum + vec_count : nullptr;
+    long long rem = count - vec_count;
+    int grid = (int)((rem + kApplyThreads - 1) / kApplyThreads);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    e = launch_kind(kind, [&](auto k) {
+      apply_scalar_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(t, rem);
+    });
+    if (e != cudaSuccess) return fail_cuda(nullptr, e, "apply_scalar_kernel");
+  }
+  return TFG_OK;
+}
+
+// ---- cross-rank barrier ----------------------------------------------------------------
+struct BarrierArgs {
+  uint32_t* flags[TFG_MAX_GPUS];  // every rank's flag array (own one local, others peer-mapped)
+  int* err;
+  int me, n;
+  uint32_t epoch;
+};
+
+__global__ void barrier_kernel(const __grid_constant__ BarrierArgs a) {
+  int t = threadIdx.x;
+  if (t >= a.n || t == a.me) return;
+  __threadfence_system();  // my earlier stores (gradients, pulled parameters) before the flag
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.flags[t] + a.me), "r"(a.epoch) : "memory");
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t seen;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.flags[a.me] + t) : "memory");
+    if ((int32_t)(seen - a.epoch) >= 0) break;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 20ull * 1000 * 1000 * 1000) {  // 20 s: a peer rank died; fail, do not hang
+      atomicExch(a.err, 1);
+      break;
+    }
+    __nanosleep(200);
+  }
+}
+
+int launch_barrier(tfg_job* j) {
+  BarrierArgs a = {};
+  for (int g = 0; g < j->n_gpus; ++g) a.flags[g] = j->peer_flags[g];
+  a.err = j->dev_err;
+  a.me = j->gpu_rank;
+  a.n = j->n_gpus;
+  a.epoch = ++j->epoch;
+  barrier_kernel<<<1, 32, 0, j->stream>>>(a);
+  j->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(j, e, "barrier_kernel");
+  return TFG_OK;
+}
+
+}  // namespace tfg

@@ -1,0 +1,113 @@
+// Internal declarations shared by the libtfgraft translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/tfgraft.h"
+
+namespace tfg {
+
+constexpr int kPadFloats = 32;          // every variable starts on a 128-B boundary
+constexpr int kNumSMs = 148;            // B200
+
+void set_thread_error(const std::string& s);
+const char* thread_error();
+
+struct VarInfo {
+  std::string name, op_type;
+  int dtype = TFG_DT_F32;
+  std::vector<int64_t> shape;
+  bool trainable = true;
+  int ps_task = -1;      // /job:ps/task:k, -1 = worker-local (no ps job)
+  int64_t count = 0;     // elements
+  int64_t offset = -1;   // element offset in the flat fp32 space, -1 = not in it
+  int64_t padded = 0;    // count rounded up to kPadFloats
+};
+
+struct Segment {         // a range of the flat space whose update this rank applies
+  int64_t off;           // element offset (multiple of 4)
+  int64_t cnt;           // elements (multiple of 4)
+  int64_t chunk0;        // index of the segment's first work chunk
+};
+
+struct MnistModel;       // model_mnist.cu
+
+}  // namespace tfg
+
+struct tfg_job {
+  // cluster (jobs sorted by name, as Go marshals the ClusterSpec map)
+  std::vector<std::pair<std::string, std::vector<std::string>>> cluster;
+  int gpu_rank = 0, n_gpus = 1;
+  int n_ps = 0, n_replicas = 1;
+  std::vector<int> local_replicas;     // global replica ids hosted here, ascending
+  // variables
+  std::vector<tfg::VarInfo> vars;
+  int rr_next = 0;
+  bool finalized = false;
+  int layout = TFG_LAYOUT_LOGICAL;
+  int64_t flat_count = 0;
+  std::vector<tfg::Segment> segs;
+  int64_t n_chunks = 0;
+  // device state
+  int device = 0;
+  bool bound = false, own_stream = false;
+  cudaStream_t stream = nullptr;
+  float* params = nullptr;
+  float* accum = nullptr;
+  std::vector<float*> grads;           // one flat buffer per local replica slot
+  float* loss = nullptr;               // [TFG_MAX_REPLICAS + 1]; [r] = replica r, last = mean
+  uint32_t* flags = nullptr;           // [TFG_MAX_GPUS] barrier epochs written by peers
+  int* dev_err = nullptr;              // device-side error word (barrier timeout)
+  tfg::Segment* d_segs = nullptr;
+  float* h_loss = nullptr;             // pinned
+  int* h_err = nullptr;                // pinned
+  // peers (index = GPU rank / global replica id); own entries point at own buffers
+  float* peer_params[TFG_MAX_GPUS] = {};
+  float* peer_loss[TFG_MAX_GPUS] = {};
+  uint32_t* peer_flags[TFG_MAX_GPUS] = {};
+  float* peer_grads[TFG_MAX_REPLICAS] = {};
+  std::vector<void*> ipc_opened;
+  uint32_t epoch = 0;
+  // optimizer
+  int opt_kind = TFG_OPT_SGD;
+  float lr = 0.01f, mu = 0.9f;
+  int64_t global_step = 0;
+  // model
+  tfg::MnistModel* model = nullptr;
+  int64_t launches = 0;
+  std::string err;
+};
+
+namespace tfg {
+
+int fail(tfg_job* j, int rc, const std::string& msg);
+int fail_cuda(tfg_job* j, cudaError_t e, const char* what);
+
+#define TFG_CUDA(j, call)                                         \
+  do {                                                            \
+    cudaError_t e__ = (call);                                     \
+    if (e__ != cudaSuccess) return tfg::fail_cuda((j), e__, #call); \
+  } while (0)
+
+// apply.cu
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed);
+int launch_barrier(tfg_job* j);
+int launch_dense_apply(int kind, float* var, float* accum, const float* const* grads, int n_grads,
+                       float divisor, int64_t count, float lr, float mu, float* const* pull,
+                       int n_pull, cudaStream_t s);
+// smoke.cu
+int launch_smoke(int32_t* out_dev, int n_tasks, cudaStream_t s);
+// model_mnist.cu
+int mnist_build(tfg_job* j, int batch, int math);
+void mnist_destroy(tfg_job* j);
+int mnist_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels);
+int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes);
+int mnist_batch(const tfg_job* j);
+float* mnist_stage_images(tfg_job* j, int slot);
+int32_t* mnist_stage_labels(tfg_job* j, int slot);
+
+}  // namespace tfg

@@ -1,0 +1,358 @@
+// Sparse embedding PS path: partition index math, row gather and
+// scatter-sub with duplicate ids applied in order of appearance.
+//
+// HBM-bound random-row traffic.  Algorithmic bytes per id (fp32 rows of width D, int64
+// ids): gather 8 + 8*D; scatter-sub 8 + 12*D.
+//
+// scatter-sub = stable LSD radix sort of (local row, position) pairs in scratch memory,
+// then one warp per distinct row walks its run in position order, keeping the row in
+// registers: table[row] = fl(table[row] - fl(scale * rows[i])) for each i in turn, which
+// is what a sequential CPU loop over i computes ([TF1.3] scatter_sub on the CPU).
+#include "common.cuh"
+
+namespace tfg {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kKeysPerWarp = 256;
+constexpr int kSortTile = kSortWarps * kKeysPerWarp;  // 2048 keys per block
+
+struct Part {
+  long long vocab;
+  long long ipp;     // vocab / n_shards
+  long long extras;  // vocab % n_shards
+  int n_shards, shard, strategy;
+};
+
+// [TF1.3] embedding_ops: "mod": p = id % S, row = id / S.  "div": p = max(id / (ipp+1),
+// (id - extras) / ipp), row = p < extras ? id % (ipp+1) : (id - extras) % ipp.
+__host__ __device__ inline void locate(const Part& pt, long long id, int* shard, long long* row) {
+  if (pt.strategy == TFG_PART_MOD) {
+    *shard = (int)(id % pt.n_shards);
+    *row = id / pt.n_shards;
+    return;
+  }
+  if (pt.ipp == 0) {  // fewer rows than shards: shard k holds row k
+    *shard = (int)id;
+    *row = 0;
+    return;
+  }
+  long long a = id / (pt.ipp + 1), b = (id - pt.extras) / pt.ipp;
+  long long p = a > b ? a : b;
+  *shard = (int)p;
+  *row = p < pt.extras ? id % (pt.ipp + 1) : (id - pt.extras) % pt.ipp;
+}
+
+static Part make_part(int64_t vocab, int n_shards, int shard, int strategy) {
+  Part p;
+  p.vocab = vocab;
+  p.ipp = vocab / n_shards;
+  p.extras = vocab % n_shards;
+  p.n_shards = n_shards;
+  p.shard = shard;
+  p.strategy = strategy;
+  return p;
+}
+
+static long long shard_rows(int64_t vocab, int n_shards, int shard, int strategy) {
+  if (strategy == TFG_PART_MOD) return shard < vocab ? (vocab - shard + n_shards - 1) / n_shards : 0;
+  return vocab / n_shards + (shard < vocab % n_shards ? 1 : 0);
+}
+
+// ---- gather ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_kernel(const float* __restrict__ table, Part pt, const long long* __restrict__ ids,
+              long long n, int dim, float* __restrict__ out, int* bad) {
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long i = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+    long long id = ids[i];
+    if (id < 0 || id >= pt.vocab) {
+      if (lane == 0 && bad) atomicAdd(bad, 1);
+      continue;
+    }
+    int sh;
+    long long row;
+    locate(pt, id, &sh, &row);
+    if (sh != pt.shard) continue;
+    const float* src = table + row * (long long)dim;
+    float* dst = out + i * (long long)dim;
+    if ((dim & 3) == 0) {
+      for (int c = lane * 4; c < dim; c += 128)
+        *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+    } else {
+      for (int c = lane; c < dim; c += 32) dst[c] = src[c];
+    }
+  }
+}
+
+// ---- stable radix sort of (row key, position) ------------------------------------------
+__global__ void __launch_bounds__(256)
+make_keys_kernel(Part pt, const long long* __restrict__ ids, long long n, uint32_t sentinel,
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long id = ids[i];
+    uint32_t k = sentinel;
+    if (id >= 0 && id < pt.vocab) {
+      int sh;
+      long long row;
+      locate(pt, id, &sh, &row);
+      if (sh == pt.shard) k = (uint32_t)row;
+    }
+    keys[i] = k;
+    vals[i] = (uint32_t)i;
+  }
+}
+
+// digit counts of this warp's 256-key sub-tile into cnt[warp][256]
+__device__ __forceinline__ void warp_digit_counts(const uint32_t* keys, long long n, int shift,
+                                                  uint32_t (*cnt)[256]) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int d = lane; d < 256; d += 32) cnt[w][d] = 0;
+  __syncwarp();
+  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    long long i = base + c * 32 + lane;
+    if (i < n) atomicAdd(&cnt[w][(keys[i] >> shift) & 255u], 1u);
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_kernel(const uint32_t* __restrict__ keys, long long n, int shift, uint32_t* __restrict__ hist,
+                 int n_blocks) {
+  __shared__ uint32_t cnt[kSortWarps][256];
+  warp_digit_counts(keys, n, shift, cnt);
+  __syncthreads();
+  for (int d = threadIdx.x; d < 256; d += kSortThreads) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) s += cnt[w][d];
+    hist[(size_t)d * n_blocks + blockIdx.x] = s;  // digit-major
+  }
+}
+
+// exclusive scan of hist[256 * n_blocks] in place (one block; n_blocks is n / 2048)
+__global__ void __launch_bounds__(1024) sort_scan_kernel(uint32_t* hist, long long total) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (long long base = 0; base < total; base += 1024) {
+    long long i = base + threadIdx.x;
+    uint32_t v = i < total ? hist[i] : 0u, x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sums[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      uint32_t s = warp_sums[lane], t = s;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += y;
+      }
+      warp_sums[lane] = t - s;  // exclusive prefix of warp totals
+    }
+    __syncthreads();
+    uint32_t excl = carry + warp_sums[w] + x - v;
+    if (i < total) hist[i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                    long long n, int shift, const uint32_t* __restrict__ hist, int n_blocks,
+                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
+  __shared__ uint32_t cnt[kSortWarps][256];
+  warp_digit_counts(keys_in, n, shift, cnt);
+  __syncthreads();
+  // cnt[w][d] <- global position of the first key of digit d in warp w's sub-tile
+  for (int d = threadIdx.x; d < 256; d += kSortThreads) {
+    uint32_t run = hist[(size_t)d * n_blocks + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+      uint32_t c = cnt[w][d];
+      cnt[w][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    long long i = base + c * 32 + lane;
+    bool live = i < n;
+    uint32_t k = live ? keys_in[i] : 0u, v = live ? vals_in[i] : 0u;
+    uint32_t d = live ? ((k >> shift) & 255u) : 256u + lane;  // dead lanes match nobody
+    uint32_t peers = __match_any_sync(0xffffffffu, d);
+    uint32_t before = __popc(peers & ((1u << lane) - 1u));
+    uint32_t pos = 0;
+    if (live) pos = cnt[w][d] + before;
+    __syncwarp();
+    if (live && before == 0) cnt[w][d] += __popc(peers);  // lowest lane of the group
+    __syncwarp();
+    if (live) {
+      keys_out[pos] = k;
+      vals_out[pos] = v;
+    }
+  }
+}
+
+// ---- apply the sorted runs -----------------------------------------------------------------
+template <int VEC>
+__global__ void __launch_bounds__(256)
+scatter_sub_runs_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
+                        const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
+                        const float* __restrict__ rows, float scale) {
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long p = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
+    const uint32_t k = keys[p];
+    if (k == sentinel) continue;
+    if (p > 0 && keys[p - 1] == k) continue;  // not the head of its run
+    float* trow = table + (long long)k * dim;
+    for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {  // column panel kept in registers
+      const int c = c0 + lane * VEC;
+      float acc[VEC];
+      if (c < dim) {
+        if (VEC == 4) {
+          float4 t = *reinterpret_cast<const float4*>(trow + c);
+          acc[0] = t.x; acc[1 % VEC] = t.y; acc[2 % VEC] = t.z; acc[3 % VEC] = t.w;
+        } else {
+#pragma unroll
+          for (int u = 0; u < VEC; ++u) acc[u] = trow[c + u];
+        }
+      }
+      for (long long q = p; q < n && keys[q] == k; ++q) {
+        const float* g = rows + (long long)vals[q] * dim;
+        if (c < dim) {
+          float gv[VEC];
+          if (VEC == 4) {
+            float4 t = *reinterpret_cast<const float4*>(g + c);
+            gv[0] = t.x; gv[1 % VEC] = t.y; gv[2 % VEC] = t.z; gv[3 % VEC] = t.w;
+          } else {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) gv[u] = g[c + u];
+          }
+#pragma unroll
+          for (int u = 0; u < VEC; ++u) acc[u] = __fsub_rn(acc[u], __fmul_rn(scale, gv[u]));
+        }
+      }
+      if (c < dim) {
+        if (VEC == 4) {
+          *reinterpret_cast<float4*>(trow + c) = make_float4(acc[0], acc[1 % VEC], acc[2 % VEC], acc[3 % VEC]);
+        } else {
+#pragma unroll
+          for (int u = 0; u < VEC; ++u) trow[c + u] = acc[u];
+        }
+      }
+    }
+  }
+}
+
+static int bits_for(uint32_t v) {
+  int b = 0;
+  while (b < 32 && (v >> b) != 0) ++b;
+  return b < 1 ? 1 : b;
+}
+
+}  // namespace tfg
+
+using namespace tfg;
+
+extern "C" {
+
+int64_t tfg_sparse_shard_rows(int64_t vocab, int n_shards, int shard, int strategy) {
+  if (vocab < 0 || n_shards < 1 || shard < 0 || shard >= n_shards ||
+      (strategy != TFG_PART_MOD && strategy != TFG_PART_DIV))
+    return -1;
+  return shard_rows(vocab, n_shards, shard, strategy);
+}
+
+static int check_sparse(int64_t vocab, int dim, int n_shards, int shard, int strategy, int64_t n) {
+  if (vocab < 1 || dim < 1 || n < 0) return fail(nullptr, TFG_EINVAL, "bad table shape or id count");
+  if (n_shards < 1 || shard < 0 || shard >= n_shards) return fail(nullptr, TFG_EINVAL, "bad shard");
+  if (strategy != TFG_PART_MOD && strategy != TFG_PART_DIV)
+    return fail(nullptr, TFG_EINVAL, "unknown partition strategy");
+  return TFG_OK;
+}
+
+int tfg_sparse_gather(const float* table, int64_t vocab, int dim, int n_shards, int shard,
+                      int strategy, const int64_t* ids, int64_t n, float* out, int* bad, void* stream) {
+  int rc = check_sparse(vocab, dim, n_shards, shard, strategy, n);
+  if (rc) return rc;
+  if (n == 0) return TFG_OK;
+  if (!table || !ids || !out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  Part pt = make_part(vocab, n_shards, shard, strategy);
+  long long blocks = (n + 7) / 8;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  gather_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, pt, (const long long*)ids, n, dim,
+                                                               out, bad);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "gather_kernel");
+  return TFG_OK;
+}
+
+size_t tfg_sparse_scratch_bytes(int64_t n) {
+  if (n < 0) return 0;
+  size_t nb = (size_t)((n + kSortTile - 1) / kSortTile);
+  size_t arr = ((size_t)n * 4 + 255) / 256 * 256;
+  return 4 * arr + ((nb * 256 * 4 + 255) / 256 * 256) + 256;
+}
+
+int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
+                           const int64_t* ids, int64_t n, const float* rows, float scale,
+                           void* scratch, size_t scratch_bytes, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = check_sparse(vocab, dim, n_shards, shard, strategy, n);
+  if (rc) return rc;
+  if (n == 0) return TFG_OK;
+  if (!table || !ids || !rows || !scratch) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  if (n >= (1ll << 31)) return fail(nullptr, TFG_ELIMIT, "more than 2^31-1 ids in one call");
+  if (scratch_bytes < tfg_sparse_scratch_bytes(n)) return fail(nullptr, TFG_EINVAL, "scratch too small");
+  if ((uintptr_t)scratch % 256 != 0) return fail(nullptr, TFG_EINVAL, "scratch must be 256-B aligned");
+  long long srows = shard_rows(vocab, n_shards, shard, strategy);
+  if (srows >= 0xffffffffll) return fail(nullptr, TFG_ELIMIT, "shard has more than 2^32-2 rows");
+  Part pt = make_part(vocab, n_shards, shard, strategy);
+  const uint32_t sentinel = (uint32_t)srows;  // one past the last valid row: sorts last
+  const int n_blocks = (int)((n + kSortTile - 1) / kSortTile);
+  size_t arr = ((size_t)n * 4 + 255) / 256 * 256;
+  char* base = (char*)scratch;
+  uint32_t* keys[2] = {(uint32_t*)base, (uint32_t*)(base + arr)};
+  uint32_t* vals[2] = {(uint32_t*)(base + 2 * arr), (uint32_t*)(base + 3 * arr)};
+  uint32_t* hist = (uint32_t*)(base + 4 * arr);
+  int kb = (int)((n + 255) / 256);
+  if (kb > kNumSMs * 16) kb = kNumSMs * 16;
+  make_keys_kernel<<<kb, 256, 0, s>>>(pt, (const long long*)ids, n, sentinel, keys[0], vals[0]);
+  int cur = 0;
+  const int passes = (bits_for(sentinel) + 7) / 8;
+  for (int p = 0; p < passes; ++p) {
+    sort_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur], n, 8 * p, hist, n_blocks);
+    sort_scan_kernel<<<1, 1024, 0, s>>>(hist, 256ll * n_blocks);
+    sort_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur], vals[cur], n, 8 * p, hist, n_blocks,
+                                                          keys[cur ^ 1], vals[cur ^ 1]);
+    cur ^= 1;
+  }
+  long long blocks = (n + 7) / 8;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  if ((dim & 3) == 0)
+    scatter_sub_runs_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel,
+                                                           rows, scale);
+  else
+    scatter_sub_runs_kernel<1><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel,
+                                                           rows, scale);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "sparse scatter_sub kernels");
+  return TFG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,140 @@
+"""Parity of the sample model's forward/backward and of the whole synchronous step with
+the PyTorch-CPU floating-point reference (oracle/model_ref.py).
+
+Tolerances (stated per math mode, SURVEY.md §7 hard part 3):
+  fp32  -- same arithmetic, different summation order: |d| <= 2e-4 * max|ref| + 1e-6
+  bf16  -- 8-bit-mantissa operands, fp32 accumulate: logits/grads 3e-2 * max|ref|, loss 1e-2 rel
+  tf32  -- 10-bit-mantissa operands:                 logits/grads 5e-3 * max|ref|, loss 2e-3 rel
+"""
+import json
+
+import numpy as np
+import pytest
+
+from k8s_b200.syncps import MNIST_VARS, SyncPSJob, mnist_init, synthetic_batch
+from oracle import model_ref as M
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+TOL = {"fp32": (2e-4, 1e-5), "bf16": (3e-2, 1e-2), "tf32": (5e-3, 2e-3)}
+
+
+def close(got, ref, frac, what):
+    scale = float(np.abs(ref).max())
+    err = float(np.abs(got.reshape(ref.shape) - ref).max())
+    assert err <= frac * scale + 1e-6, "%s: max err %.3e vs scale %.3e (allowed %.1e of scale)" % (what, err, scale, frac)
+
+
+def tf_config(n_workers=0, n_ps=0):
+    c = {"master": ["m-0:2222"]}
+    if n_workers:
+        c["worker"] = ["w-%d:2222" % i for i in range(n_workers)]
+    if n_ps:
+        c["ps"] = ["p-%d:2222" % i for i in range(n_ps)]
+    return json.dumps({"cluster": c, "task": {"type": "master", "index": 0}, "environment": "cloud"})
+
+
+def modes(lib_modes=("fp32", "bf16", "tf32")):
+    return list(lib_modes)
+
+
+@pytest.mark.parametrize("math", modes())
+@pytest.mark.parametrize("batch", [1, 8, 32, 128])
+def test_forward_backward_matches_reference(math, batch):
+    j = SyncPSJob(tf_config(), 0, 1, cuda_device=0)
+    try:
+        j.build_mnist(batch, math=math)
+    except Exception as e:
+        if "not built yet" in str(e):
+            pytest.skip(str(e))
+        raise
+    x, y = synthetic_batch(0, batch)
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    j.forward_backward(0, dx.data_ptr(), dy.data_ptr())
+    j.sync()
+    loss_ref, grads_ref, logits_ref = M.loss_and_grads(mnist_init(0), x, y)
+    frac, loss_rel = TOL[math]
+    close(j.logits(0), logits_ref, frac, "logits")
+    loss = j.loss(0)
+    assert abs(loss - loss_ref) <= loss_rel * abs(loss_ref) + 1e-6
+    for v, name in enumerate(MNIST_VARS):
+        close(j.get_grad(0, v), grads_ref[v], frac, "grad " + name)
+    j.close()
+
+
+@pytest.mark.parametrize("math", modes())
+@pytest.mark.parametrize("kind", ["sgd", "momentum"])
+def test_tf_job_yaml_two_replicas_two_ps_on_one_gpu(math, kind):
+    """BASELINE config 1 (examples/tf_job.yaml: 1 MASTER + 1 WORKER + 2 PS) on one GPU rank,
+    through the host-buffer entry point, three steps."""
+    batch = 16
+    j = SyncPSJob(tf_config(n_workers=1, n_ps=2), 0, 1, cuda_device=0)
+    try:
+        j.build_mnist(batch, math=math)
+    except Exception as e:
+        if "not built yet" in str(e):
+            pytest.skip(str(e))
+        raise
+    j.optimizer(kind, 0.01, 0.9)
+    assert j.local_replicas == [0, 1]
+    params = mnist_init(0)
+    accum = [np.zeros_like(p) for p in params]
+    frac, loss_rel = TOL[math]
+    for step in range(3):
+        batches = [synthetic_batch(r, batch, step) for r in range(2)]
+        loss = j.step([b[0] for b in batches], [b[1] for b in batches])
+        loss_ref, _ = M.sync_step(params, accum, batches, kind, 0.01, 0.9)
+        assert abs(loss - loss_ref) <= (loss_rel * (step + 1)) * abs(loss_ref) + 1e-6, (step, loss, loss_ref)
+        for v, name in enumerate(MNIST_VARS):
+            close(j.get_var(v), params[v], frac * (step + 1) * 0.05 + 1e-6, "step %d param %s" % (step, name))
+    assert j.global_step == 3
+    assert [j.placement(v)["ps_task"] for v in range(8)] == [0, 1, 0, 1, 0, 1, 0, 1]
+    j.close()
+
+
+def test_two_emulated_gpu_ranks_match_single_rank_bitwise():
+    """The multi-rank exchange adds no arithmetic of its own: 2 replicas on 2 (emulated) GPU
+    ranks give bit-identical parameters to the same 2 replicas hosted by 1 rank."""
+    batch = 8
+    cfg = tf_config(n_workers=1, n_ps=2)
+    one = SyncPSJob(cfg, 0, 1, cuda_device=0)
+    one.build_mnist(batch)
+    two = [SyncPSJob(cfg, r, 2, cuda_device=0) for r in range(2)]
+    for j in two:
+        j.build_mnist(batch)
+    two[0].attach_local_peer(1, two[1])
+    two[1].attach_local_peer(0, two[0])
+    batches = [synthetic_batch(r, batch) for r in range(2)]
+    dev = [(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()) for x, y in batches]
+    one.step([b[0] for b in batches], [b[1] for b in batches])
+    for r, j in enumerate(two):
+        j.forward_backward(0, dev[r][0].data_ptr(), dev[r][1].data_ptr())
+    for j in two:
+        j.sync()
+    for j in two:
+        j.push_apply_pull(with_barriers=False)
+    for j in two:
+        j.sync()
+    for v in range(8):
+        a = one.get_var(v)
+        for j in two:
+            np.testing.assert_array_equal(a.view(np.uint32), j.get_var(v).view(np.uint32))
+    for j in two + [one]:
+        j.close()
+
+
+def test_step_is_deterministic():
+    batch = 32
+    outs = []
+    for _ in range(2):
+        j = SyncPSJob(tf_config(), 0, 1, cuda_device=0)
+        j.build_mnist(batch)
+        x, y = synthetic_batch(0, batch)
+        losses = [j.step([x], [y]) for _ in range(3)]
+        outs.append((losses, [j.get_var(v).copy() for v in range(8)]))
+        j.close()
+    assert outs[0][0] == outs[1][0]
+    for a, b in zip(outs[0][1], outs[1][1]):
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert outs[0][0][2] < outs[0][0][0]      # three SGD steps on one batch reduce its loss
