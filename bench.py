@@ -1,0 +1,421 @@
+#!/usr/bin/env python
+"""bench.py -- examples/sec of the synchronous PS step (BASELINE.json metric) on N B200s.
+
+    python bench.py --gpus 1 --steps K --warmup W            # this repo's CUDA path
+    torchrun ... bench.py --gpus N --steps K --warmup W       # one rank per GPU
+    python bench.py --impl reference ...                      # CPU arm (oracle port, see below)
+
+A step = forward + backward of the sample MNIST CNN on every training replica, gradient
+push + mean + optimizer apply on the shard owners, parameter pull.  The
+workload is a TfJob document built the way examples/tf_job_gpu.yaml (N = 1: one MASTER, no
+PS, no exchange) and BASELINE config 3 (N > 1: N replicas + N PS shards) describe it, run
+through this repo's trainer to obtain each rank's TF_CONFIG.
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for what each key means.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BATCH = 128          # examples per replica per step
+N_INPUT_SETS = 8     # distinct resident input batches cycled through
+FLOP_PER_EXAMPLE_FWD = 2 * (28 * 28 * 32 * 25 + 14 * 14 * 64 * 800 + 3136 * 1024 + 1024 * 10)
+
+
+def parse_args(argv=None):
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH, help="examples per replica per step")
+    ap.add_argument("--math", default=os.environ.get("TFGRAFT_MATH", "auto"),
+                    choices=["auto", "fp32", "bf16", "tf32"])
+    ap.add_argument("--layout", default="balanced", choices=["logical", "balanced"])
+    ap.add_argument("--opt", default="momentum", choices=["sgd", "momentum", "nesterov"])
+    ap.add_argument("--ps-params", type=int, default=256 << 20,
+                    help="parameters of the PS-update roofline probe (BASELINE config 5)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args(argv)
+
+
+def tf_job_doc(n_gpus: int) -> dict:
+    """The TfJob document of the benchmark: tf_job_gpu.yaml's shape at N = 1, BASELINE
+    config 3's (1 MASTER + N-1 WORKER + N PS) beyond."""
+    tmpl = {"spec": {"containers": [{"image": "tf_sample", "name": "tensorflow",
+                                     "resources": {"limits": {"nvidia.com/gpu": 1}}}],
+                     "restartPolicy": "OnFailure"}}
+    specs = [{"tfReplicaType": "MASTER", "template": tmpl}]
+    if n_gpus > 1:
+        specs.append({"replicas": n_gpus - 1, "tfReplicaType": "WORKER", "template": tmpl})
+        specs.append({"replicas": n_gpus, "tfReplicaType": "PS"})
+    return {"apiVersion": "tensorflow.org/v1alpha1", "kind": "TfJob",
+            "metadata": {"name": "bench-sync-ps"}, "spec": {"RuntimeId": "b200", "replicaSpecs": specs}}
+
+
+def tf_config_for_rank(n_gpus: int, rank: int) -> str:
+    """TF_CONFIG of the training replica hosted by GPU `rank`, produced by the trainer."""
+    from k8s_b200 import spec as S
+    from k8s_b200 import trainer as T
+    be = T.RecordingBackend()
+    tj = T.TrainingJob(be, S.tf_job_from_dict(tf_job_doc(n_gpus)))
+    tj.reconcile(S.ControllerConfig())
+    tj.reconcile(S.ControllerConfig())
+    if tj.job.status.phase == S.PHASE_FAILED:
+        raise RuntimeError(tj.job.status.reason)
+    name = "bench-sync-ps-%s-b200-%d" % (("master", 0) if rank == 0 else ("worker", rank - 1))
+    env = [c["env"] for c in be.jobs[name]["spec"]["template"]["spec"]["containers"]][0]
+    return [e["value"] for e in env if e["name"] == "TF_CONFIG"][0]
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def measured_peaks() -> dict:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
+            "source": "fallback (B200_PROFILING.md)"}
+
+
+LR = 0.001   # SURVEY.md §8d says 0.01; with sigma=0.1 weights and N(0,1) images that overshoots
+             # to inf within a few steps, so the timed runs use 0.001 (timing is unaffected)
+
+
+# ---- CPU arm: the oracle port of the step on the box's host cores ---------------------------
+def cpu_step_rate(n_replicas: int, batch: int, opt: str, steps: int, warmup: int):
+    """examples/s of the oracle's synchronous step (torch-CPU fp32 forward/backward per
+    replica + the C oracle's apply), all host threads.  The only other place besides tests
+    and smoke() that executes oracle/."""
+    import torch
+    from k8s_b200.syncps import mnist_init, synthetic_batch
+    from oracle import model_ref as M
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    params = mnist_init(0)
+    accum = [np.zeros_like(p) for p in params]
+    sets = [[synthetic_batch(r, batch, s) for r in range(n_replicas)] for s in range(2)]
+    for s in range(warmup):
+        M.sync_step(params, accum, sets[s % 2], opt, LR, 0.9)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        M.sync_step(params, accum, sets[s % 2], opt, LR, 0.9)
+    dt = time.perf_counter() - t0
+    return n_replicas * batch * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference(a) -> dict:
+    """--impl reference.  The reference's own implementation of this path is TensorFlow
+    1.3's gRPC PS runtime launched by a Go operator: neither can be built or installed in
+    this image (DESIGN.md "Oracle"), so the arm times the oracle port ("kind": "port")."""
+    n = a.gpus
+    value, ms, cores = cpu_step_rate(n, a.batch, a.opt, a.steps, max(a.warmup, 1))
+    return {
+        "impl": "reference", "metric": "examples/sec sync-PS step", "value": value, "unit": "examples/s",
+        "n_gpus": n, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": config_dict(a, n, "fp32"),
+        "cpu_baseline": {"value": value, "unit": "examples/s", "cores": cores, "kind": "port",
+                         "sample": "%d full steps of %d replicas x %d examples (whole workload, "
+                                   "oracle/model_ref.py + oracle.c)" % (a.steps, n, a.batch)},
+        "e2e": {"value": value, "unit": "examples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
+def config_dict(a, n: int, math: str) -> dict:
+    return {
+        "workload": ("tf_sample MNIST CNN sync-PS step: %s" %
+                     ("examples/tf_job_gpu.yaml shape, 1 MASTER on 1 B200, no PS exchange" if n == 1 else
+                      "1 MASTER + %d WORKER + %d PS shards on %d B200 (BASELINE config 3 shape)" % (n - 1, n, n))),
+        "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
+        "optimizer": a.opt, "lr": LR, "math": math, "layout": a.layout,
+        "params": 3274634, "parallelism": "dp%d + %d PS shards" % (n, n),
+        "l2": "flushed between timed steps (256 MiB write, untimed)",
+    }
+
+
+# ---- algorithmic work per launch of every kernel in the step (DESIGN.md "Kernels") ----------
+def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int):
+    """-> (bound, amount per launch): FLOPs for the contractions ("tensor"), bytes for the
+    rest ("hbm").  B = examples per replica."""
+    M2 = B * 196
+    gemm = {"gemm conv2 fwd": (M2, 64, 800), "gemm conv2 dgrad": (M2, 800, 64), "gemm conv2 wgrad": (800, 64, M2),
+            "gemm fc1 fwd": (B, 1024, 3136), "gemm fc1 dgrad": (B, 3136, 1024), "gemm fc1 wgrad": (3136, 1024, B),
+            "gemm fc2 fwd": (B, 10, 1024), "gemm fc2 dgrad": (B, 1024, 10), "gemm fc2 wgrad": (1024, 10, B)}
+    if name in gemm:
+        m, n, k = gemm[name]
+        return "tensor", 2.0 * m * n * k
+    f = 4
+    hbm = {
+        "conv1_pool_relu_kernel": B * 784 * f + B * 6272 * (f + 1),
+        "conv1_bwd_kernel": B * 784 * f + B * 6272 * (f + 1) + B * 832 * f,
+        "im2col_kernel": B * 6272 * f + M2 * 800 * f,
+        "pool_relu_kernel": M2 * 64 * f + B * 3136 * (f + 1),
+        "unpool_kernel": B * 3136 * (2 * f + 1) + M2 * 64 * f,
+        "relu_mask_kernel": B * 3136 * 3 * f,
+        "col2im_mask_kernel": M2 * 800 * f + B * 6272 * 2 * f,
+        "softmax_xent_kernel": B * (10 * 2 * f + 2 * f),
+        "push_apply_pull_kernel": n_params * f * (n_replicas + 2 + (2 if opt != "sgd" else 0)),
+    }
+    if name in hbm:
+        return "hbm", float(hbm[name])
+    return "hbm", None
+
+
+def ps_update_probe(lib, L, torch, stream, n_params: int, opt: str, peaks: dict) -> dict:
+    """PS-update GB/s of BASELINE config 5's dense shard: one fused apply launch over
+    n_params fp32 parameters resident in HBM (>> L2), CUDA events on the launching stream."""
+    kind = L.OPT_KINDS[opt]
+    with torch.cuda.stream(stream):
+        v = torch.randn(n_params, device="cuda")
+        g = torch.randn(n_params, device="cuda")
+        m = torch.zeros(n_params, device="cuda")
+        ga = L.ptr_array([g])
+        times = []
+        for i in range(8):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            lib.check(lib.dense_apply(kind, v.data_ptr(), m.data_ptr(), ga, 1, 1.0, n_params, LR, 0.9, None, 0,
+                                      stream.cuda_stream))
+            e1.record(stream)
+            stream.synchronize()
+            if i >= 3:
+                times.append(e0.elapsed_time(e1))
+    bpp = 12 if opt == "sgd" else 20
+    ms = float(np.mean(times))
+    gbs = bpp * n_params / (ms * 1e-3) / 1e9
+    return {"kernel": "push_apply_pull_kernel", "params": n_params, "optimizer": opt, "bytes_per_param": bpp,
+            "ms": ms, "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+            "peak_source": peaks["source"]}
+
+
+def run_graft(a) -> dict:
+    import torch
+    import torch.distributed as dist
+    from k8s_b200 import lib as L
+    from k8s_b200.syncps import SyncPSJob, synthetic_batch
+
+    n = a.gpus
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != n:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torchrun --nproc-per-node %d" % (n, world, n))
+    lib = L.load()
+    if lib.device_count_checked() <= local:
+        raise SystemExit("no CUDA device %d: the CUDA path has no CPU fallback" % local)
+    torch.cuda.set_device(local)
+    if n > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stream = torch.cuda.Stream()
+    peaks = measured_peaks()
+
+    math = a.math
+    job = None
+    for cand in (["bf16", "fp32"] if math == "auto" else [math]):
+        job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
+        try:
+            job.build_mnist(a.batch, math=cand, layout=a.layout)
+            math = cand
+            break
+        except L.TfgError as e:
+            job.close()
+            job = None
+            if math != "auto" or "not built yet" not in e.message:
+                raise
+    job.optimizer(a.opt, LR, 0.9)
+    job.connect_peers(dist if n > 1 else None)
+    slots = job.local_replicas
+    B = a.batch
+
+    # synthetic inputs: resident in HBM for `value`, in pinned host memory for `e2e`
+    host, dev = [], []
+    for s in range(N_INPUT_SETS):
+        hx, hy, dx, dy = [], [], [], []
+        for r in slots:
+            x, y = synthetic_batch(r, B, s)
+            px, py = torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()
+            hx.append(px); hy.append(py)
+            dx.append(px.cuda()); dy.append(py.cuda())
+        host.append((hx, hy)); dev.append((dx, dy))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+
+    def barrier():
+        if n > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """K steps, each bracketed by events on the job's stream, L2 flushed (untimed) in
+        between; returns the summed device time in ms, max over ranks."""
+        evs = []
+        barrier()
+        for k in range(steps):
+            with torch.cuda.stream(stream):
+                flush.fill_(k & 0xFF)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            fn(k)
+            e1.record(stream)
+            evs.append((e0, e1))
+        barrier()
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        if n > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def step_dev(k):
+        dx, dy = dev[k % N_INPUT_SETS]
+        job.step_dev(dx, dy)
+
+    losses = []
+
+    def step_e2e(k):
+        hx, hy = host[k % N_INPUT_SETS]
+        losses.append(job.step(hx, hy))
+
+    for k in range(max(a.warmup, 3)):
+        step_dev(k)
+    job.sync()
+    launches0 = job.launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_dev = timed(step_dev, a.steps)
+    launches_timed = job.launches - launches0
+    for k in range(3):
+        step_e2e(k)
+    ms_e2e = timed(step_e2e, a.steps)
+    clocks = sampler.stop()
+
+    # per-kernel device time over another K steps (events behind every launch)
+    job.profile(True)
+    for k in range(a.steps):
+        step_dev(k)
+    prof = job.profile_report()
+    job.profile(False)
+    examples = a.steps * B * n
+    value = examples / (ms_dev * 1e-3)
+    e2e = examples / (ms_e2e * 1e-3)
+    out = {
+        "metric": "examples/sec sync-PS step", "value": value, "unit": "examples/s", "n_gpus": n,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_dev / a.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"fp32": "f32", "bf16": "bf16", "tf32": "tf32"}[math], "data": "synthetic",
+        "config": config_dict(a, n, math),
+        "e2e": {"value": e2e, "unit": "examples/s", "ms_per_step": ms_e2e / a.steps,
+                "h2d_bytes_per_step": n * B * (784 * 4 + 4),
+                "d2h_bytes_per_step": 4 * n, "last_loss": losses[-1] if losses else None},
+        "gpu_launches": int(launches_timed),
+        "clocks": clocks,
+    }
+    if rank == 0:
+        total = sum(v["ms"] for v in prof.values()) or 1.0
+        top = max(prof, key=lambda k_: prof[k_]["ms"])
+        bound, amount = algorithmic_work(top, B, 3274634, a.opt, n)
+        per_launch_ms = prof[top]["ms"] / prof[top]["count"]
+        roof = {"kernel": top, "bound": bound, "share_of_step": prof[top]["ms"] / total,
+                "ms_per_launch": per_launch_ms, "traffic": None, "peak_source": peaks["source"]}
+        if amount is not None and bound == "tensor":
+            ach = amount / (per_launch_ms * 1e-3) / 1e12
+            roof.update(achieved=ach, peak=peaks["bf16_tflops_sustained"], unit="TFLOP/s",
+                        frac=ach / peaks["bf16_tflops_sustained"], algorithmic_flops=amount)
+        elif amount is not None:
+            ach = amount / (per_launch_ms * 1e-3) / 1e9
+            roof.update(achieved=ach, peak=peaks["hbm_gbs"], unit="GB/s", frac=ach / peaks["hbm_gbs"],
+                        algorithmic_bytes=amount)
+        out["roofline"] = roof
+        out["kernels"] = {k_: {"count": v["count"], "ms_per_launch": v["ms"] / v["count"],
+                               "share": v["ms"] / total} for k_, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+    job.close()
+    del dev, flush
+    torch.cuda.empty_cache()
+    if rank == 0:
+        out["ps_update"] = ps_update_probe(lib, L, torch, stream, a.ps_params, a.opt, peaks)
+        if n == 1 and not a.no_cpu_baseline:
+            v, ms, cores = cpu_step_rate(1, B, a.opt, 250, 3)
+            out["cpu_baseline"] = {"value": v, "unit": "examples/s", "cores": cores, "kind": "port",
+                                   "sample": "250 full steps of 1 replica x %d examples (oracle port, "
+                                             "torch-CPU fwd/bwd + C apply)" % B}
+    if n > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def main(argv=None) -> int:
+    a = parse_args(argv)
+    rank = int(os.environ.get("RANK", "0"))
+    if a.impl == "reference":
+        if rank == 0:
+            print(json.dumps(run_reference(a)), flush=True)
+        return 0
+    out = run_graft(a)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -233,6 +233,12 @@ int tfg_job_sync(tfg_job* job);
 /* kernels launched by this job since creation (bench.py's gpu_launches) */
 int64_t tfg_launch_count(const tfg_job* job);
 
+/* per-kernel device time of this job's launches, measured with CUDA events on the job's
+ * stream (bench.py's roofline leg).  enable(1) starts a fresh record; report() writes
+ * {"kernel":{"count":n,"ms":total},...} and starts over. */
+int tfg_profile_enable(tfg_job* job, int on);
+int tfg_profile_report(tfg_job* job, char* json_out, size_t json_cap);
+
 /* ---- smoke workload (A9) -----------------------------------------------------------
  * For every task of every job in the cluster: c = a * b with
  * a = b = arange(100).reshape(10,10), int32 (tf_smoke.py:53-60).  out_host receives

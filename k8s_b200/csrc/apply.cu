@@ -182,7 +182,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
   cudaError_t e = launch_kind(j->opt_kind, [&](auto k) {
     push_apply_pull_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(a);
   });
-  j->launches++;
+  prof_mark(j, "push_apply_pull_kernel");
   if (e != cudaSuccess) return fail_cuda(j, e, "push_apply_pull_kernel");
   return TFG_OK;
 }
@@ -277,7 +277,7 @@ int launch_barrier(tfg_job* j) {
   a.n = j->n_gpus;
   a.epoch = ++j->epoch;
   barrier_kernel<<<1, 32, 0, j->stream>>>(a);
-  j->launches++;
+  prof_mark(j, "barrier_kernel");
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(j, e, "barrier_kernel");
   return TFG_OK;

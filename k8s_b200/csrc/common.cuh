@@ -79,6 +79,10 @@ struct tfg_job {
   // model
   tfg::MnistModel* model = nullptr;
   int64_t launches = 0;
+  // optional per-kernel timing: one event after every launch (see prof_mark)
+  bool prof_on = false;
+  std::vector<std::pair<const char*, cudaEvent_t>> prof_ev;
+  size_t prof_used = 0;
   std::string err;
 };
 
@@ -92,6 +96,11 @@ int fail_cuda(tfg_job* j, cudaError_t e, const char* what);
     cudaError_t e__ = (call);                                     \
     if (e__ != cudaSuccess) return tfg::fail_cuda((j), e__, #call); \
   } while (0)
+
+// Count a launch and, when profiling is on, drop an event behind it.  The job's stream is
+// serial, so the span between consecutive events is the kernel's duration plus any gap in
+// front of it.
+void prof_mark(tfg_job* j, const char* what);
 
 // apply.cu
 int launch_job_apply(tfg_job* j, bool summed_local, int n_summed);

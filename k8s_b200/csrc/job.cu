@@ -26,6 +26,19 @@ int fail_cuda(tfg_job* j, cudaError_t e, const char* what) {
   return fail(j, rc, m);
 }
 
+void prof_mark(tfg_job* j, const char* what) {
+  j->launches++;
+  if (!j->prof_on) return;
+  if (j->prof_used == j->prof_ev.size()) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) { j->prof_on = false; return; }
+    j->prof_ev.emplace_back(what, e);
+  }
+  j->prof_ev[j->prof_used].first = what;
+  cudaEventRecord(j->prof_ev[j->prof_used].second, j->stream);
+  j->prof_used++;
+}
+
 // [TF1.3] replica_device_setter default ps_ops (python/training/device_setter.py).
 static bool is_ps_op(const std::string& t) {
   return t == "Variable" || t == "VariableV2" || t == "VarHandleOp";
@@ -155,6 +168,7 @@ int tfg_job_destroy(tfg_job* j) {
     cudaSetDevice(j->device);
     cudaStreamSynchronize(j->stream);
     mnist_destroy(j);
+    for (auto& pe : j->prof_ev) cudaEventDestroy(pe.second);
     for (void* p : j->ipc_opened) cudaIpcCloseMemHandle(p);
     cudaFree(j->params);
     cudaFree(j->accum);
@@ -656,6 +670,48 @@ int tfg_job_sync(tfg_job* j) {
 
 int64_t tfg_launch_count(const tfg_job* j) { return j ? j->launches : -1; }
 
+int tfg_profile_enable(tfg_job* j, int on) {
+  if (!j || !j->bound) return fail(j, TFG_ESTATE, "job is not bound to a device");
+  TFG_CUDA(j, cudaSetDevice(j->device));
+  TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+  j->prof_used = 0;
+  j->prof_on = on != 0;
+  if (j->prof_on) prof_mark(j, "(start)");
+  return TFG_OK;
+}
+
+int tfg_profile_report(tfg_job* j, char* json_out, size_t cap) {
+  if (!j || !j->bound || !json_out || cap < 3) return fail(j, TFG_EINVAL, "bad argument");
+  TFG_CUDA(j, cudaSetDevice(j->device));
+  TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+  std::vector<std::pair<std::string, std::pair<long long, double>>> agg;
+  for (size_t i = 1; i < j->prof_used; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, j->prof_ev[i - 1].second, j->prof_ev[i].second) != cudaSuccess) continue;
+    std::string name = j->prof_ev[i].first;
+    if (name == "(start)") continue;   // a marker, not a kernel
+    bool found = false;
+    for (auto& a : agg)
+      if (a.first == name) { a.second.first++; a.second.second += ms; found = true; break; }
+    if (!found) agg.push_back({name, {1, (double)ms}});
+  }
+  std::string out = "{";
+  for (size_t i = 0; i < agg.size(); ++i) {
+    char buf[96];
+    snprintf(buf, sizeof buf, "{\"count\":%lld,\"ms\":%.6f}", agg[i].second.first, agg[i].second.second);
+    if (i) out += ",";
+    json::escape(agg[i].first, &out);
+    out += ":";
+    out += buf;
+  }
+  out += "}";
+  j->prof_used = 0;
+  if (j->prof_on) prof_mark(j, "(start)");
+  if (out.size() + 1 > cap) return fail(j, TFG_ELIMIT, "json_out too small");
+  memcpy(json_out, out.c_str(), out.size() + 1);
+  return TFG_OK;
+}
+
 // ---- smoke (A9) ----------------------------------------------------------------------
 int tfg_smoke(tfg_job* j, int all_tasks, int32_t* out_host, size_t cap, int* n_tasks_out) {
   if (!j || !out_host) return fail(j, TFG_EINVAL, "NULL argument");
@@ -678,7 +734,7 @@ int tfg_smoke(tfg_job* j, int all_tasks, int32_t* out_host, size_t cap, int* n_t
       int gpu = (int)((replica_base + i) % j->n_gpus);
       if (all_tasks || gpu == j->gpu_rank) {
         rc = launch_smoke(d + 100 * (size_t)t, 1, j->stream);
-        j->launches++;
+        prof_mark(j, "smoke_mul_kernel");
         if (rc) { cudaFree(d); return fail(j, rc, "smoke kernel launch failed"); }
       }
     }

@@ -368,13 +368,13 @@ static inline int blocks_for(long long n, int per = 256) {
 
 #define LAUNCH_OK(j, what)                                          \
   do {                                                              \
-    (j)->launches++;                                                \
+    prof_mark((j), what);                                           \
     cudaError_t e__ = cudaGetLastError();                           \
     if (e__ != cudaSuccess) return fail_cuda((j), e__, what);       \
   } while (0)
 
 // C = A*B through the CUDA-core kernel.  splits > 1 needs `partial` of splits*M*N floats.
-static int sgemm(tfg_job* j, const float* A, bool a_kcontig, long long sam, long long sak,
+static int sgemm(tfg_job* j, const char* name, const float* A, bool a_kcontig, long long sam, long long sak,
                  const float* Bm, bool b_ncontig, long long sbk, long long sbn, float* C, int M, int N,
                  int K, GemmEpi epi, int splits, float* partial) {
   dim3 grid((N + 63) / 64, (M + 63) / 64, splits);
@@ -390,7 +390,7 @@ static int sgemm(tfg_job* j, const float* A, bool a_kcontig, long long sam, long
     sgemm_kernel<false, true><<<grid, 256, 0, s>>>(A, Bm, dst, M, N, K, sam, sak, sbk, sbn, kps, e);
   else
     sgemm_kernel<false, false><<<grid, 256, 0, s>>>(A, Bm, dst, M, N, K, sam, sak, sbk, sbn, kps, e);
-  LAUNCH_OK(j, "sgemm_kernel");
+  LAUNCH_OK(j, name);
   if (splits > 1) {
     const int MN = M * N;
     colsum_stage2_kernel<<<(MN + 255) / 256, 256, 0, s>>>(partial, C, splits, MN, MN);
@@ -525,16 +525,16 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     im2col_kernel<float><<<blocks_for((long long)M2 * 200), 256, 0, st>>>(s.a1, s.col, nullptr, B);
     LAUNCH_OK(j, "im2col_kernel");
     // y2[M2,64] = col[M2,800] * W2[800,64] + b2
-    if ((rc = sgemm(j, s.col, true, 800, 1, par(2), true, 64, 1, s.y2, M2, 64, 800,
+    if ((rc = sgemm(j, "gemm conv2 fwd", s.col, true, 800, 1, par(2), true, 64, 1, s.y2, M2, 64, 800,
                     GemmEpi{par(3), nullptr, 0}, 1, nullptr))) return rc;
     pool_relu_kernel<<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.y2, s.a2, s.idx2, B, 7, 64);
     LAUNCH_OK(j, "pool_relu_kernel");
     // h1[B,1024] = relu(a2[B,3136] * W3[3136,1024] + b3)
-    if ((rc = sgemm(j, s.a2, true, 3136, 1, par(4), true, 1024, 1, s.h1, B, 1024, 3136,
+    if ((rc = sgemm(j, "gemm fc1 fwd", s.a2, true, 3136, 1, par(4), true, 1024, 1, s.h1, B, 1024, 3136,
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
   }
   // logits[B,10] = h1 * W4[1024,10] + b4
-  if ((rc = sgemm(j, s.h1, true, 1024, 1, par(6), true, 10, 1, s.logits, B, 10, 1024,
+  if ((rc = sgemm(j, "gemm fc2 fwd", s.h1, true, 1024, 1, par(6), true, 10, 1, s.logits, B, 10, 1024,
                   GemmEpi{par(7), nullptr, 0}, 1, nullptr))) return rc;
   softmax_xent_kernel<<<(B + 7) / 8, 256, 0, st>>>(s.logits, labels, s.dlogits, s.loss_vec, B);
   LAUNCH_OK(j, "softmax_xent_kernel");
@@ -543,30 +543,30 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
 
   // ---------------- backward ----------------
   // dW4[1024,10] = h1^T * dlogits ; db4 = colsum(dlogits)
-  if ((rc = sgemm(j, s.h1, false, 1, 1024, s.dlogits, true, 10, 1, grd(6), 1024, 10, B,
+  if ((rc = sgemm(j, "gemm fc2 wgrad", s.h1, false, 1, 1024, s.dlogits, true, 10, 1, grd(6), 1024, 10, B,
                   GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
   if ((rc = colsum(j, s.dlogits, grd(7), B, 10, s.scratch))) return rc;
   // dh1[B,1024] = dlogits * W4^T, masked by h1 > 0
-  if ((rc = sgemm(j, s.dlogits, true, 10, 1, par(6), false, 1, 10, s.dh1, B, 1024, 10,
+  if ((rc = sgemm(j, "gemm fc2 dgrad", s.dlogits, true, 10, 1, par(6), false, 1, 10, s.dh1, B, 1024, 10,
                   GemmEpi{nullptr, s.h1, 0}, 1, nullptr))) return rc;
   if ((rc = colsum(j, s.dh1, grd(5), B, 1024, s.scratch))) return rc;
   if (tc) {
     if ((rc = mnist_tc_backward(j, slot))) return rc;  // dW3, da2, dcol, dW2 on the tensor path
   } else {
     // dW3[3136,1024] = a2^T * dh1
-    if ((rc = sgemm(j, s.a2, false, 1, 3136, s.dh1, true, 1024, 1, grd(4), 3136, 1024, B,
+    if ((rc = sgemm(j, "gemm fc1 wgrad", s.a2, false, 1, 3136, s.dh1, true, 1024, 1, grd(4), 3136, 1024, B,
                     GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
     // da2[B,3136] = dh1 * W3^T
-    if ((rc = sgemm(j, s.dh1, true, 1024, 1, par(4), false, 1, 1024, s.da2, B, 3136, 1024,
+    if ((rc = sgemm(j, "gemm fc1 dgrad", s.dh1, true, 1024, 1, par(4), false, 1, 1024, s.da2, B, 3136, 1024,
                     GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
     unpool_kernel<float><<<blocks_for((long long)B * 3136), 256, 0, st>>>(
         s.da2, s.a2, s.idx2, s.dy2, nullptr, nullptr, B, 7, 64);
     LAUNCH_OK(j, "unpool_kernel");
     // dW2[800,64] = col^T * dy2, split-K over M2
-    if ((rc = sgemm(j, s.col, false, 1, 800, s.dy2, true, 64, 1, grd(2), 800, 64, M2,
+    if ((rc = sgemm(j, "gemm conv2 wgrad", s.col, false, 1, 800, s.dy2, true, 64, 1, grd(2), 800, 64, M2,
                     GemmEpi{nullptr, nullptr, 0}, kSplitW2, s.scratch))) return rc;
     // dcol[M2,800] = dy2 * W2^T
-    if ((rc = sgemm(j, s.dy2, true, 64, 1, par(2), false, 1, 64, s.dcol, M2, 800, 64,
+    if ((rc = sgemm(j, "gemm conv2 dgrad", s.dy2, true, 64, 1, par(2), false, 1, 64, s.dcol, M2, 800, 64,
                     GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
   }
   // db2 = sum over pooled positions of the masked pooled gradient

@@ -206,6 +206,14 @@ class SyncPSJob:
     def sync(self) -> None:
         self._ck(self.lib.job_sync(self.h))
 
+    def profile(self, on: bool = True) -> None:
+        self._ck(self.lib.profile_enable(self.h, int(on)))
+
+    def profile_report(self) -> Dict[str, Dict[str, float]]:
+        buf = C.create_string_buffer(1 << 16)
+        self._ck(self.lib.profile_report(self.h, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
     @property
     def launches(self) -> int:
         return self.lib.launch_count(self.h)
