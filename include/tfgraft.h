@@ -200,6 +200,33 @@ int tfg_sparse_scatter_sub(float* table_dev, int64_t vocab, int dim, int n_shard
                            const float* rows_dev, float scale,
                            void* scratch_dev, size_t scratch_bytes, void* stream);
 
+/* Scatter-sub for callers that cannot allocate device memory.  No counterpart in the
+ * reference: this entry point exists only for this library's users.
+ *
+ * tfg_sparse_scatter_sub needs a scratch buffer, which somebody has to cudaMalloc.  Some
+ * callers cannot: a PS process that shares its GPU with a framework whose allocator has
+ * already claimed all device memory (the reference's default PS starts TensorFlow with
+ * per_process_gpu_memory_fraction = 1.0, so a later cudaMalloc in that process fails), or
+ * a step loop that must not take the device-wide synchronisation cudaMalloc/cudaFree
+ * imply.  For them the scratch lives inside the library image, in a fixed device array of
+ * TFG_SPARSE_STATIC_SCRATCH_BYTES (about 1.03 MiB) that every GPU using the library keeps
+ * until the process exits.  The caller still passes table, ids and rows; results are
+ * identical to tfg_sparse_scatter_sub.
+ *   - n > TFG_SPARSE_STATIC_MAX_IDS is rejected with TFG_ELIMIT (split the batch: applying
+ *     consecutive slices of ids in order gives the same table).
+ *   - The first call on each device looks up the array's device address, once, with that
+ *     device current; make that first call before starting any stream capture.
+ *   - The call itself performs no cudaMalloc / cudaFree and calls no allocating library.
+ *   - All calls on a device share the one array and it keeps the previous call's contents.
+ *     Nothing in it has to start at zero (every word a call reads it has written first),
+ *     but two calls that overlap on the GPU -- different streams, or different host
+ *     threads -- race on it: issue them on one stream, or serialise them yourself. */
+#define TFG_SPARSE_STATIC_MAX_IDS 65536
+#define TFG_SPARSE_STATIC_SCRATCH_BYTES 1081600
+int tfg_sparse_scatter_sub_static(float* table_dev, int64_t vocab, int dim, int n_shards,
+                                  int shard, int strategy, const int64_t* ids_dev, int64_t n,
+                                  const float* rows_dev, float scale, void* stream);
+
 /* ---- the sample model (A16) and the full step --------------------------------------
  * The reference's examples name an image (tf_sample) whose only arithmetic is the smoke
  * multiply below; the MNIST CNN is build-defined with the canonical mnist_deep shapes

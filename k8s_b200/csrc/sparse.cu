@@ -355,4 +355,39 @@ int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, i
   return TFG_OK;
 }
 
+// ---- scatter-sub without any allocation ---------------------------------------------------
+// For callers that cannot cudaMalloc (see include/tfgraft.h): the sort scratch is this
+// file-scope device array, part of the library image on every GPU that loads it.  In host
+// code `g_static_scratch` is only a handle for the runtime, not a device address, so the
+// address is fetched once per device with cudaGetSymbolAddress and that pointer is what the
+// kernels receive.
+static __device__ __align__(256) unsigned char g_static_scratch[TFG_SPARSE_STATIC_SCRATCH_BYTES];
+
+static void* g_static_scratch_addr[64] = {};   // per CUDA device ordinal, filled on first use
+
+int tfg_sparse_scatter_sub_static(float* table, int64_t vocab, int dim, int n_shards, int shard,
+                                  int strategy, const int64_t* ids, int64_t n, const float* rows,
+                                  float scale, void* stream) {
+  if (n > TFG_SPARSE_STATIC_MAX_IDS)
+    return fail(nullptr, TFG_ELIMIT,
+                "tfg_sparse_scatter_sub_static: n = " + std::to_string(n) + " ids exceeds the built-in "
+                "scratch (TFG_SPARSE_STATIC_MAX_IDS = " + std::to_string(TFG_SPARSE_STATIC_MAX_IDS) +
+                "); split the batch or use tfg_sparse_scatter_sub with your own scratch");
+  static_assert(TFG_SPARSE_STATIC_SCRATCH_BYTES % 256 == 0, "scratch size keeps 256-B alignment");
+  if (tfg_sparse_scratch_bytes(TFG_SPARSE_STATIC_MAX_IDS) > TFG_SPARSE_STATIC_SCRATCH_BYTES)
+    return fail(nullptr, TFG_ESTATE, "built-in scratch is smaller than the sort needs");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetDevice");
+  if (dev < 0 || dev >= 64) return fail(nullptr, TFG_ELIMIT, "CUDA device ordinal beyond 63");
+  void* scratch = g_static_scratch_addr[dev];
+  if (!scratch) {  // once per device, with that device current
+    e = cudaGetSymbolAddress(&scratch, g_static_scratch);
+    if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetSymbolAddress(g_static_scratch)");
+    g_static_scratch_addr[dev] = scratch;
+  }
+  return tfg_sparse_scatter_sub(table, vocab, dim, n_shards, shard, strategy, ids, n, rows, scale, scratch,
+                                TFG_SPARSE_STATIC_SCRATCH_BYTES, stream);
+}
+
 }  // extern "C"

@@ -21,6 +21,7 @@ PART_MOD, PART_DIV = 0, 1
 DT_F32, DT_I64 = 0, 1
 BUF_PARAMS, BUF_GRADS, BUF_ACCUM, BUF_LOSS, BUF_FLAGS = 0, 1, 2, 3, 4
 MAX_REPLICAS, MAX_GPUS, IPC_HANDLE_BYTES = 64, 16, 64
+SPARSE_STATIC_MAX_IDS, SPARSE_STATIC_SCRATCH_BYTES = 65536, 1081600
 OPT_KINDS = {"sgd": OPT_SGD, "momentum": OPT_MOMENTUM, "nesterov": OPT_NESTEROV}
 MATH_MODES = {"fp32": MATH_FP32, "bf16": MATH_BF16, "tf32": MATH_TF32}
 LAYOUTS = {"logical": LAYOUT_LOGICAL, "balanced": LAYOUT_BALANCED}
@@ -92,6 +93,8 @@ _SIGS = {
     "tfg_sparse_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "tfg_sparse_scatter_sub": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
                                          C.c_int64, _p, C.c_float, _p, C.c_size_t, _p]),
+    "tfg_sparse_scatter_sub_static": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
+                                                C.c_int64, _p, C.c_float, _p]),
     "tfg_model_mnist_cnn": (C.c_int, [_p, C.c_int, C.c_int]),
     "tfg_forward_backward": (C.c_int, [_p, C.c_int, _p, _p]),
     "tfg_logits_get": (C.c_int, [_p, C.c_int, _p, C.c_size_t]),
