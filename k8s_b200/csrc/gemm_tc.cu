@@ -1,10 +1,422 @@
-// Tensor path of the sample model -- placeholder until the tcgen05 GEMM lands.
+// Host side of the tensor path: TMA tensor maps, launches of the tcgen05 GEMM
+// (gemm_tc.cuh), the operand-preparation kernels (casts, transposes, im2col in operand
+// precision) and the model's contractions in math modes bf16 / tf32.
+#include <cuda_bf16.h>
+#include <cudaTypedefs.h>
+
+#include <algorithm>
+
 #include "common.cuh"
+#include "gemm_tc.cuh"
 #include "model_mnist.cuh"
 
 namespace tfg {
-int mnist_tc_build(tfg_job* j) { return fail(j, TFG_ESTATE, "tensor math modes are not built yet"); }
-void mnist_tc_destroy(tfg_job*) {}
-int mnist_tc_forward(tfg_job* j, int) { return fail(j, TFG_ESTATE, "tensor math modes are not built yet"); }
-int mnist_tc_backward(tfg_job* j, int) { return fail(j, TFG_ESTATE, "tensor math modes are not built yet"); }
+
+// ---- tensor maps ---------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled get_encode() {
+  static PFN_cuTensorMapEncodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &st) == cudaSuccess &&
+        st == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+  }
+  return fn;
+}
+
+// rows x cols (K) matrix, K contiguous, leading dimension ld elements; box = 128 B of K x box_rows
+static int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t cols, int64_t ld,
+                    int box_rows) {
+  PFN_cuTensorMapEncodeTiled enc = get_encode();
+  if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  const int esize = kind == TFG_MATH_BF16 ? 2 : 4;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || ((ld * esize) & 15) != 0)
+    return fail(nullptr, TFG_EINVAL, "tensor-path operand must be 16-byte aligned with a 16-byte row pitch");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)(ld * esize)};
+  cuuint32_t box[2] = {(cuuint32_t)(tc::kBlockKBytes / esize), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, kind == TFG_MATH_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                   2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+  return TFG_OK;
+}
+
+struct TcGemm {
+  CUtensorMap a, b;
+  float* C = nullptr;          // [M, ldc]
+  float* partial = nullptr;    // [splits][M][N] when splits > 1
+  int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
+  tc::Epilogue epi = {nullptr, nullptr, 0};
+  const char* name = "gemm";
+};
+
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, long long mn) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= mn) return;
+  float s = 0.f;
+  for (int z = 0; z < splits; ++z) s += partial[z * mn + i];   // fixed order: deterministic
+  out[i] = s;
+}
+
+template <int BN, int KIND>
+static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                               tc::Epilogue epi, cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes<BN>();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::gemm_tn_kernel<BN, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  dim3 grid((g.N + BN - 1) / BN, (g.M + tc::kBlockM - 1) / tc::kBlockM, splits);
+  tc::gemm_tn_kernel<BN, KIND><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, dst, g.M, g.N, ldc, k_blocks, kps, epi);
+  return cudaGetLastError();
+}
+
+// j may be NULL (stateless test entry point)
+static int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
+  const int block_k = tc::kBlockKBytes / (kind == TFG_MATH_BF16 ? 2 : 4);
+  const int k_blocks = (g.K + block_k - 1) / block_k;
+  int splits = std::max(1, std::min(g.splits, k_blocks));
+  const int kps = (k_blocks + splits - 1) / splits;
+  splits = (k_blocks + kps - 1) / kps;                 // no empty split
+  float* dst = splits > 1 ? g.partial : g.C;
+  const int ldc = splits > 1 ? g.N : g.ldc;
+  tc::Epilogue epi = splits > 1 ? tc::Epilogue{nullptr, nullptr, 0} : g.epi;
+  if (splits > 1 && (!g.partial || g.ldc != g.N))
+    return fail(j, TFG_EINVAL, "split-K needs a partial buffer and a dense output");
+  cudaError_t e;
+  if (kind == TFG_MATH_BF16)
+    e = g.block_n == 64 ? launch_inst<64, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s)
+                        : launch_inst<128, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  else
+    e = g.block_n == 64 ? launch_inst<64, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s)
+                        : launch_inst<128, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (j) prof_mark(j, g.name);
+  if (e != cudaSuccess) return fail_cuda(j, e, g.name);
+  if (splits > 1) {
+    const long long mn = (long long)g.M * g.N;
+    splitk_reduce_kernel<<<(int)((mn + 255) / 256), 256, 0, s>>>(g.partial, g.C, splits, mn);
+    if (j) prof_mark(j, "split-K reduce");
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail_cuda(j, e, "splitk_reduce_kernel");
+  }
+  return TFG_OK;
+}
+
+// ---- operand preparation ---------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ src, T* __restrict__ dst, long long n4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x)
+    store4(dst + 4 * i, *reinterpret_cast<const float4*>(src + 4 * i));
+}
+
+// src [R, C] (row pitch C) -> dst [C, ldt], 32x32 tiles through shared memory
+template <typename Tin, typename T>
+__global__ void __launch_bounds__(256)
+transpose_kernel(const Tin* __restrict__ src, T* __restrict__ dst, int R, int C, long long ldt) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = r0 + ty + 8 * i, c = c0 + tx;
+    tile[ty + 8 * i][tx] = (r < R && c < C) ? to_f32<Tin>(src[(long long)r * C + c]) : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + 8 * i, r = r0 + tx;
+    if (c < C && r < R) dst[(long long)c * ldt + r] = cvt<T>(tile[tx][ty + 8 * i]);
+  }
+}
+
+// row-major im2col of a1[B,14,14,32] in operand precision: col[m, (kh*5+kw)*32 + c]
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
+  const long long total = (long long)B * 196 * 25 * 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i & 7);
+    const int kk = (int)((i >> 3) % 25);
+    const long long m = (i >> 3) / 25;
+    const int ow = (int)(m % 14), oh = (int)((m / 14) % 14);
+    const long long b = m / 196;
+    const int ih = oh + kk / 5 - 2, iw = ow + kk % 5 - 2;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ih >= 0 && ih < 14 && iw >= 0 && iw < 14)
+      v = *reinterpret_cast<const float4*>(a1 + ((b * 14 + ih) * 14 + iw) * 32 + c4 * 4);
+    store4(col + m * 800 + kk * 32 + c4 * 4, v);
+  }
+}
+
+// transposed im2col: col_t[(kh*5+kw)*32 + c, m] with row pitch ldm; one block = 32 rows m x one tap
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_t_kernel(const float* __restrict__ a1, T* __restrict__ col_t, int B, long long ldm) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const long long M = (long long)B * 196;
+  const long long m0 = (long long)blockIdx.x * 32;
+  const int kk = blockIdx.y;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long m = m0 + ty + 8 * i;
+    float v = 0.f;
+    if (m < M) {
+      const int ow = (int)(m % 14), oh = (int)((m / 14) % 14);
+      const long long b = m / 196;
+      const int ih = oh + kk / 5 - 2, iw = ow + kk % 5 - 2;
+      if (ih >= 0 && ih < 14 && iw >= 0 && iw < 14) v = a1[((b * 14 + ih) * 14 + iw) * 32 + tx];
+    }
+    tile[ty + 8 * i][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = ty + 8 * i;
+    const long long m = m0 + tx;
+    if (m < M) col_t[(long long)(kk * 32 + c) * ldm + m] = cvt<T>(tile[tx][c]);
+  }
+}
+
+// dense un-pooled gradient in operand precision: gy[m, c] = argmax position ? masked grad : 0
+template <typename T>
+__global__ void __launch_bounds__(256)
+unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, const uint8_t* __restrict__ idx,
+                 T* __restrict__ gy, int B, int HO, int C) {
+  const long long total = (long long)B * HO * HO * C;
+  const int HI = HO * 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int pw = (int)((i / C) % HO), ph = (int)((i / C / HO) % HO);
+    const long long b = i / C / HO / HO;
+    const float g = a[i] > 0.f ? gp[i] : 0.f;
+    const int arg = idx[i];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const long long m = (b * HI + 2 * ph + dy) * HI + 2 * pw + dx;
+        gy[m * C + c] = cvt<T>((dy * 2 + dx == arg) ? g : 0.f);
+      }
+  }
+}
+
+
+// ---- model state of the tensor path --------------------------------------------------------
+struct TcShared {          // per job: operand-precision copies of the weights
+  void* w2_lp = nullptr;   // [800, 64]    (B operand of conv2 dgrad: N = 800, K = 64)
+  void* w2_t = nullptr;    // [64, 800]    (B operand of conv2 fwd:   N = 64,  K = 800)
+  void* w3_lp = nullptr;   // [3136, 1024] (B operand of fc1 dgrad)
+  void* w3_t = nullptr;    // [1024, 3136] (B operand of fc1 fwd)
+};
+
+struct TcSlot {            // per replica slot: operand copies of activations + GEMM descriptors
+  void *col_lp = nullptr, *col_t = nullptr, *a2_lp = nullptr, *a2_t = nullptr;
+  void *dh1_lp = nullptr, *dh1_t = nullptr, *dy2_lp = nullptr, *dy2_t = nullptr;
+  float* partial = nullptr;
+  long long ld_b = 0, ld_m2 = 0;
+  TcGemm conv2_fwd, fc1_fwd, fc1_wgrad, fc1_dgrad, conv2_wgrad, conv2_dgrad;
+};
+
+constexpr int kSplitW2Tc = 21;   // 7 M-tiles x 21 K-splits = 147 CTAs on 148 SMs
+
+static inline int blocks_for(long long n, int per = 256) {
+  long long b = (n + per - 1) / per;
+  if (b > kNumSMs * 16) b = kNumSMs * 16;
+  return (int)std::max<long long>(b, 1);
+}
+
+#define TC_LAUNCH_OK(j, what)                                     \
+  do {                                                            \
+    prof_mark((j), what);                                         \
+    cudaError_t e__ = cudaGetLastError();                         \
+    if (e__ != cudaSuccess) return fail_cuda((j), e__, what);     \
+  } while (0)
+
+void mnist_tc_destroy(tfg_job* j) {
+  MnistModel* m = j->model;
+  if (!m) return;
+  if (m->tc) {
+    TcShared* sh = static_cast<TcShared*>(m->tc);
+    cudaFree(sh->w2_lp); cudaFree(sh->w2_t); cudaFree(sh->w3_lp); cudaFree(sh->w3_t);
+    delete sh;
+    m->tc = nullptr;
+  }
+  for (auto& sl : m->slots) {
+    if (!sl.tc) continue;
+    TcSlot* t = static_cast<TcSlot*>(sl.tc);
+    void* ps[] = {t->col_lp, t->col_t, t->a2_lp, t->a2_t, t->dh1_lp, t->dh1_t, t->dy2_lp, t->dy2_t, t->partial};
+    for (void* p : ps) cudaFree(p);
+    delete t;
+    sl.tc = nullptr;
+  }
+}
+
+// Allocations only; tensor maps need the flat parameter/gradient buffers, which exist after
+// tfg_vars_finalize, so they are encoded lazily on the first forward (mnist_tc_prepare).
+int mnist_tc_build(tfg_job* j) {
+  MnistModel* m = j->model;
+  const size_t es = m->math == TFG_MATH_BF16 ? 2 : 4;
+  const long long B = m->B, M2 = B * 196;
+  TcShared* sh = new TcShared();
+  m->tc = sh;
+  cudaError_t e = cudaSuccess;
+  auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16); };
+  alloc(&sh->w2_lp, 800 * 64 * es);
+  alloc(&sh->w2_t, 64 * 800 * es);
+  alloc(&sh->w3_lp, (size_t)3136 * 1024 * es);
+  alloc(&sh->w3_t, (size_t)1024 * 3136 * es);
+  for (auto& sl : m->slots) {
+    TcSlot* t = new TcSlot();
+    sl.tc = t;
+    t->ld_b = (B + 7) / 8 * 8;
+    t->ld_m2 = (M2 + 7) / 8 * 8;
+    alloc(&t->col_lp, (size_t)M2 * 800 * es);
+    alloc(&t->col_t, (size_t)800 * t->ld_m2 * es);
+    alloc(&t->a2_lp, (size_t)B * 3136 * es);
+    alloc(&t->a2_t, (size_t)3136 * t->ld_b * es);
+    alloc(&t->dh1_lp, (size_t)B * 1024 * es);
+    alloc(&t->dh1_t, (size_t)1024 * t->ld_b * es);
+    alloc(&t->dy2_lp, (size_t)M2 * 64 * es);
+    alloc(&t->dy2_t, (size_t)64 * t->ld_m2 * es);
+    alloc((void**)&t->partial, sizeof(float) * kSplitW2Tc * 800 * 64);
+  }
+  if (e != cudaSuccess) return fail_cuda(j, e, "cudaMalloc(tensor-path operands)");
+  return TFG_OK;
+}
+
+static int mnist_tc_prepare(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  MnistSlot& s = m->slots[slot];
+  TcSlot* t = static_cast<TcSlot*>(s.tc);
+  TcShared* sh = static_cast<TcShared*>(m->tc);
+  if (t->conv2_fwd.C) return TFG_OK;
+  const int kind = m->math;
+  const int B = m->B, M2 = B * 196;
+  const float* P = j->params;
+  float* G = j->grads[slot];
+  auto par = [&](int v) { return P + j->vars[m->var[v]].offset; };
+  auto grd = [&](int v) { return G + j->vars[m->var[v]].offset; };
+  int rc;
+  auto mk = [&](TcGemm& g, const char* name, const void* A, long long a_rows, long long lda, const void* Bp,
+                long long b_rows, long long ldb, int K, float* C, int block_n, int splits,
+                tc::Epilogue epi) -> int {
+    g.name = name; g.M = (int)a_rows; g.N = (int)b_rows; g.K = K; g.C = C; g.ldc = (int)b_rows;
+    g.block_n = block_n; g.splits = splits; g.epi = epi; g.partial = t->partial;
+    if ((rc = make_map(&g.a, kind, A, a_rows, K, lda, tc::kBlockM))) return rc;
+    return make_map(&g.b, kind, Bp, b_rows, K, ldb, block_n);
+  };
+  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", t->col_lp, M2, 800, sh->w2_t, 64, 800, 800, s.y2, 64, 1,
+               tc::Epilogue{par(3), nullptr, 0}))) return rc;
+  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", t->a2_lp, B, 3136, sh->w3_t, 1024, 3136, 3136, s.h1, 64, 1,
+               tc::Epilogue{par(5), nullptr, 1}))) return rc;
+  if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", t->a2_t, 3136, t->ld_b, t->dh1_t, 1024, t->ld_b, B, grd(4), 128, 1,
+               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", t->dh1_lp, B, 1024, sh->w3_lp, 3136, 1024, 1024, s.da2, 64, 1,
+               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", t->col_t, 800, t->ld_m2, t->dy2_t, 64, t->ld_m2, M2, grd(2), 64,
+               kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", t->dy2_lp, M2, 64, sh->w2_lp, 800, 64, 64, s.dcol, 128, 1,
+               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  return TFG_OK;
+}
+
+template <typename T>
+static int tc_forward_t(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  MnistSlot& s = m->slots[slot];
+  TcSlot* t = static_cast<TcSlot*>(s.tc);
+  TcShared* sh = static_cast<TcShared*>(m->tc);
+  cudaStream_t st = j->stream;
+  const int B = m->B, M2 = B * 196;
+  const float* W2 = j->params + j->vars[m->var[2]].offset;
+  const float* W3 = j->params + j->vars[m->var[4]].offset;
+  int rc = mnist_tc_prepare(j, slot);
+  if (rc) return rc;
+  // weights in operand precision (they change every step)
+  cast_kernel<T><<<blocks_for(800 * 64 / 4), 256, 0, st>>>(W2, (T*)sh->w2_lp, 800 * 64 / 4);
+  TC_LAUNCH_OK(j, "cast W2");
+  transpose_kernel<float, T><<<dim3(2, 25), 256, 0, st>>>(W2, (T*)sh->w2_t, 800, 64, 800);
+  TC_LAUNCH_OK(j, "transpose W2");
+  cast_kernel<T><<<blocks_for(3136 * 1024 / 4), 256, 0, st>>>(W3, (T*)sh->w3_lp, 3136 * 1024 / 4);
+  TC_LAUNCH_OK(j, "cast W3");
+  transpose_kernel<float, T><<<dim3(32, 98), 256, 0, st>>>(W3, (T*)sh->w3_t, 3136, 1024, 3136);
+  TC_LAUNCH_OK(j, "transpose W3");
+  // conv2 as im2col GEMM
+  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 200), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
+  TC_LAUNCH_OK(j, "im2col_lp_kernel");
+  im2col_t_kernel<T><<<dim3((M2 + 31) / 32, 25), 256, 0, st>>>(s.a1, (T*)t->col_t, B, t->ld_m2);
+  TC_LAUNCH_OK(j, "im2col_t_kernel");
+  if ((rc = launch_tc(j, t->conv2_fwd, m->math, st))) return rc;
+  if ((rc = mnist_pool2(j, slot))) return rc;
+  cast_kernel<T><<<blocks_for((long long)B * 3136 / 4), 256, 0, st>>>(s.a2, (T*)t->a2_lp, (long long)B * 3136 / 4);
+  TC_LAUNCH_OK(j, "cast a2");
+  transpose_kernel<float, T><<<dim3(98, (B + 31) / 32), 256, 0, st>>>(s.a2, (T*)t->a2_t, B, 3136, t->ld_b);
+  TC_LAUNCH_OK(j, "transpose a2");
+  return launch_tc(j, t->fc1_fwd, m->math, st);
+}
+
+template <typename T>
+static int tc_backward_t(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  MnistSlot& s = m->slots[slot];
+  TcSlot* t = static_cast<TcSlot*>(s.tc);
+  cudaStream_t st = j->stream;
+  const int B = m->B, M2 = B * 196;
+  int rc;
+  cast_kernel<T><<<blocks_for((long long)B * 1024 / 4), 256, 0, st>>>(s.dh1, (T*)t->dh1_lp, (long long)B * 1024 / 4);
+  TC_LAUNCH_OK(j, "cast dh1");
+  transpose_kernel<float, T><<<dim3(32, (B + 31) / 32), 256, 0, st>>>(s.dh1, (T*)t->dh1_t, B, 1024, t->ld_b);
+  TC_LAUNCH_OK(j, "transpose dh1");
+  if ((rc = launch_tc(j, t->fc1_wgrad, m->math, st))) return rc;
+  if ((rc = launch_tc(j, t->fc1_dgrad, m->math, st))) return rc;
+  unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, B, 7, 64);
+  TC_LAUNCH_OK(j, "unpool_lp_kernel");
+  transpose_kernel<T, T><<<dim3(2, (M2 + 31) / 32), 256, 0, st>>>((const T*)t->dy2_lp, (T*)t->dy2_t, M2, 64, t->ld_m2);
+  TC_LAUNCH_OK(j, "transpose dy2");
+  if ((rc = launch_tc(j, t->conv2_wgrad, m->math, st))) return rc;
+  return launch_tc(j, t->conv2_dgrad, m->math, st);
+}
+
+int mnist_tc_forward(tfg_job* j, int slot) {
+  return j->model->math == TFG_MATH_BF16 ? tc_forward_t<__nv_bfloat16>(j, slot) : tc_forward_t<float>(j, slot);
+}
+int mnist_tc_backward(tfg_job* j, int slot) {
+  return j->model->math == TFG_MATH_BF16 ? tc_backward_t<__nv_bfloat16>(j, slot) : tc_backward_t<float>(j, slot);
+}
+
 }  // namespace tfg
+
+// ---- stateless GEMM entry point (parity tests of the tensor kernel alone) --------------------
+extern "C" int tfg_gemm_tn(int math, const void* a_dev, const void* b_dev, float* c_dev, int M, int N, int K,
+                           int64_t lda, int64_t ldb, int block_n, int splits, float* partial_dev,
+                           const float* bias_dev, int relu, void* stream) {
+  using namespace tfg;
+  if (math != TFG_MATH_BF16 && math != TFG_MATH_TF32) return fail(nullptr, TFG_EINVAL, "math must be bf16 or tf32");
+  if (!a_dev || !b_dev || !c_dev || M < 1 || N < 1 || K < 1) return fail(nullptr, TFG_EINVAL, "bad argument");
+  if (block_n != 64 && block_n != 128) return fail(nullptr, TFG_EINVAL, "block_n must be 64 or 128");
+  TcGemm g;
+  g.name = "tc gemm";
+  g.M = M; g.N = N; g.K = K; g.C = c_dev; g.ldc = N; g.block_n = block_n; g.splits = splits < 1 ? 1 : splits;
+  g.partial = partial_dev;
+  g.epi = tc::Epilogue{bias_dev, nullptr, relu};
+  int rc = make_map(&g.a, math, a_dev, M, K, lda, tc::kBlockM);
+  if (rc) return rc;
+  if ((rc = make_map(&g.b, math, b_dev, N, K, ldb, block_n))) return rc;
+  return launch_tc(nullptr, g, math, (cudaStream_t)stream);
+}

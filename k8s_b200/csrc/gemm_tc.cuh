@@ -1,0 +1,268 @@
+// tcgen05 GEMM for sm_100a:  C[M,N] (fp32) = A[M,K] * B[N,K]^T, both operands K-major
+// ("TN"), bf16 (kind::f16) or tf32 (kind::tf32) operands, fp32 accumulation in TMEM.
+//
+//   * operands reach shared memory by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle,
+//     out-of-bounds rows/columns zero-filled, so M, N and K need no padding);
+//   * one elected thread issues tcgen05.mma (M = 128, N = BLOCK_N, 32 bytes of K per
+//     instruction) over a 4-stage mbarrier ring; tcgen05.commit frees each stage;
+//   * the accumulator (128 lanes x BLOCK_N columns) is read back with tcgen05.ld by four
+//     epilogue warps (one TMEM lane quarter each), which apply bias / relu / mask and store.
+//   * gridDim.z > 1 = split-K: split z handles a contiguous range of K blocks and writes
+//     its partial product to C + z*M*ldc... (dense [z][M][N]); a fixed-order reduce follows.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue (warp w owns TMEM lanes 32*(w%4) .. +31).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tfg {
+namespace tc {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockKBytes = 128;      // one 128-B swizzle row of K per stage row
+constexpr int kStages = 4;
+constexpr int kThreads = 192;
+constexpr long long kWaitLimitCycles = 4000000000ll;   // ~2 s: a wait that long is a bug -> trap, never hang
+
+struct Epilogue {
+  const float* bias;    // [N] added to every row, or NULL
+  const float* mask;    // [M, ldc]: keep the value where mask > 0, else 0; or NULL
+  int relu;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+               :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    if (done) return;
+    if ((spin & 1023u) == 1023u) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > kWaitLimitCycles) __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// Shared-memory matrix descriptor, K-major, 128-byte swizzle: rows are 128 B apart inside an
+// 8-row atom, atoms 1024 B apart (stride byte offset); version 1 (Blackwell); layout type 2.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);        // start address   [0,14)
+  d |= static_cast<uint64_t>(1) << 16;                            // leading byte offset (unused) [16,30)
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;                    // stride byte offset [32,46)
+  d |= static_cast<uint64_t>(1) << 46;                            // descriptor version [46,48)
+  d |= static_cast<uint64_t>(2) << 61;                            // SWIZZLE_128B       [61,64)
+  return d;
+}
+
+// Instruction descriptor: D = F32, A/B format `fmt` (1 = BF16, 2 = TF32), both K-major,
+// N >> 3 at bit 17, M >> 4 at bit 24.
+__host__ __device__ constexpr uint32_t make_idesc(int fmt, int n) {
+  return (1u << 4) | (static_cast<uint32_t>(fmt) << 7) | (static_cast<uint32_t>(fmt) << 10) |
+         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(kBlockM >> 4) << 24);
+}
+
+template <int KIND>  // 0 = bf16 (kind::f16), 1 = tf32
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                     uint32_t accumulate) {
+  if (KIND == 0) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               :: "r"(smem_u32(bar)) : "memory");
+}
+
+template <int BLOCK_N>
+constexpr size_t smem_bytes() {
+  return 1024 /*alignment slack*/ + static_cast<size_t>(kStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
+         (2 * kStages + 1) * sizeof(uint64_t) + 16;
+}
+
+template <int BLOCK_N, int KIND>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
+               Epilogue epi) {
+  constexpr int kElemBytes = KIND == 0 ? 2 : 4;
+  constexpr int kBlockK = kBlockKBytes / kElemBytes;           // elements of K per stage
+  constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
+  static_assert(BLOCK_N == 64 || BLOCK_N == 128, "TMEM columns must be a power of two >= 32");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kABytes + kBBytes));
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * kBlockM, n0 = blockIdx.x * BLOCK_N;
+  const int kb_begin = blockIdx.z * k_blocks_per_split;
+  const int kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
+  const int n_kb = max(kb_end - kb_begin, 0);
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      mbar_init(tmem_full, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(smem_u32(tmem_slot)), "n"(BLOCK_N) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int i = 0; i < n_kb; ++i) {
+        const int s = i % kStages;
+        const uint32_t phase = (i / kStages) & 1;
+        mbar_wait(&empty[s], phase ^ 1);
+        mbar_expect_tx(&full[s], kABytes + kBBytes);
+        const int k_elem = (kb_begin + i) * kBlockK;
+        tma_load_2d(smem_a + s * kABytes, &map_a, &full[s], k_elem, m0);
+        tma_load_2d(smem_b + s * kBBytes, &map_b, &full[s], k_elem, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N);
+      for (int i = 0; i < n_kb; ++i) {
+        const int s = i % kStages;
+        const uint32_t phase = (i / kStages) & 1;
+        mbar_wait(&full[s], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes));
+        const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes));
+#pragma unroll
+        for (int k = 0; k < kBlockKBytes / 32; ++k)   // 32 bytes of K per instruction
+          umma<KIND>(tmem_base, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+        umma_commit(&empty[s]);                        // frees the stage when these MMAs retire
+      }
+      umma_commit(tmem_full);                          // accumulator complete
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> global =====
+    const int q = warp & 3;                            // TMEM lane quarter this warp may touch
+    const int row = m0 + q * 32 + lane;
+    if (n_kb > 0) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    float* crow = C + (static_cast<size_t>(blockIdx.z) * M + row) * static_cast<size_t>(ldc);
+    // 128-bit stores need 16-B aligned rows (C, bias and mask come from cudaMalloc / 128-B
+    // aligned variable offsets; the leading dimension decides the rest)
+    const bool vec_ok = (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                        (!epi.bias || (reinterpret_cast<uintptr_t>(epi.bias) & 15) == 0) &&
+                        (!epi.mask || (reinterpret_cast<uintptr_t>(epi.mask) & 15) == 0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
+      uint32_t r[16];
+      if (n_kb > 0) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+            : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      } else {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) r[u] = 0u;
+      }
+      if (row < M && vec_ok && n0 + c0 + 16 <= N) {
+#pragma unroll
+        for (int u = 0; u < 16; u += 4) {
+          const int col = n0 + c0 + u;
+          float4 v = make_float4(__uint_as_float(r[u]), __uint_as_float(r[u + 1]), __uint_as_float(r[u + 2]),
+                                 __uint_as_float(r[u + 3]));
+          if (epi.bias) {
+            const float4 b = *reinterpret_cast<const float4*>(epi.bias + col);
+            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+          }
+          if (epi.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          if (epi.mask) {
+            const float4 k = *reinterpret_cast<const float4*>(epi.mask + static_cast<size_t>(row) * ldc + col);
+            v.x = k.x > 0.f ? v.x : 0.f; v.y = k.y > 0.f ? v.y : 0.f;
+            v.z = k.z > 0.f ? v.z : 0.f; v.w = k.w > 0.f ? v.w : 0.f;
+          }
+          *reinterpret_cast<float4*>(crow + col) = v;
+        }
+      } else if (row < M) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+          const int col = n0 + c0 + u;
+          if (col < N) {
+            float v = __uint_as_float(r[u]);
+            if (epi.bias) v += epi.bias[col];
+            if (epi.relu) v = fmaxf(v, 0.f);
+            if (epi.mask) v = epi.mask[static_cast<size_t>(row) * ldc + col] > 0.f ? v : 0.f;
+            crow[col] = v;
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(BLOCK_N) : "memory");
+  }
+}
+
+}  // namespace tc
+}  // namespace tfg

@@ -503,6 +503,14 @@ int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes) {
   return TFG_OK;
 }
 
+int mnist_pool2(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  MnistSlot& s = m->slots[slot];
+  pool_relu_kernel<<<blocks_for((long long)m->B * 3136), 256, 0, j->stream>>>(s.y2, s.a2, s.idx2, m->B, 7, 64);
+  LAUNCH_OK(j, "pool_relu_kernel");
+  return TFG_OK;
+}
+
 int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* labels) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
@@ -527,8 +535,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     // y2[M2,64] = col[M2,800] * W2[800,64] + b2
     if ((rc = sgemm(j, "gemm conv2 fwd", s.col, true, 800, 1, par(2), true, 64, 1, s.y2, M2, 64, 800,
                     GemmEpi{par(3), nullptr, 0}, 1, nullptr))) return rc;
-    pool_relu_kernel<<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.y2, s.a2, s.idx2, B, 7, 64);
-    LAUNCH_OK(j, "pool_relu_kernel");
+    if ((rc = mnist_pool2(j, slot))) return rc;
     // h1[B,1024] = relu(a2[B,3136] * W3[3136,1024] + b3)
     if ((rc = sgemm(j, "gemm fc1 fwd", s.a2, true, 3136, 1, par(4), true, 1024, 1, s.h1, B, 1024, 3136,
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;

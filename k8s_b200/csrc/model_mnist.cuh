@@ -57,6 +57,9 @@ struct MnistModel {
   void* tc = nullptr;            // tensor-path shared state (weight copies, tensor maps)
 };
 
+// model_mnist.cu: y2 -> a2, idx2 (shared by both math paths)
+int mnist_pool2(tfg_job* j, int slot);
+
 // gemm_tc.cu
 int mnist_tc_build(tfg_job* j);
 void mnist_tc_destroy(tfg_job* j);
