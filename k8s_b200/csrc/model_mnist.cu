@@ -359,6 +359,136 @@ __global__ void __launch_bounds__(256) loss_mean_kernel(const float* __restrict_
   if (threadIdx.x == 0) *out = part[0] / (float)B;
 }
 
+
+// ===== classifier head, forward: logits = h1 * W4 + b4, softmax cross-entropy, dlogits ======
+// One warp per example.  Lanes stride K = 1024; the 10 partial sums per lane are combined by
+// xor-shuffles (fixed order), after which every lane holds all 10 logits.
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, const float* __restrict__ b4,
+                const int32_t* __restrict__ labels, float* __restrict__ logits, float* __restrict__ dlogits,
+                float* __restrict__ loss_vec, int B) {
+  const int lane = threadIdx.x & 31;
+  const int ex = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (ex >= B) return;
+  float acc[10];
+#pragma unroll
+  for (int n = 0; n < 10; ++n) acc[n] = 0.f;
+  const float* h = h1 + (size_t)ex * 1024;
+#pragma unroll 4
+  for (int k = lane; k < 1024; k += 32) {
+    const float hv = h[k];
+    const float2* w = reinterpret_cast<const float2*>(w4 + k * 10);   // rows are 40 B: 8-B aligned
+#pragma unroll
+    for (int n2 = 0; n2 < 5; ++n2) {
+      const float2 wv = w[n2];
+      acc[2 * n2] = fmaf(hv, wv.x, acc[2 * n2]);
+      acc[2 * n2 + 1] = fmaf(hv, wv.y, acc[2 * n2 + 1]);
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < 10; ++n) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
+    acc[n] += b4[n];
+  }
+  float mx = acc[0];
+#pragma unroll
+  for (int n = 1; n < 10; ++n) mx = fmaxf(mx, acc[n]);
+  float e[10], sum = 0.f;
+#pragma unroll
+  for (int n = 0; n < 10; ++n) { e[n] = expf(acc[n] - mx); sum += e[n]; }
+  const int lab = labels[ex];
+  float zl = 0.f;
+#pragma unroll
+  for (int n = 0; n < 10; ++n) zl = (n == lab) ? acc[n] : zl;
+#pragma unroll
+  for (int n = 0; n < 10; ++n)
+    if (lane == n) {
+      logits[ex * 10 + n] = acc[n];
+      dlogits[ex * 10 + n] = (e[n] / sum - (n == lab ? 1.f : 0.f)) / (float)B;
+    }
+  if (lane == 0) loss_vec[ex] = logf(sum) - (zl - mx);
+}
+
+// ===== classifier head, backward, one thread per hidden unit k ==============================
+//   dW4[k,:] = sum_b h1[b,k] * dlogits[b,:]        dh1[b,k] = (h1[b,k] > 0) * sum_n dlogits[b,n] W4[k,n]
+//   db3[k]   = sum_b dh1[b,k]                      db4[n]   = sum_b dlogits[b,n]   (last block)
+// Sequential over b in every thread: deterministic, no atomics.
+__global__ void __launch_bounds__(128)
+fc2_bwd_kernel(const float* __restrict__ h1, const float* __restrict__ dlogits, const float* __restrict__ w4,
+               float* __restrict__ dw4, float* __restrict__ db4, float* __restrict__ dh1,
+               float* __restrict__ db3, int B) {
+  __shared__ float dl[64][10];
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool tail_block = blockIdx.x == gridDim.x - 1;     // the extra block computes db4
+  float w[10], dw[10];
+  float bsum = 0.f, db4acc = 0.f;
+#pragma unroll
+  for (int n = 0; n < 10; ++n) { w[n] = (!tail_block) ? w4[k * 10 + n] : 0.f; dw[n] = 0.f; }
+  for (int b0 = 0; b0 < B; b0 += 64) {
+    const int nb = min(64, B - b0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb * 10; i += blockDim.x) dl[i / 10][i % 10] = dlogits[(size_t)b0 * 10 + i];
+    __syncthreads();
+    if (tail_block) {
+      if (threadIdx.x < 10)
+        for (int b = 0; b < nb; ++b) db4acc += dl[b][threadIdx.x];
+      continue;
+    }
+#pragma unroll 4
+    for (int b = 0; b < nb; ++b) {
+      const float hv = h1[(size_t)(b0 + b) * 1024 + k];
+      float v = 0.f;
+#pragma unroll
+      for (int n = 0; n < 10; ++n) {
+        const float d = dl[b][n];
+        dw[n] = fmaf(hv, d, dw[n]);
+        v = fmaf(d, w[n], v);
+      }
+      v = hv > 0.f ? v : 0.f;
+      dh1[(size_t)(b0 + b) * 1024 + k] = v;
+      bsum += v;
+    }
+  }
+  if (tail_block) {
+    if (threadIdx.x < 10) db4[threadIdx.x] = db4acc;
+    return;
+  }
+#pragma unroll
+  for (int n = 0; n < 10; ++n) dw4[k * 10 + n] = dw[n];
+  db3[k] = bsum;
+}
+
+// ===== masked column sums with enough blocks to fill the chip ==============================
+// in[R,C] (optionally zeroed where mask[r,c] <= 0) -> partial[chunk][C]; block = 64 columns x 4 row lanes
+__global__ void __launch_bounds__(256)
+colsum_wide_kernel(const float* __restrict__ in, const float* __restrict__ mask, float* __restrict__ partial,
+                   int R, int C, int rows_per_chunk) {
+  __shared__ float red[4][64];
+  const int cx = threadIdx.x & 63, ry = threadIdx.x >> 6;
+  const int c = blockIdx.x * 64 + cx;
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(R, r0 + rows_per_chunk);
+  float s = 0.f;
+  if (c < C)
+    for (int r = r0 + ry; r < r1; r += 4) {
+      const float v = in[(size_t)r * C + c];
+      s += (!mask || mask[(size_t)r * C + c] > 0.f) ? v : 0.f;
+    }
+  red[ry][cx] = s;
+  __syncthreads();
+  if (ry == 0 && c < C) partial[(size_t)blockIdx.y * C + c] = ((red[0][cx] + red[1][cx]) + red[2][cx]) + red[3][cx];
+}
+
+// [B][832] per-image conv1 partials -> dW1 (columns 0..799) and db1 (800..831), image order
+__global__ void __launch_bounds__(256)
+conv1_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw1, float* __restrict__ db1, int B) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 832) return;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b) s += partial[(size_t)b * 832 + c];
+  if (c < 800) dw1[c] = s; else db1[c - 800] = s;
+}
+
 // ---------------------------------------------------------------------------------------
 static inline int blocks_for(long long n, int per = 256) {
   long long b = (n + per - 1) / per;
@@ -399,13 +529,14 @@ static int sgemm(tfg_job* j, const char* name, const float* A, bool a_kcontig, l
   return TFG_OK;
 }
 
-static int colsum(tfg_job* j, const float* in, float* out, int R, int C, float* partial) {
-  const int rows_per_chunk = 64;
-  const int chunks = (R + rows_per_chunk - 1) / rows_per_chunk;
+static int colsum(tfg_job* j, const float* in, const float* mask, float* out, int R, int C, float* partial) {
+  const int col_blocks = (C + 63) / 64;
+  int chunks = std::max(1, std::min((R + 15) / 16, 2 * kNumSMs / col_blocks));
+  const int rows_per_chunk = (R + chunks - 1) / chunks;
+  chunks = (R + rows_per_chunk - 1) / rows_per_chunk;
   cudaStream_t s = j->stream;
-  dim3 g1((C + 255) / 256, chunks);
-  colsum_stage1_kernel<<<g1, 256, 0, s>>>(in, partial, R, C, rows_per_chunk);
-  LAUNCH_OK(j, "colsum_stage1_kernel");
+  colsum_wide_kernel<<<dim3(col_blocks, chunks), 256, 0, s>>>(in, mask, partial, R, C, rows_per_chunk);
+  LAUNCH_OK(j, "colsum_wide_kernel");
   colsum_stage2_kernel<<<(C + 255) / 256, 256, 0, s>>>(partial, out, chunks, C, C);
   LAUNCH_OK(j, "colsum_stage2_kernel");
   return TFG_OK;
@@ -540,23 +671,16 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     if ((rc = sgemm(j, "gemm fc1 fwd", s.a2, true, 3136, 1, par(4), true, 1024, 1, s.h1, B, 1024, 3136,
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
   }
-  // logits[B,10] = h1 * W4[1024,10] + b4
-  if ((rc = sgemm(j, "gemm fc2 fwd", s.h1, true, 1024, 1, par(6), true, 10, 1, s.logits, B, 10, 1024,
-                  GemmEpi{par(7), nullptr, 0}, 1, nullptr))) return rc;
-  softmax_xent_kernel<<<(B + 7) / 8, 256, 0, st>>>(s.logits, labels, s.dlogits, s.loss_vec, B);
-  LAUNCH_OK(j, "softmax_xent_kernel");
+  // logits = h1 * W4 + b4, softmax cross-entropy and dlogits in one warp-shuffle kernel
+  head_fwd_kernel<<<(B + 7) / 8, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B);
+  LAUNCH_OK(j, "head_fwd_kernel");
   loss_mean_kernel<<<1, 256, 0, st>>>(s.loss_vec, j->loss + j->local_replicas[slot], B);
   LAUNCH_OK(j, "loss_mean_kernel");
 
   // ---------------- backward ----------------
-  // dW4[1024,10] = h1^T * dlogits ; db4 = colsum(dlogits)
-  if ((rc = sgemm(j, "gemm fc2 wgrad", s.h1, false, 1, 1024, s.dlogits, true, 10, 1, grd(6), 1024, 10, B,
-                  GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
-  if ((rc = colsum(j, s.dlogits, grd(7), B, 10, s.scratch))) return rc;
-  // dh1[B,1024] = dlogits * W4^T, masked by h1 > 0
-  if ((rc = sgemm(j, "gemm fc2 dgrad", s.dlogits, true, 10, 1, par(6), false, 1, 10, s.dh1, B, 1024, 10,
-                  GemmEpi{nullptr, s.h1, 0}, 1, nullptr))) return rc;
-  if ((rc = colsum(j, s.dh1, grd(5), B, 1024, s.scratch))) return rc;
+  // dW4, db4, dh1 (masked by h1 > 0) and db3 in one pass over the batch
+  fc2_bwd_kernel<<<1024 / 128 + 1, 128, 0, st>>>(s.h1, s.dlogits, par(6), grd(6), grd(7), s.dh1, grd(5), B);
+  LAUNCH_OK(j, "fc2_bwd_kernel");
   if (tc) {
     if ((rc = mnist_tc_backward(j, slot))) return rc;  // dW3, da2, dcol, dW2 on the tensor path
   } else {
@@ -577,18 +701,14 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                     GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
   }
   // db2 = sum over pooled positions of the masked pooled gradient
-  relu_mask_kernel<<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.da2m, (long long)B * 3136);
-  LAUNCH_OK(j, "relu_mask_kernel");
-  if ((rc = colsum(j, s.da2m, grd(3), B * 49, 64, s.scratch))) return rc;
+  if ((rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
   col2im_mask_kernel<<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
   LAUNCH_OK(j, "col2im_mask_kernel");
   conv1_bwd_kernel<<<B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  colsum_stage2_kernel<<<(800 + 255) / 256, 256, 0, st>>>(s.scratch, grd(0), B, 800, 832);
-  LAUNCH_OK(j, "conv1 dW reduce");
-  colsum_stage2_kernel<<<1, 256, 0, st>>>(s.scratch + 800, grd(1), B, 32, 832);
-  LAUNCH_OK(j, "conv1 db reduce");
+  conv1_reduce_kernel<<<(832 + 255) / 256, 256, 0, st>>>(s.scratch, grd(0), grd(1), B);
+  LAUNCH_OK(j, "conv1_reduce_kernel");
   return TFG_OK;
 }
 

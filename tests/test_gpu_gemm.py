@@ -61,4 +61,6 @@ def test_gemm_tn_relu_and_argument_checks(lib):
     assert lib.gemm_tn(L.MATH_FP32, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 64, 1, None, None, 0, 0) == 2
     assert lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 96, 1, None, None, 0, 0) == 2
     assert lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 60, 60, 60, 64, 1, None, None, 0, 0) == 2  # 120-B pitch
-    assert lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 64, 2, None, None, 0, 0) == 2  # split-K w/o partial
+    a2 = torch.randn(64, 128).bfloat16().cuda()
+    b2 = torch.randn(32, 128).bfloat16().cuda()
+    assert lib.gemm_tn(L.MATH_BF16, a2.data_ptr(), b2.data_ptr(), c.data_ptr(), 64, 32, 128, 128, 128, 64, 2, None, None, 0, 0) == 2  # split-K w/o partial

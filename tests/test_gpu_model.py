@@ -2,9 +2,20 @@
 the PyTorch-CPU floating-point reference (oracle/model_ref.py).
 
 Tolerances (stated per math mode, SURVEY.md §7 hard part 3):
-  fp32  -- same arithmetic, different summation order: |d| <= 2e-4 * max|ref| + 1e-6
-  bf16  -- 8-bit-mantissa operands, fp32 accumulate: logits/grads 3e-2 * max|ref|, loss 1e-2 rel
-  tf32  -- 10-bit-mantissa operands:                 logits/grads 5e-3 * max|ref|, loss 2e-3 rel
+  fp32  -- same arithmetic as the reference, different summation order:
+           max|d| <= 2e-4 * max|ref| per tensor, loss 1e-5 relative.
+  bf16 / tf32 -- the contractions round their operands (8 / 10 mantissa bits; tcgen05 kind::tf32
+           TRUNCATES the low 13 bits, measured with scripts/probe_tf32.py) and accumulate in
+           fp32.  Element-wise max-norm bounds are meaningless here: a relu sign or a max-pool
+           arg-max that flips on a near-tie changes whole gradient columns, and a ONE-ulp
+           perturbation of the fp32 weights already moves the CPU reference's own gradients
+           by up to 14 % in max-norm (measured).  The bounds are therefore relative L2 norms:
+             * vs the SAME arithmetic on the CPU (oracle/model_ref.py:forward_q rounds the same
+               operands at the same places): ||d|| <= 5e-2 ||ref|| per gradient tensor -- the
+               measured self-sensitivity of that reference under 1-ulp weight noise is <= 2.7e-2;
+             * vs the un-rounded fp32 reference: ||d|| <= 0.20 ||ref|| (bf16), 0.06 (tf32)
+               (the CPU emulation itself sits at 0.12 / 0.03), logits 3e-2 / 5e-3 of max|ref|,
+               loss 1e-2 / 2e-3 relative.
 """
 import json
 
@@ -17,13 +28,22 @@ from oracle import model_ref as M
 pytestmark = pytest.mark.gpu
 torch = pytest.importorskip("torch")
 
-TOL = {"fp32": (2e-4, 1e-5), "bf16": (3e-2, 1e-2), "tf32": (5e-3, 2e-3)}
+TOL = {"fp32": (2e-4, 1e-5), "bf16": (2e-3, 1e-4), "tf32": (2e-3, 1e-4)}      # logits / loss vs same-arithmetic reference
+L2_SAME = {"bf16": 5e-2, "tf32": 5e-2}
+L2_FP32 = {"bf16": 0.20, "tf32": 0.06}
+TOL_FWD_VS_FP32 = {"fp32": (2e-4, 1e-5), "bf16": (3e-2, 1e-2), "tf32": (5e-3, 2e-3)}
 
 
 def close(got, ref, frac, what):
     scale = float(np.abs(ref).max())
     err = float(np.abs(got.reshape(ref.shape) - ref).max())
     assert err <= frac * scale + 1e-6, "%s: max err %.3e vs scale %.3e (allowed %.1e of scale)" % (what, err, scale, frac)
+
+
+def rel_l2(got, ref):
+    ref = np.asarray(ref, dtype=np.float64).ravel()
+    got = np.asarray(got, dtype=np.float64).ravel()
+    return float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30))
 
 
 def tf_config(n_workers=0, n_ps=0):
@@ -53,13 +73,21 @@ def test_forward_backward_matches_reference(math, batch):
     dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
     j.forward_backward(0, dx.data_ptr(), dy.data_ptr())
     j.sync()
-    loss_ref, grads_ref, logits_ref = M.loss_and_grads(mnist_init(0), x, y)
+    loss32, grads32, logits32 = M.loss_and_grads(mnist_init(0), x, y)
+    loss_ref, grads_ref, logits_ref = M.loss_and_grads(mnist_init(0), x, y, math=math)
     frac, loss_rel = TOL[math]
     close(j.logits(0), logits_ref, frac, "logits")
     loss = j.loss(0)
+    close(j.logits(0), logits32, TOL_FWD_VS_FP32[math][0], "logits vs fp32")
+    assert abs(loss - loss32) <= TOL_FWD_VS_FP32[math][1] * abs(loss32) + 1e-6
     assert abs(loss - loss_ref) <= loss_rel * abs(loss_ref) + 1e-6
     for v, name in enumerate(MNIST_VARS):
-        close(j.get_grad(0, v), grads_ref[v], frac, "grad " + name)
+        g = j.get_grad(0, v)
+        if math == "fp32":
+            close(g, grads_ref[v], frac, "grad " + name)
+        else:
+            assert rel_l2(g, grads_ref[v]) <= L2_SAME[math], "grad %s vs same-arithmetic reference: %.3e" % (name, rel_l2(g, grads_ref[v]))
+            assert rel_l2(g, grads32[v]) <= L2_FP32[math], "grad %s vs fp32 reference: %.3e" % (name, rel_l2(g, grads32[v]))
     j.close()
 
 
@@ -79,15 +107,20 @@ def test_tf_job_yaml_two_replicas_two_ps_on_one_gpu(math, kind):
     j.optimizer(kind, 0.001, 0.9)   # 0.01 overshoots on this init: errors would be amplified chaotically
     assert j.local_replicas == [0, 1]
     params = mnist_init(0)
+    init = [p.copy() for p in params]
     accum = [np.zeros_like(p) for p in params]
     frac, loss_rel = TOL[math]
+    upd_tol = 1e-3 if math == "fp32" else L2_SAME[math]
     for step in range(3):
         batches = [synthetic_batch(r, batch, step) for r in range(2)]
         loss = j.step([b[0] for b in batches], [b[1] for b in batches])
-        loss_ref, _ = M.sync_step(params, accum, batches, kind, 0.001, 0.9)
-        assert abs(loss - loss_ref) <= (loss_rel * (step + 1)) * abs(loss_ref) + 1e-6, (step, loss, loss_ref)
-        for v, name in enumerate(MNIST_VARS):
-            close(j.get_var(v), params[v], frac * (step + 1) * 0.05 + 1e-6, "step %d param %s" % (step, name))
+        loss_ref, _ = M.sync_step(params, accum, batches, kind, 0.001, 0.9, math=math)
+        step_loss_rel = loss_rel if math == "fp32" else 5e-3        # later steps start from slightly different parameters
+        assert abs(loss - loss_ref) <= (step_loss_rel * (step + 1)) * abs(loss_ref) + 1e-6, (step, loss, loss_ref)
+        for v, name in enumerate(MNIST_VARS):     # the accumulated update, not the (dominant) initial value
+            got_upd = j.get_var(v) - init[v].ravel()
+            e = rel_l2(got_upd, params[v].ravel() - init[v].ravel())
+            assert e <= upd_tol * (step + 1), "step %d update of %s: rel L2 %.3e" % (step, name, e)
     assert j.global_step == 3
     assert [j.placement(v)["ps_task"] for v in range(8)] == [0, 1, 0, 1, 0, 1, 0, 1]
     j.close()
