@@ -246,20 +246,24 @@ struct BarrierArgs {
   uint32_t* flags[TFG_MAX_GPUS];  // every rank's flag array (own one local, others peer-mapped)
   int* err;
   int me, n;
-  uint32_t epoch;
+  uint32_t* epoch_ctr;   // device-resident: the kernel advances it, so a captured launch replays correctly
 };
 
 __global__ void barrier_kernel(const __grid_constant__ BarrierArgs a) {
   int t = threadIdx.x;
+  __shared__ uint32_t epoch_s;
+  if (t == 0) epoch_s = ++(*a.epoch_ctr);   // every rank runs the same number of barriers
+  __syncthreads();
+  const uint32_t epoch = epoch_s;
   if (t >= a.n || t == a.me) return;
   __threadfence_system();  // my earlier stores (gradients, pulled parameters) before the flag
-  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.flags[t] + a.me), "r"(a.epoch) : "memory");
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.flags[t] + a.me), "r"(epoch) : "memory");
   unsigned long long t0, t1;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (;;) {
     uint32_t seen;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.flags[a.me] + t) : "memory");
-    if ((int32_t)(seen - a.epoch) >= 0) break;
+    if ((int32_t)(seen - epoch) >= 0) break;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
     if (t1 - t0 > 20ull * 1000 * 1000 * 1000) {  // 20 s: a peer rank died; fail, do not hang
       atomicExch(a.err, 1);
@@ -275,7 +279,7 @@ int launch_barrier(tfg_job* j) {
   a.err = j->dev_err;
   a.me = j->gpu_rank;
   a.n = j->n_gpus;
-  a.epoch = ++j->epoch;
+  a.epoch_ctr = j->dev_epoch;
   barrier_kernel<<<1, 32, 0, j->stream>>>(a);
   prof_mark(j, "barrier_kernel");
   cudaError_t e = cudaGetLastError();

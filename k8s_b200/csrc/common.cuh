@@ -71,7 +71,7 @@ struct tfg_job {
   uint32_t* peer_flags[TFG_MAX_GPUS] = {};
   float* peer_grads[TFG_MAX_REPLICAS] = {};
   std::vector<void*> ipc_opened;
-  uint32_t epoch = 0;
+  uint32_t* dev_epoch = nullptr;       // barrier epoch counter, advanced by the barrier kernel itself
   // optimizer
   int opt_kind = TFG_OPT_SGD;
   float lr = 0.01f, mu = 0.9f;
@@ -83,6 +83,15 @@ struct tfg_job {
   bool prof_on = false;
   std::vector<std::pair<const char*, cudaEvent_t>> prof_ev;
   size_t prof_used = 0;
+  // CUDA graphs of the whole step, keyed by the input pointers they were captured with
+  struct StepGraph {
+    std::vector<const void*> key;
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;
+    int calls = 0;
+  };
+  std::vector<StepGraph> step_graphs;
+  bool use_graphs = true;
   std::string err;
 };
 

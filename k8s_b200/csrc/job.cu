@@ -176,6 +176,9 @@ int tfg_job_destroy(tfg_job* j) {
     cudaFree(j->loss);
     cudaFree(j->flags);
     cudaFree(j->dev_err);
+    cudaFree(j->dev_epoch);
+    for (auto& g : j->step_graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
     cudaFree(j->d_segs);
     if (j->h_loss) cudaFreeHost(j->h_loss);
     if (j->h_err) cudaFreeHost(j->h_err);
@@ -203,6 +206,9 @@ int tfg_job_bind(tfg_job* j, int cuda_device, void* stream) {
   TFG_CUDA(j, cudaMemset(j->flags, 0, sizeof(uint32_t) * TFG_MAX_GPUS));
   TFG_CUDA(j, cudaMalloc(&j->dev_err, sizeof(int)));
   TFG_CUDA(j, cudaMemset(j->dev_err, 0, sizeof(int)));
+  TFG_CUDA(j, cudaMalloc(&j->dev_epoch, sizeof(uint32_t)));
+  TFG_CUDA(j, cudaMemset(j->dev_epoch, 0, sizeof(uint32_t)));
+  if (const char* g = getenv("TFGRAFT_GRAPH")) j->use_graphs = atoi(g) != 0;
   TFG_CUDA(j, cudaMallocHost(&j->h_loss, sizeof(float) * (TFG_MAX_REPLICAS + 1)));
   TFG_CUDA(j, cudaMallocHost(&j->h_err, sizeof(int)));
   *j->h_err = 0;
@@ -599,9 +605,64 @@ int tfg_logits_get(tfg_job* j, int slot, float* host, size_t bytes) {
   return mnist_logits(j, slot, host, bytes);
 }
 
-static int step_tail(tfg_job* j, float* loss_out) {
-  int rc = tfg_push_apply_pull(j, 1);
+// Device work of one step: forward/backward of every hosted replica, then barrier, fused
+// push+apply+pull, barrier.  Pure stream work with fixed pointers, hence capturable.
+static int step_device_work(tfg_job* j, const float* const* images, const int32_t* const* labels) {
+  int rc;
+  for (size_t s = 0; s < j->grads.size(); ++s)
+    if ((rc = mnist_forward_backward(j, (int)s, images[s], labels[s]))) return rc;
+  if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
+  if ((rc = launch_job_apply(j, false, j->n_replicas))) return rc;
+  if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
+  return TFG_OK;
+}
+
+// Runs the step eagerly the first time a set of input pointers is seen (this also performs
+// every one-time set-up), captures it into a CUDA graph the second time, replays afterwards:
+// the ~30 launches of a step cost one graph launch.  TFGRAFT_GRAPH=0 or profiling = eager.
+static int step_run(tfg_job* j, const float* const* images, const int32_t* const* labels) {
+  int rc = check_peers(j);
   if (rc) return rc;
+  const size_t ns = j->grads.size();
+  tfg_job::StepGraph* g = nullptr;
+  if (j->use_graphs && !j->prof_on) {
+    std::vector<const void*> key;
+    for (size_t s = 0; s < ns; ++s) { key.push_back(images[s]); key.push_back(labels[s]); }
+    for (auto& e : j->step_graphs)
+      if (e.key == key) g = &e;
+    if (!g && j->step_graphs.size() < 32) {
+      j->step_graphs.emplace_back();
+      g = &j->step_graphs.back();
+      g->key = key;
+    }
+  }
+  if (!g || ++g->calls == 1) {
+    rc = step_device_work(j, images, labels);
+  } else if (!g->exec) {
+    const int64_t l0 = j->launches;
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(j->stream, cudaStreamCaptureModeRelaxed);
+    if (e != cudaSuccess) return fail_cuda(j, e, "cudaStreamBeginCapture");
+    rc = step_device_work(j, images, labels);
+    e = cudaStreamEndCapture(j->stream, &graph);
+    if (rc == TFG_OK && e == cudaSuccess) e = cudaGraphInstantiate(&g->exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    g->launches = j->launches - l0;
+    j->launches = l0;
+    if (rc) return rc;
+    if (e != cudaSuccess) { g->exec = nullptr; j->use_graphs = false; return fail_cuda(j, e, "step graph capture"); }
+    TFG_CUDA(j, cudaGraphLaunch(g->exec, j->stream));
+    j->launches += g->launches;
+  } else {
+    TFG_CUDA(j, cudaGraphLaunch(g->exec, j->stream));
+    j->launches += g->launches;
+  }
+  if (rc) return rc;
+  j->global_step += 1;
+  return TFG_OK;
+}
+
+static int step_finish(tfg_job* j, float* loss_out) {
   if (loss_out) {
     TFG_CUDA(j, cudaMemcpyAsync(j->h_loss, j->loss + TFG_MAX_REPLICAS, sizeof(float),
                                 cudaMemcpyDeviceToHost, j->stream));
@@ -619,12 +680,11 @@ int tfg_step_dense_dev(tfg_job* j, const float* const* images, const int32_t* co
   if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   if (!images || !labels) return fail(j, TFG_EINVAL, "NULL input");
   TFG_CUDA(j, cudaSetDevice(j->device));
-  for (size_t s = 0; s < j->grads.size(); ++s) {
+  for (size_t s = 0; s < j->grads.size(); ++s)
     if (!images[s] || !labels[s]) return fail(j, TFG_EINVAL, "NULL input for a replica slot");
-    int rc = mnist_forward_backward(j, (int)s, images[s], labels[s]);
-    if (rc) return rc;
-  }
-  return step_tail(j, loss_out);
+  int rc = step_run(j, images, labels);
+  if (rc) return rc;
+  return step_finish(j, loss_out);
 }
 
 int tfg_step_dense(tfg_job* j, const float* const* images_host, const int32_t* const* labels_host,
@@ -634,18 +694,20 @@ int tfg_step_dense(tfg_job* j, const float* const* images_host, const int32_t* c
   if (!images_host || !labels_host || !loss_out) return fail(j, TFG_EINVAL, "NULL argument");
   TFG_CUDA(j, cudaSetDevice(j->device));
   const int B = mnist_batch(j);
+  std::vector<const float*> di(j->grads.size());
+  std::vector<const int32_t*> dl(j->grads.size());
   for (size_t s = 0; s < j->grads.size(); ++s) {
     if (!images_host[s] || !labels_host[s]) return fail(j, TFG_EINVAL, "NULL input for a replica slot");
-    float* di = mnist_stage_images(j, (int)s);
-    int32_t* dl = mnist_stage_labels(j, (int)s);
-    TFG_CUDA(j, cudaMemcpyAsync(di, images_host[s], sizeof(float) * 784 * (size_t)B,
+    di[s] = mnist_stage_images(j, (int)s);
+    dl[s] = mnist_stage_labels(j, (int)s);
+    TFG_CUDA(j, cudaMemcpyAsync(const_cast<float*>(di[s]), images_host[s], sizeof(float) * 784 * (size_t)B,
                                 cudaMemcpyHostToDevice, j->stream));
-    TFG_CUDA(j, cudaMemcpyAsync(dl, labels_host[s], sizeof(int32_t) * (size_t)B,
+    TFG_CUDA(j, cudaMemcpyAsync(const_cast<int32_t*>(dl[s]), labels_host[s], sizeof(int32_t) * (size_t)B,
                                 cudaMemcpyHostToDevice, j->stream));
-    int rc = mnist_forward_backward(j, (int)s, di, dl);
-    if (rc) return rc;
   }
-  return step_tail(j, loss_out);
+  int rc = step_run(j, di.data(), dl.data());
+  if (rc) return rc;
+  return step_finish(j, loss_out);
 }
 
 int tfg_loss_get(tfg_job* j, int replica, float* loss_out) {
