@@ -261,14 +261,15 @@ int tfg_job_sync(tfg_job* job);
 int64_t tfg_launch_count(const tfg_job* job);
 
 /* The tensor-path GEMM alone (parity tests, profiling): C[M,N] fp32 (dense, ldc = N) =
- * A[M,K] * B[N,K]^T with both operands K-major in `math` precision (TFG_MATH_BF16: bf16
- * elements, TFG_MATH_TF32: fp32 elements), leading dimensions lda/ldb in elements (row pitch
- * a multiple of 16 bytes), tcgen05 tile 128 x block_n (64 or 128).  splits > 1 = split-K
+ * A(M x K) * B(N x K)^T in `math` precision (TFG_MATH_BF16: bf16 elements, TFG_MATH_TF32:
+ * fp32 elements).  An operand is K-major (stored [rows, K], x_mn_major = 0) or MN-major
+ * (stored [K, rows], x_mn_major = 1); lda/ldb = row pitch of the stored matrix in elements
+ * (a multiple of 16 bytes).  tcgen05 tile 128 x block_n (64 or 128).  splits > 1 = split-K
  * through partial_dev (splits*M*N floats), reduced in a fixed order.  bias_dev[N] / relu are
  * applied when splits == 1.  The contractions of the sample model (A16) are instances of it. */
-int tfg_gemm_tn(int math, const void* a_dev, const void* b_dev, float* c_dev, int M, int N, int K,
-                int64_t lda, int64_t ldb, int block_n, int splits, float* partial_dev,
-                const float* bias_dev, int relu, void* stream);
+int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const void* b_dev, int b_mn_major,
+                float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb, int block_n, int splits,
+                float* partial_dev, const float* bias_dev, int relu, void* stream);
 
 /* per-kernel device time of this job's launches, measured with CUDA events on the job's
  * stream (bench.py's roofline leg).  enable(1) starts a fresh record; report() writes

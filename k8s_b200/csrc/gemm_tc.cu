@@ -25,9 +25,10 @@ static PFN_cuTensorMapEncodeTiled get_encode() {
   return fn;
 }
 
-// rows x cols (K) matrix, K contiguous, leading dimension ld elements; box = 128 B of K x box_rows
+// Operand with `rows` (M or N) and `cols` (K).  K-major: stored [rows, K], pitch ld, box = 128 B
+// of K x box_rows.  MN-major: stored [K, rows], pitch ld, box = 128 B of rows x one stage of K.
 static int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t cols, int64_t ld,
-                    int box_rows) {
+                    int box_rows, bool mn_major = false) {
   PFN_cuTensorMapEncodeTiled enc = get_encode();
   if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
   const int esize = kind == TFG_MATH_BF16 ? 2 : 4;
@@ -36,10 +37,16 @@ static int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, i
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)(ld * esize)};
   cuuint32_t box[2] = {(cuuint32_t)(tc::kBlockKBytes / esize), (cuuint32_t)box_rows};
+  if (mn_major) {
+    dims[0] = (cuuint64_t)rows; dims[1] = (cuuint64_t)cols;
+    box[0] = (cuuint32_t)(128 / esize); box[1] = (cuuint32_t)(tc::kBlockKBytes / esize);
+  }
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, kind == TFG_MATH_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
                    2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   (mn_major && kind == TFG_MATH_TF32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                                       : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
@@ -51,6 +58,7 @@ struct TcGemm {
   float* C = nullptr;          // [M, ldc]
   float* partial = nullptr;    // [splits][M][N] when splits > 1
   int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
+  bool a_mn = false, b_mn = false;
   tc::Epilogue epi = {nullptr, nullptr, 0};
   const char* name = "gemm";
 };
@@ -64,20 +72,30 @@ splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out,
   out[i] = s;
 }
 
-template <int BN, int KIND>
+template <int BN, int KIND, bool A_MN, bool B_MN>
 static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
                                tc::Epilogue epi, cudaStream_t s) {
   static bool attr_set = false;
   constexpr size_t smem = tc::smem_bytes<BN>();
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc::gemm_tn_kernel<BN, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   dim3 grid((g.N + BN - 1) / BN, (g.M + tc::kBlockM - 1) / tc::kBlockM, splits);
-  tc::gemm_tn_kernel<BN, KIND><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, dst, g.M, g.N, ldc, k_blocks, kps, epi);
+  tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, dst, g.M, g.N, ldc, k_blocks,
+                                                                              kps, epi);
   return cudaGetLastError();
+}
+
+template <int BN, int KIND>
+static cudaError_t launch_major(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                                tc::Epilogue epi, cudaStream_t s) {
+  if (!g.a_mn && !g.b_mn) return launch_inst<BN, KIND, false, false>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (!g.a_mn && g.b_mn) return launch_inst<BN, KIND, false, true>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (g.a_mn && g.b_mn) return launch_inst<BN, KIND, true, true>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  return launch_inst<BN, KIND, true, false>(g, dst, ldc, k_blocks, kps, splits, epi, s);
 }
 
 // j may be NULL (stateless test entry point)
@@ -94,11 +112,11 @@ static int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
     return fail(j, TFG_EINVAL, "split-K needs a partial buffer and a dense output");
   cudaError_t e;
   if (kind == TFG_MATH_BF16)
-    e = g.block_n == 64 ? launch_inst<64, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s)
-                        : launch_inst<128, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+    e = g.block_n == 64 ? launch_major<64, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s)
+                        : launch_major<128, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   else
-    e = g.block_n == 64 ? launch_inst<64, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s)
-                        : launch_inst<128, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+    e = g.block_n == 64 ? launch_major<64, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s)
+                        : launch_major<128, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   if (j) prof_mark(j, g.name);
   if (e != cudaSuccess) return fail_cuda(j, e, g.name);
   if (splits > 1) {
@@ -122,26 +140,6 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ src
     store4(dst + 4 * i, *reinterpret_cast<const float4*>(src + 4 * i));
 }
 
-// src [R, C] (row pitch C) -> dst [C, ldt], 32x32 tiles through shared memory
-template <typename Tin, typename T>
-__global__ void __launch_bounds__(256)
-transpose_kernel(const Tin* __restrict__ src, T* __restrict__ dst, int R, int C, long long ldt) {
-  __shared__ float tile[32][33];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int r = r0 + ty + 8 * i, c = c0 + tx;
-    tile[ty + 8 * i][tx] = (r < R && c < C) ? to_f32<Tin>(src[(long long)r * C + c]) : 0.f;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = c0 + ty + 8 * i, r = r0 + tx;
-    if (c < C && r < R) dst[(long long)c * ldt + r] = cvt<T>(tile[tx][ty + 8 * i]);
-  }
-}
-
 // row-major im2col of a1[B,14,14,32] in operand precision: col[m, (kh*5+kw)*32 + c]
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -159,36 +157,6 @@ im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
     if (ih >= 0 && ih < 14 && iw >= 0 && iw < 14)
       v = *reinterpret_cast<const float4*>(a1 + ((b * 14 + ih) * 14 + iw) * 32 + c4 * 4);
     store4(col + m * 800 + kk * 32 + c4 * 4, v);
-  }
-}
-
-// transposed im2col: col_t[(kh*5+kw)*32 + c, m] with row pitch ldm; one block = 32 rows m x one tap
-template <typename T>
-__global__ void __launch_bounds__(256)
-im2col_t_kernel(const float* __restrict__ a1, T* __restrict__ col_t, int B, long long ldm) {
-  __shared__ float tile[32][33];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const long long M = (long long)B * 196;
-  const long long m0 = (long long)blockIdx.x * 32;
-  const int kk = blockIdx.y;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const long long m = m0 + ty + 8 * i;
-    float v = 0.f;
-    if (m < M) {
-      const int ow = (int)(m % 14), oh = (int)((m / 14) % 14);
-      const long long b = m / 196;
-      const int ih = oh + kk / 5 - 2, iw = ow + kk % 5 - 2;
-      if (ih >= 0 && ih < 14 && iw >= 0 && iw < 14) v = a1[((b * 14 + ih) * 14 + iw) * 32 + tx];
-    }
-    tile[ty + 8 * i][tx] = v;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = ty + 8 * i;
-    const long long m = m0 + tx;
-    if (m < M) col_t[(long long)(kk * 32 + c) * ldm + m] = cvt<T>(tile[tx][c]);
   }
 }
 
@@ -218,18 +186,22 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
 
 
 // ---- model state of the tensor path --------------------------------------------------------
+// Operands are the row-major buffers themselves, cast to operand precision; which index is
+// contiguous decides K-major vs MN-major per GEMM, so nothing is ever transposed:
+//   conv2 fwd   y2[M2,64]     = col[M2,800] (K)   x W2[800,64]   (MN)
+//   fc1   fwd   h1[B,1024]    = a2[B,3136]  (K)   x W3[3136,1024] (MN)
+//   fc1   wgrad dW3[3136,1024]= a2[B,3136]  (MN)  x dh1[B,1024]  (MN)      K = B
+//   fc1   dgrad da2[B,3136]   = dh1[B,1024] (K)   x W3[3136,1024] (K)
+//   conv2 wgrad dW2[800,64]   = col[M2,800] (MN)  x dy2[M2,64]   (MN)      K = M2, split-K
+//   conv2 dgrad dcol[M2,800]  = dy2[M2,64]  (K)   x W2[800,64]   (K)
 struct TcShared {          // per job: operand-precision copies of the weights
-  void* w2_lp = nullptr;   // [800, 64]    (B operand of conv2 dgrad: N = 800, K = 64)
-  void* w2_t = nullptr;    // [64, 800]    (B operand of conv2 fwd:   N = 64,  K = 800)
-  void* w3_lp = nullptr;   // [3136, 1024] (B operand of fc1 dgrad)
-  void* w3_t = nullptr;    // [1024, 3136] (B operand of fc1 fwd)
+  void* w2_lp = nullptr;   // [800, 64]
+  void* w3_lp = nullptr;   // [3136, 1024]
 };
 
 struct TcSlot {            // per replica slot: operand copies of activations + GEMM descriptors
-  void *col_lp = nullptr, *col_t = nullptr, *a2_lp = nullptr, *a2_t = nullptr;
-  void *dh1_lp = nullptr, *dh1_t = nullptr, *dy2_lp = nullptr, *dy2_t = nullptr;
+  void *col_lp = nullptr, *a2_lp = nullptr, *dh1_lp = nullptr, *dy2_lp = nullptr;
   float* partial = nullptr;
-  long long ld_b = 0, ld_m2 = 0;
   TcGemm conv2_fwd, fc1_fwd, fc1_wgrad, fc1_dgrad, conv2_wgrad, conv2_dgrad;
 };
 
@@ -253,14 +225,14 @@ void mnist_tc_destroy(tfg_job* j) {
   if (!m) return;
   if (m->tc) {
     TcShared* sh = static_cast<TcShared*>(m->tc);
-    cudaFree(sh->w2_lp); cudaFree(sh->w2_t); cudaFree(sh->w3_lp); cudaFree(sh->w3_t);
+    cudaFree(sh->w2_lp); cudaFree(sh->w3_lp);
     delete sh;
     m->tc = nullptr;
   }
   for (auto& sl : m->slots) {
     if (!sl.tc) continue;
     TcSlot* t = static_cast<TcSlot*>(sl.tc);
-    void* ps[] = {t->col_lp, t->col_t, t->a2_lp, t->a2_t, t->dh1_lp, t->dh1_t, t->dy2_lp, t->dy2_t, t->partial};
+    void* ps[] = {t->col_lp, t->a2_lp, t->dh1_lp, t->dy2_lp, t->partial};
     for (void* p : ps) cudaFree(p);
     delete t;
     sl.tc = nullptr;
@@ -278,22 +250,14 @@ int mnist_tc_build(tfg_job* j) {
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16); };
   alloc(&sh->w2_lp, 800 * 64 * es);
-  alloc(&sh->w2_t, 64 * 800 * es);
   alloc(&sh->w3_lp, (size_t)3136 * 1024 * es);
-  alloc(&sh->w3_t, (size_t)1024 * 3136 * es);
   for (auto& sl : m->slots) {
     TcSlot* t = new TcSlot();
     sl.tc = t;
-    t->ld_b = (B + 7) / 8 * 8;
-    t->ld_m2 = (M2 + 7) / 8 * 8;
     alloc(&t->col_lp, (size_t)M2 * 800 * es);
-    alloc(&t->col_t, (size_t)800 * t->ld_m2 * es);
     alloc(&t->a2_lp, (size_t)B * 3136 * es);
-    alloc(&t->a2_t, (size_t)3136 * t->ld_b * es);
     alloc(&t->dh1_lp, (size_t)B * 1024 * es);
-    alloc(&t->dh1_t, (size_t)1024 * t->ld_b * es);
     alloc(&t->dy2_lp, (size_t)M2 * 64 * es);
-    alloc(&t->dy2_t, (size_t)64 * t->ld_m2 * es);
     alloc((void**)&t->partial, sizeof(float) * kSplitW2Tc * 800 * 64);
   }
   if (e != cudaSuccess) return fail_cuda(j, e, "cudaMalloc(tensor-path operands)");
@@ -313,26 +277,28 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   auto par = [&](int v) { return P + j->vars[m->var[v]].offset; };
   auto grd = [&](int v) { return G + j->vars[m->var[v]].offset; };
   int rc;
-  auto mk = [&](TcGemm& g, const char* name, const void* A, long long a_rows, long long lda, const void* Bp,
-                long long b_rows, long long ldb, int K, float* C, int block_n, int splits,
+  // operand = (pointer, row-major pitch, mn_major); rows/K follow from the GEMM shape
+  auto mk = [&](TcGemm& g, const char* name, int M, int N, int K, const void* A, long long lda, bool a_mn,
+                const void* Bp, long long ldb, bool b_mn, float* C, int block_n, int splits,
                 tc::Epilogue epi) -> int {
-    g.name = name; g.M = (int)a_rows; g.N = (int)b_rows; g.K = K; g.C = C; g.ldc = (int)b_rows;
+    g.name = name; g.M = M; g.N = N; g.K = K; g.C = C; g.ldc = N;
     g.block_n = block_n; g.splits = splits; g.epi = epi; g.partial = t->partial;
-    if ((rc = make_map(&g.a, kind, A, a_rows, K, lda, tc::kBlockM))) return rc;
-    return make_map(&g.b, kind, Bp, b_rows, K, ldb, block_n);
+    g.a_mn = a_mn; g.b_mn = b_mn;
+    if ((rc = make_map(&g.a, kind, A, M, K, lda, tc::kBlockM, a_mn))) return rc;
+    return make_map(&g.b, kind, Bp, N, K, ldb, block_n, b_mn);
   };
-  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", t->col_lp, M2, 800, sh->w2_t, 64, 800, 800, s.y2, 64, 1,
+  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, sh->w2_lp, 64, true, s.y2, 64, 1,
                tc::Epilogue{par(3), nullptr, 0}))) return rc;
-  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", t->a2_lp, B, 3136, sh->w3_t, 1024, 3136, 3136, s.h1, 64, 1,
+  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, t->a2_lp, 3136, false, sh->w3_lp, 1024, true, s.h1, 64, 1,
                tc::Epilogue{par(5), nullptr, 1}))) return rc;
-  if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", t->a2_t, 3136, t->ld_b, t->dh1_t, 1024, t->ld_b, B, grd(4), 128, 1,
-               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
-  if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", t->dh1_lp, B, 1024, sh->w3_lp, 3136, 1024, 1024, s.da2, 64, 1,
-               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
-  if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", t->col_t, 800, t->ld_m2, t->dy2_t, 64, t->ld_m2, M2, grd(2), 64,
-               kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
-  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", t->dy2_lp, M2, 64, sh->w2_lp, 800, 64, 64, s.dcol, 128, 1,
-               tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, t->a2_lp, 3136, true, t->dh1_lp, 1024, true, grd(4),
+               128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, t->dh1_lp, 1024, false, sh->w3_lp, 1024, false, s.da2,
+               64, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
+               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, sh->w2_lp, 64, false, s.dcol,
+               128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   return TFG_OK;
 }
 
@@ -351,23 +317,15 @@ static int tc_forward_t(tfg_job* j, int slot) {
   // weights in operand precision (they change every step)
   cast_kernel<T><<<blocks_for(800 * 64 / 4), 256, 0, st>>>(W2, (T*)sh->w2_lp, 800 * 64 / 4);
   TC_LAUNCH_OK(j, "cast W2");
-  transpose_kernel<float, T><<<dim3(2, 25), 256, 0, st>>>(W2, (T*)sh->w2_t, 800, 64, 800);
-  TC_LAUNCH_OK(j, "transpose W2");
   cast_kernel<T><<<blocks_for(3136 * 1024 / 4), 256, 0, st>>>(W3, (T*)sh->w3_lp, 3136 * 1024 / 4);
   TC_LAUNCH_OK(j, "cast W3");
-  transpose_kernel<float, T><<<dim3(32, 98), 256, 0, st>>>(W3, (T*)sh->w3_t, 3136, 1024, 3136);
-  TC_LAUNCH_OK(j, "transpose W3");
   // conv2 as im2col GEMM
   im2col_lp_kernel<T><<<blocks_for((long long)M2 * 200), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
   TC_LAUNCH_OK(j, "im2col_lp_kernel");
-  im2col_t_kernel<T><<<dim3((M2 + 31) / 32, 25), 256, 0, st>>>(s.a1, (T*)t->col_t, B, t->ld_m2);
-  TC_LAUNCH_OK(j, "im2col_t_kernel");
   if ((rc = launch_tc(j, t->conv2_fwd, m->math, st))) return rc;
   if ((rc = mnist_pool2(j, slot))) return rc;
   cast_kernel<T><<<blocks_for((long long)B * 3136 / 4), 256, 0, st>>>(s.a2, (T*)t->a2_lp, (long long)B * 3136 / 4);
   TC_LAUNCH_OK(j, "cast a2");
-  transpose_kernel<float, T><<<dim3(98, (B + 31) / 32), 256, 0, st>>>(s.a2, (T*)t->a2_t, B, 3136, t->ld_b);
-  TC_LAUNCH_OK(j, "transpose a2");
   return launch_tc(j, t->fc1_fwd, m->math, st);
 }
 
@@ -377,18 +335,14 @@ static int tc_backward_t(tfg_job* j, int slot) {
   MnistSlot& s = m->slots[slot];
   TcSlot* t = static_cast<TcSlot*>(s.tc);
   cudaStream_t st = j->stream;
-  const int B = m->B, M2 = B * 196;
+  const int B = m->B;
   int rc;
   cast_kernel<T><<<blocks_for((long long)B * 1024 / 4), 256, 0, st>>>(s.dh1, (T*)t->dh1_lp, (long long)B * 1024 / 4);
   TC_LAUNCH_OK(j, "cast dh1");
-  transpose_kernel<float, T><<<dim3(32, (B + 31) / 32), 256, 0, st>>>(s.dh1, (T*)t->dh1_t, B, 1024, t->ld_b);
-  TC_LAUNCH_OK(j, "transpose dh1");
   if ((rc = launch_tc(j, t->fc1_wgrad, m->math, st))) return rc;
   if ((rc = launch_tc(j, t->fc1_dgrad, m->math, st))) return rc;
   unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, B, 7, 64);
   TC_LAUNCH_OK(j, "unpool_lp_kernel");
-  transpose_kernel<T, T><<<dim3(2, (M2 + 31) / 32), 256, 0, st>>>((const T*)t->dy2_lp, (T*)t->dy2_t, M2, 64, t->ld_m2);
-  TC_LAUNCH_OK(j, "transpose dy2");
   if ((rc = launch_tc(j, t->conv2_wgrad, m->math, st))) return rc;
   return launch_tc(j, t->conv2_dgrad, m->math, st);
 }
@@ -403,9 +357,9 @@ int mnist_tc_backward(tfg_job* j, int slot) {
 }  // namespace tfg
 
 // ---- stateless GEMM entry point (parity tests of the tensor kernel alone) --------------------
-extern "C" int tfg_gemm_tn(int math, const void* a_dev, const void* b_dev, float* c_dev, int M, int N, int K,
-                           int64_t lda, int64_t ldb, int block_n, int splits, float* partial_dev,
-                           const float* bias_dev, int relu, void* stream) {
+extern "C" int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const void* b_dev, int b_mn_major,
+                           float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb, int block_n, int splits,
+                           float* partial_dev, const float* bias_dev, int relu, void* stream) {
   using namespace tfg;
   if (math != TFG_MATH_BF16 && math != TFG_MATH_TF32) return fail(nullptr, TFG_EINVAL, "math must be bf16 or tf32");
   if (!a_dev || !b_dev || !c_dev || M < 1 || N < 1 || K < 1) return fail(nullptr, TFG_EINVAL, "bad argument");
@@ -414,9 +368,10 @@ extern "C" int tfg_gemm_tn(int math, const void* a_dev, const void* b_dev, float
   g.name = "tc gemm";
   g.M = M; g.N = N; g.K = K; g.C = c_dev; g.ldc = N; g.block_n = block_n; g.splits = splits < 1 ? 1 : splits;
   g.partial = partial_dev;
+  g.a_mn = a_mn_major != 0; g.b_mn = b_mn_major != 0;
   g.epi = tc::Epilogue{bias_dev, nullptr, relu};
-  int rc = make_map(&g.a, math, a_dev, M, K, lda, tc::kBlockM);
+  int rc = make_map(&g.a, math, a_dev, M, K, lda, tc::kBlockM, g.a_mn);
   if (rc) return rc;
-  if ((rc = make_map(&g.b, math, b_dev, N, K, ldb, block_n))) return rc;
+  if ((rc = make_map(&g.b, math, b_dev, N, K, ldb, block_n, g.b_mn))) return rc;
   return launch_tc(nullptr, g, math, (cudaStream_t)stream);
 }

@@ -1,5 +1,7 @@
-// tcgen05 GEMM for sm_100a:  C[M,N] (fp32) = A[M,K] * B[N,K]^T, both operands K-major
-// ("TN"), bf16 (kind::f16) or tf32 (kind::tf32) operands, fp32 accumulation in TMEM.
+// tcgen05 GEMM for sm_100a:  C[M,N] (fp32) = A(M x K) * B(N x K)^T with bf16 (kind::f16) or
+// tf32 (kind::tf32) operands and fp32 accumulation in TMEM.  Each operand may be stored
+// K-major ([rows, K], K contiguous) or MN-major ([K, rows], rows contiguous), so every
+// product of two row-major matrices, transposed or not, runs without a transposed copy.
 //
 //   * operands reach shared memory by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle,
 //     out-of-bounds rows/columns zero-filled, so M, N and K need no padding);
@@ -71,22 +73,30 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
-// Shared-memory matrix descriptor, K-major, 128-byte swizzle: rows are 128 B apart inside an
-// 8-row atom, atoms 1024 B apart (stride byte offset); version 1 (Blackwell); layout type 2.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+// Shared-memory matrix descriptor, 128-byte swizzle, version 1 (Blackwell), layout type 2.
+//   K-major : a tile row (128 B of K) every 128 B, 8-row atoms 1024 B apart = stride byte
+//             offset; the leading byte offset is not used.
+//   MN-major: a 128-B line holds 64 bf16 / 32 tf32 consecutive rows of ONE k; 8 consecutive
+//             k form a 1024-B atom (stride byte offset = 1024); the next 128 B worth of rows
+//             is a separate TMA box `lbo_bytes` further on (leading byte offset).
+//   MN-major with 32-bit elements (tf32) uses the "128B swizzle, 32-byte base" layout
+//             (type 1): 32-B chunks are swizzled, 4 consecutive k form a 512-B atom.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                   uint32_t sbo_bytes = 1024, uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);        // start address   [0,14)
-  d |= static_cast<uint64_t>(1) << 16;                            // leading byte offset (unused) [16,30)
-  d |= static_cast<uint64_t>(1024 >> 4) << 32;                    // stride byte offset [32,46)
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;   // leading byte offset [16,30)
+  d |= static_cast<uint64_t>(sbo_bytes >> 4) << 32;               // stride byte offset [32,46)
   d |= static_cast<uint64_t>(1) << 46;                            // descriptor version [46,48)
-  d |= static_cast<uint64_t>(2) << 61;                            // SWIZZLE_128B       [61,64)
+  d |= static_cast<uint64_t>(layout_type) << 61;                  // 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B [61,64)
   return d;
 }
 
-// Instruction descriptor: D = F32, A/B format `fmt` (1 = BF16, 2 = TF32), both K-major,
-// N >> 3 at bit 17, M >> 4 at bit 24.
-__host__ __device__ constexpr uint32_t make_idesc(int fmt, int n) {
+// Instruction descriptor: D = F32, A/B format `fmt` (1 = BF16, 2 = TF32), operand majors at
+// bits 15/16 (0 = K-major, 1 = MN-major), N >> 3 at bit 17, M >> 4 at bit 24.
+__host__ __device__ constexpr uint32_t make_idesc(int fmt, int n, bool a_mn, bool b_mn) {
   return (1u << 4) | (static_cast<uint32_t>(fmt) << 7) | (static_cast<uint32_t>(fmt) << 10) |
+         (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u) |
          (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(kBlockM >> 4) << 24);
 }
 
@@ -117,14 +127,20 @@ constexpr size_t smem_bytes() {
          (2 * kStages + 1) * sizeof(uint64_t) + 16;
 }
 
-template <int BLOCK_N, int KIND>
+template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
                Epilogue epi) {
   constexpr int kElemBytes = KIND == 0 ? 2 : 4;
   constexpr int kBlockK = kBlockKBytes / kElemBytes;           // elements of K per stage
   constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
+  constexpr int kMnElems = 128 / kElemBytes;                   // rows per 128-B line of an MN-major box
+  constexpr int kChunkBytes = kBlockK * 128;                   // one MN-major box: kBlockK lines of 128 B
+  constexpr int kUmmaK = 32 / kElemBytes;                      // K per instruction: 16 (bf16), 8 (tf32)
+  // descriptor start-address step (16-B units) per instruction along K
+  constexpr uint32_t kStepA = A_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
+  constexpr uint32_t kStepB = B_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
   static_assert(BLOCK_N == 64 || BLOCK_N == 128, "TMEM columns must be a power of two >= 32");
 
   extern __shared__ uint8_t smem_raw[];
@@ -171,24 +187,39 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         mbar_wait(&empty[s], phase ^ 1);
         mbar_expect_tx(&full[s], kABytes + kBBytes);
         const int k_elem = (kb_begin + i) * kBlockK;
-        tma_load_2d(smem_a + s * kABytes, &map_a, &full[s], k_elem, m0);
-        tma_load_2d(smem_b + s * kBBytes, &map_b, &full[s], k_elem, n0);
+        if (!A_MN) {
+          tma_load_2d(smem_a + s * kABytes, &map_a, &full[s], k_elem, m0);
+        } else {
+#pragma unroll
+          for (int c = 0; c < kBlockM / kMnElems; ++c)
+            tma_load_2d(smem_a + s * kABytes + c * kChunkBytes, &map_a, &full[s], m0 + c * kMnElems, k_elem);
+        }
+        if (!B_MN) {
+          tma_load_2d(smem_b + s * kBBytes, &map_b, &full[s], k_elem, n0);
+        } else {
+#pragma unroll
+          for (int c = 0; c < BLOCK_N / kMnElems; ++c)
+            tma_load_2d(smem_b + s * kBBytes + c * kChunkBytes, &map_b, &full[s], n0 + c * kMnElems, k_elem);
+        }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N);
+      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
       for (int i = 0; i < n_kb; ++i) {
         const int s = i % kStages;
         const uint32_t phase = (i / kStages) & 1;
         mbar_wait(&full[s], phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes));
-        const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes));
+        constexpr bool kBase32 = KIND == 1;   // MN-major tf32: 32-byte-base swizzle, 4-line atoms
+        const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), A_MN ? kChunkBytes : 16,
+                                           (A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
+        const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16,
+                                           (B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
 #pragma unroll
-        for (int k = 0; k < kBlockKBytes / 32; ++k)   // 32 bytes of K per instruction
-          umma<KIND>(tmem_base, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+        for (int k = 0; k < kBlockK / kUmmaK; ++k)    // 32 bytes of K per instruction
+          umma<KIND>(tmem_base, da + kStepA * k, db + kStepB * k, idesc, (i | k) != 0);
         umma_commit(&empty[s]);                        // frees the stage when these MMAs retire
       }
       umma_commit(tmem_full);                          // accumulator complete

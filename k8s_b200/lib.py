@@ -103,8 +103,8 @@ _SIGS = {
     "tfg_loss_get": (C.c_int, [_p, C.c_int, C.POINTER(C.c_float)]),
     "tfg_job_sync": (C.c_int, [_p]),
     "tfg_launch_count": (C.c_int64, [_p]),
-    "tfg_gemm_tn": (C.c_int, [C.c_int, _p, _p, _p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int,
-                              C.c_int, _p, _p, C.c_int, _p]),
+    "tfg_gemm_tc": (C.c_int, [C.c_int, _p, C.c_int, _p, C.c_int, _p, C.c_int, C.c_int, C.c_int, C.c_int64,
+                              C.c_int64, C.c_int, C.c_int, _p, _p, C.c_int, _p]),
     "tfg_profile_enable": (C.c_int, [_p, C.c_int]),
     "tfg_profile_report": (C.c_int, [_p, C.c_char_p, C.c_size_t]),
     "tfg_smoke": (C.c_int, [_p, C.c_int, _p, C.c_size_t, C.POINTER(C.c_int)]),

@@ -23,20 +23,27 @@ SHAPES = [
 ]
 
 
+@pytest.mark.parametrize("majors", ["KK", "KM", "MM", "MK"])     # storage of A and B: K-major or MN-major
 @pytest.mark.parametrize("math", ["bf16", "tf32"])
 @pytest.mark.parametrize("M,N,K,block_n,splits", SHAPES)
-def test_gemm_tn_matches_float64(lib, math, M, N, K, block_n, splits):
+def test_gemm_tc_matches_float64(lib, math, majors, M, N, K, block_n, splits):
     g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
     a = torch.randn(M, K, generator=g)
     b = torch.randn(N, K, generator=g)
     if math == "bf16":
         a, b = a.bfloat16(), b.bfloat16()
-    da, db = a.cuda().contiguous(), b.cuda().contiguous()
+    a_mn, b_mn = majors[0] == "M", majors[1] == "M"
+    esize = 2 if math == "bf16" else 4
+    if (a_mn and (M * esize) % 16) or (b_mn and (N * esize) % 16):
+        pytest.skip("row pitch of the MN-major operand is not a multiple of 16 bytes")
+    da = (a.t() if a_mn else a).contiguous().cuda()               # MN-major = stored [K, rows]
+    db = (b.t() if b_mn else b).contiguous().cuda()
+    lda, ldb = (M if a_mn else K), (N if b_mn else K)
     c = torch.full((M, N), float("nan"), device="cuda")
     partial = torch.empty(max(splits, 1) * M * N, device="cuda")
     bias = torch.randn(N, generator=g).cuda() if splits == 1 else None
-    rc = lib.gemm_tn(L.MATH_MODES[math], da.data_ptr(), db.data_ptr(), c.data_ptr(), M, N, K, K, K, block_n,
-                     splits, partial.data_ptr(), bias.data_ptr() if bias is not None else None, 0, 0)
+    rc = lib.gemm_tc(L.MATH_MODES[math], da.data_ptr(), int(a_mn), db.data_ptr(), int(b_mn), c.data_ptr(), M, N, K,
+                     lda, ldb, block_n, splits, partial.data_ptr(), bias.data_ptr() if bias is not None else None, 0, 0)
     lib.check(rc)
     torch.cuda.synchronize()
     ref = a.double() @ b.double().T
@@ -49,18 +56,22 @@ def test_gemm_tn_matches_float64(lib, math, M, N, K, block_n, splits):
     assert bool((err <= tol).all()), "max err %.3e at bound %.3e" % (float(err.max()), float(bound.max()))
 
 
-def test_gemm_tn_relu_and_argument_checks(lib):
+def test_gemm_tc_relu_and_argument_checks(lib):
     a = torch.randn(64, 64).bfloat16().cuda()
     b = torch.randn(32, 64).bfloat16().cuda()
     c = torch.empty(64, 32, device="cuda")
-    lib.check(lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 64, 1, None,
-                          None, 1, 0))
+
+    def call(math, K, ld, block_n, splits, aa=a, bb=b):
+        return lib.gemm_tc(math, aa.data_ptr(), 0, bb.data_ptr(), 0, c.data_ptr(), 64, 32, K, ld, ld, block_n, splits,
+                           None, None, 1, 0)
+
+    lib.check(call(L.MATH_BF16, 64, 64, 64, 1))
     torch.cuda.synchronize()
     ref = torch.relu(a.float() @ b.float().T)
     assert torch.allclose(c, ref, rtol=1e-4, atol=1e-4)
-    assert lib.gemm_tn(L.MATH_FP32, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 64, 1, None, None, 0, 0) == 2
-    assert lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 64, 64, 64, 96, 1, None, None, 0, 0) == 2
-    assert lib.gemm_tn(L.MATH_BF16, a.data_ptr(), b.data_ptr(), c.data_ptr(), 64, 32, 60, 60, 60, 64, 1, None, None, 0, 0) == 2  # 120-B pitch
+    assert call(L.MATH_FP32, 64, 64, 64, 1) == 2
+    assert call(L.MATH_BF16, 64, 64, 96, 1) == 2
+    assert call(L.MATH_BF16, 60, 60, 64, 1) == 2                     # 120-byte pitch
     a2 = torch.randn(64, 128).bfloat16().cuda()
     b2 = torch.randn(32, 128).bfloat16().cuda()
-    assert lib.gemm_tn(L.MATH_BF16, a2.data_ptr(), b2.data_ptr(), c.data_ptr(), 64, 32, 128, 128, 128, 64, 2, None, None, 0, 0) == 2  # split-K w/o partial
+    assert call(L.MATH_BF16, 128, 128, 64, 2, a2, b2) == 2           # split-K without a partial buffer
