@@ -64,11 +64,14 @@ struct TcGemm {
 };
 
 __global__ void __launch_bounds__(256)
-splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, long long mn) {
+splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, long long mn,
+                     const float* __restrict__ bias, int N, int relu) {
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (i >= mn) return;
   float s = 0.f;
   for (int z = 0; z < splits; ++z) s += partial[z * mn + i];   // fixed order: deterministic
+  if (bias) s += bias[i % N];
+  if (relu) s = fmaxf(s, 0.f);
   out[i] = s;
 }
 
@@ -121,7 +124,9 @@ static int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
   if (e != cudaSuccess) return fail_cuda(j, e, g.name);
   if (splits > 1) {
     const long long mn = (long long)g.M * g.N;
-    splitk_reduce_kernel<<<(int)((mn + 255) / 256), 256, 0, s>>>(g.partial, g.C, splits, mn);
+    if (g.epi.mask) return fail(j, TFG_EINVAL, "split-K cannot apply a mask epilogue");
+    splitk_reduce_kernel<<<(int)((mn + 255) / 256), 256, 0, s>>>(g.partial, g.C, splits, mn, g.epi.bias, g.N,
+                                                                 g.epi.relu);
     if (j) prof_mark(j, "split-K reduce");
     if ((e = cudaGetLastError()) != cudaSuccess) return fail_cuda(j, e, "splitk_reduce_kernel");
   }
@@ -206,6 +211,8 @@ struct TcSlot {            // per replica slot: operand copies of activations + 
 };
 
 constexpr int kSplitW2Tc = 21;   // 7 M-tiles x 21 K-splits = 147 CTAs on 148 SMs
+constexpr int kSplitFc1Fwd = 7;  // B = 128: 16 N-tiles x 7 K-splits = 112 CTAs instead of 16
+constexpr int kSplitFc1Dgrad = 3;  // 49 N-tiles x 3 = 147 CTAs
 
 static inline int blocks_for(long long n, int per = 256) {
   long long b = (n + per - 1) / per;
@@ -258,7 +265,9 @@ int mnist_tc_build(tfg_job* j) {
     alloc(&t->a2_lp, (size_t)B * 3136 * es);
     alloc(&t->dh1_lp, (size_t)B * 1024 * es);
     alloc(&t->dy2_lp, (size_t)M2 * 64 * es);
-    alloc((void**)&t->partial, sizeof(float) * kSplitW2Tc * 800 * 64);
+    alloc((void**)&t->partial, sizeof(float) * std::max<size_t>({(size_t)kSplitW2Tc * 800 * 64,
+                                                                  (size_t)kSplitFc1Fwd * B * 1024,
+                                                                  (size_t)kSplitFc1Dgrad * B * 3136}));
   }
   if (e != cudaSuccess) return fail_cuda(j, e, "cudaMalloc(tensor-path operands)");
   return TFG_OK;
@@ -289,12 +298,12 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   };
   if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, sh->w2_lp, 64, true, s.y2, 64, 1,
                tc::Epilogue{par(3), nullptr, 0}))) return rc;
-  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, t->a2_lp, 3136, false, sh->w3_lp, 1024, true, s.h1, 64, 1,
-               tc::Epilogue{par(5), nullptr, 1}))) return rc;
+  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, t->a2_lp, 3136, false, sh->w3_lp, 1024, true, s.h1, 64,
+               kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1}))) return rc;
   if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, t->a2_lp, 3136, true, t->dh1_lp, 1024, true, grd(4),
                128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, t->dh1_lp, 1024, false, sh->w3_lp, 1024, false, s.da2,
-               64, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+               64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
                64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, sh->w2_lp, 64, false, s.dcol,

@@ -124,7 +124,7 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 template <int BLOCK_N>
 constexpr size_t smem_bytes() {
   return 1024 /*alignment slack*/ + static_cast<size_t>(kStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kStages + 1) * sizeof(uint64_t) + 16;
+         (2 * kStages + 1) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
 }
 
 template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
@@ -151,6 +151,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   uint64_t* empty = full + kStages;
   uint64_t* tmem_full = empty + kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);   // 4 epilogue warps x [32][33] floats
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * kBlockM, n0 = blockIdx.x * BLOCK_N;
@@ -225,22 +226,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       umma_commit(tmem_full);                          // accumulator complete
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> global =====
+    // ===== epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =====
+    // tcgen05.ld hands thread t row t of its lane quarter.  Storing that directly would make
+    // every store instruction touch 32 different rows; instead each warp bounces a 32x32 block
+    // through its private staging tile so that 8 lanes write one 128-byte row segment.
     const int q = warp & 3;                            // TMEM lane quarter this warp may touch
-    const int row = m0 + q * 32 + lane;
+    float (*stage)[33] = reinterpret_cast<float (*)[33]>(stage_base + (warp - 2) * 32 * 33);
     if (n_kb > 0) {
       mbar_wait(tmem_full, 0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
-    float* crow = C + (static_cast<size_t>(blockIdx.z) * M + row) * static_cast<size_t>(ldc);
-    // 128-bit stores need 16-B aligned rows (C, bias and mask come from cudaMalloc / 128-B
+    float* cbase = C + static_cast<size_t>(blockIdx.z) * M * static_cast<size_t>(ldc);
+    // 128-bit accesses need 16-B aligned rows (C, bias and mask come from cudaMalloc / 128-B
     // aligned variable offsets; the leading dimension decides the rest)
     const bool vec_ok = (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
                         (!epi.bias || (reinterpret_cast<uintptr_t>(epi.bias) & 15) == 0) &&
                         (!epi.mask || (reinterpret_cast<uintptr_t>(epi.mask) & 15) == 0);
 #pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
-      uint32_t r[16];
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      uint32_t r[32];
       if (n_kb > 0) {
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
         asm volatile(
@@ -249,17 +253,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
             : "r"(taddr) : "memory");
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+              "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+              "=r"(r[30]), "=r"(r[31])
+            : "r"(taddr + 16) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       } else {
 #pragma unroll
-        for (int u = 0; u < 16; ++u) r[u] = 0u;
+        for (int u = 0; u < 32; ++u) r[u] = 0u;
       }
-      if (row < M && vec_ok && n0 + c0 + 16 <= N) {
 #pragma unroll
-        for (int u = 0; u < 16; u += 4) {
-          const int col = n0 + c0 + u;
-          float4 v = make_float4(__uint_as_float(r[u]), __uint_as_float(r[u + 1]), __uint_as_float(r[u + 2]),
-                                 __uint_as_float(r[u + 3]));
+      for (int u = 0; u < 32; ++u) stage[lane][u] = __uint_as_float(r[u]);   // bank (lane + u) % 32
+      __syncwarp();
+      const int cc = (lane & 7) * 4;
+      const int col = n0 + c0 + cc;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int rr = i * 4 + (lane >> 3);
+        const int row = m0 + q * 32 + rr;
+        float4 v = make_float4(stage[rr][cc], stage[rr][cc + 1], stage[rr][cc + 2], stage[rr][cc + 3]);
+        if (row >= M || col >= N) continue;
+        float* dst = cbase + static_cast<size_t>(row) * ldc + col;
+        if (vec_ok && col + 3 < N) {
           if (epi.bias) {
             const float4 b = *reinterpret_cast<const float4*>(epi.bias + col);
             v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
@@ -270,21 +288,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             v.x = k.x > 0.f ? v.x : 0.f; v.y = k.y > 0.f ? v.y : 0.f;
             v.z = k.z > 0.f ? v.z : 0.f; v.w = k.w > 0.f ? v.w : 0.f;
           }
-          *reinterpret_cast<float4*>(crow + col) = v;
-        }
-      } else if (row < M) {
+          *reinterpret_cast<float4*>(dst) = v;
+        } else {
+          const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int u = 0; u < 16; ++u) {
-          const int col = n0 + c0 + u;
-          if (col < N) {
-            float v = __uint_as_float(r[u]);
-            if (epi.bias) v += epi.bias[col];
-            if (epi.relu) v = fmaxf(v, 0.f);
-            if (epi.mask) v = epi.mask[static_cast<size_t>(row) * ldc + col] > 0.f ? v : 0.f;
-            crow[col] = v;
+          for (int u = 0; u < 4; ++u) {
+            if (col + u >= N) break;
+            float x = vv[u];
+            if (epi.bias) x += epi.bias[col + u];
+            if (epi.relu) x = fmaxf(x, 0.f);
+            if (epi.mask) x = epi.mask[static_cast<size_t>(row) * ldc + col + u] > 0.f ? x : 0.f;
+            dst[u] = x;
           }
         }
       }
+      __syncwarp();
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

@@ -70,10 +70,10 @@ conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1
 // g1m = gradient at the pooled pre-relu map (already masked by a1 > 0).
 __global__ void __launch_bounds__(256)
 conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
-                 const uint8_t* __restrict__ idx1, float* __restrict__ partial /*[B][832]*/) {
+                 const uint8_t* __restrict__ idx1, float* __restrict__ partial /*[2B][832]*/) {
   __shared__ float xs[32][33];
   __shared__ float red[8][26][32];
-  const int b = blockIdx.x, t = threadIdx.x, w = t >> 5, c = t & 31;
+  const int b = blockIdx.x >> 1, half = blockIdx.x & 1, t = threadIdx.x, w = t >> 5, c = t & 31;
   for (int i = t; i < 32 * 32; i += 256) {
     int r = i >> 5, q = i & 31;
     int ir = r - 2, ic = q - 2;
@@ -84,7 +84,8 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
   float accb = 0.f;
 #pragma unroll
   for (int k = 0; k < 25; ++k) acc[k] = 0.f;
-  for (int o = t; o < 14 * 14 * 32; o += 256) {   // o & 31 == c for every iteration
+  // this block's half of the pooled map: rows [7*half, 7*half + 7)
+  for (int o = half * (7 * 14 * 32) + t; o < (half + 1) * (7 * 14 * 32); o += 256) {   // o & 31 == c
     const int pw = (o >> 5) % 14, ph = (o >> 5) / 14;
     const size_t oi = (size_t)b * (14 * 14 * 32) + o;
     const float g = g1m[oi];
@@ -105,7 +106,7 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
     float s = red[0][k][cc];
 #pragma unroll
     for (int ww = 1; ww < 8; ++ww) s += red[ww][k][cc];
-    partial[(size_t)b * 832 + i] = s;   // [25*32 dW | 32 db]
+    partial[(size_t)blockIdx.x * 832 + i] = s;   // [25*32 dW | 32 db], two rows per image
   }
 }
 
@@ -361,26 +362,27 @@ __global__ void __launch_bounds__(256) loss_mean_kernel(const float* __restrict_
 
 
 // ===== classifier head, forward: logits = h1 * W4 + b4, softmax cross-entropy, dlogits ======
-// One warp per example.  Lanes stride K = 1024; the 10 partial sums per lane are combined by
-// xor-shuffles (fixed order), after which every lane holds all 10 logits.
+// One block of 8 warps per example: warp w covers k in [128w, 128w+128), partial sums are
+// combined by xor-shuffles and a fixed-order pass over the 8 warps.
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, const float* __restrict__ b4,
                 const int32_t* __restrict__ labels, float* __restrict__ logits, float* __restrict__ dlogits,
                 float* __restrict__ loss_vec, int B) {
-  const int lane = threadIdx.x & 31;
-  const int ex = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (ex >= B) return;
+  __shared__ float part[8][10];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int ex = blockIdx.x;
   float acc[10];
 #pragma unroll
   for (int n = 0; n < 10; ++n) acc[n] = 0.f;
   const float* h = h1 + (size_t)ex * 1024;
-#pragma unroll 4
-  for (int k = lane; k < 1024; k += 32) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int k = w * 128 + i * 32 + lane;
     const float hv = h[k];
-    const float2* w = reinterpret_cast<const float2*>(w4 + k * 10);   // rows are 40 B: 8-B aligned
+    const float2* wr = reinterpret_cast<const float2*>(w4 + k * 10);   // rows are 40 B: 8-B aligned
 #pragma unroll
     for (int n2 = 0; n2 < 5; ++n2) {
-      const float2 wv = w[n2];
+      const float2 wv = wr[n2];
       acc[2 * n2] = fmaf(hv, wv.x, acc[2 * n2]);
       acc[2 * n2 + 1] = fmaf(hv, wv.y, acc[2 * n2 + 1]);
     }
@@ -389,74 +391,88 @@ head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, cons
   for (int n = 0; n < 10; ++n) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc[n] += __shfl_xor_sync(0xffffffffu, acc[n], o);
-    acc[n] += b4[n];
+    if (lane == 0) part[w][n] = acc[n];
   }
-  float mx = acc[0];
+  __syncthreads();
+  if (w != 0) return;
+  float z = -INFINITY;
+  if (lane < 10) {
+    z = b4[lane];
 #pragma unroll
-  for (int n = 1; n < 10; ++n) mx = fmaxf(mx, acc[n]);
-  float e[10], sum = 0.f;
+    for (int ww = 0; ww < 8; ++ww) z += part[ww][lane];
+  }
+  float mx = z;
 #pragma unroll
-  for (int n = 0; n < 10; ++n) { e[n] = expf(acc[n] - mx); sum += e[n]; }
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  const float e = lane < 10 ? expf(z - mx) : 0.f;
+  float sum = e;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   const int lab = labels[ex];
-  float zl = 0.f;
-#pragma unroll
-  for (int n = 0; n < 10; ++n) zl = (n == lab) ? acc[n] : zl;
-#pragma unroll
-  for (int n = 0; n < 10; ++n)
-    if (lane == n) {
-      logits[ex * 10 + n] = acc[n];
-      dlogits[ex * 10 + n] = (e[n] / sum - (n == lab ? 1.f : 0.f)) / (float)B;
-    }
+  const float zl = __shfl_sync(0xffffffffu, z, lab & 31);
+  if (lane < 10) {
+    logits[ex * 10 + lane] = z;
+    dlogits[ex * 10 + lane] = (e / sum - (lane == lab ? 1.f : 0.f)) / (float)B;
+  }
   if (lane == 0) loss_vec[ex] = logf(sum) - (zl - mx);
 }
 
-// ===== classifier head, backward, one thread per hidden unit k ==============================
+// ===== classifier head, backward =========================================================
 //   dW4[k,:] = sum_b h1[b,k] * dlogits[b,:]        dh1[b,k] = (h1[b,k] > 0) * sum_n dlogits[b,n] W4[k,n]
-//   db3[k]   = sum_b dh1[b,k]                      db4[n]   = sum_b dlogits[b,n]   (last block)
-// Sequential over b in every thread: deterministic, no atomics.
+//   db3[k]   = sum_b dh1[b,k]                      db4[n]   = sum_b dlogits[b,n]
+// One thread per hidden unit k and per chunk of 16 examples (blockIdx.y); chunk partials
+// [chunk][1024*10 | 1024] are summed in chunk order by fc2_bwd_reduce_kernel: no atomics.
+constexpr int kFc2Chunk = 16;
+constexpr int kFc2PartialStride = 1024 * 11;
+
 __global__ void __launch_bounds__(128)
 fc2_bwd_kernel(const float* __restrict__ h1, const float* __restrict__ dlogits, const float* __restrict__ w4,
-               float* __restrict__ dw4, float* __restrict__ db4, float* __restrict__ dh1,
-               float* __restrict__ db3, int B) {
-  __shared__ float dl[64][10];
+               float* __restrict__ partial, float* __restrict__ dh1, int B) {
+  __shared__ float dl[kFc2Chunk][10];
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool tail_block = blockIdx.x == gridDim.x - 1;     // the extra block computes db4
+  const int b0 = blockIdx.y * kFc2Chunk;
+  const int nb = min(kFc2Chunk, B - b0);
+  for (int i = threadIdx.x; i < nb * 10; i += blockDim.x) dl[i / 10][i % 10] = dlogits[(size_t)b0 * 10 + i];
   float w[10], dw[10];
-  float bsum = 0.f, db4acc = 0.f;
 #pragma unroll
-  for (int n = 0; n < 10; ++n) { w[n] = (!tail_block) ? w4[k * 10 + n] : 0.f; dw[n] = 0.f; }
-  for (int b0 = 0; b0 < B; b0 += 64) {
-    const int nb = min(64, B - b0);
-    __syncthreads();
-    for (int i = threadIdx.x; i < nb * 10; i += blockDim.x) dl[i / 10][i % 10] = dlogits[(size_t)b0 * 10 + i];
-    __syncthreads();
-    if (tail_block) {
-      if (threadIdx.x < 10)
-        for (int b = 0; b < nb; ++b) db4acc += dl[b][threadIdx.x];
-      continue;
-    }
+  for (int n = 0; n < 10; ++n) { w[n] = w4[k * 10 + n]; dw[n] = 0.f; }
+  __syncthreads();
+  float bsum = 0.f;
 #pragma unroll 4
-    for (int b = 0; b < nb; ++b) {
-      const float hv = h1[(size_t)(b0 + b) * 1024 + k];
-      float v = 0.f;
+  for (int b = 0; b < nb; ++b) {
+    const float hv = h1[(size_t)(b0 + b) * 1024 + k];
+    float v = 0.f;
 #pragma unroll
-      for (int n = 0; n < 10; ++n) {
-        const float d = dl[b][n];
-        dw[n] = fmaf(hv, d, dw[n]);
-        v = fmaf(d, w[n], v);
-      }
-      v = hv > 0.f ? v : 0.f;
-      dh1[(size_t)(b0 + b) * 1024 + k] = v;
-      bsum += v;
+    for (int n = 0; n < 10; ++n) {
+      const float d = dl[b][n];
+      dw[n] = fmaf(hv, d, dw[n]);
+      v = fmaf(d, w[n], v);
     }
+    v = hv > 0.f ? v : 0.f;
+    dh1[(size_t)(b0 + b) * 1024 + k] = v;
+    bsum += v;
   }
-  if (tail_block) {
-    if (threadIdx.x < 10) db4[threadIdx.x] = db4acc;
-    return;
-  }
+  float* p = partial + (size_t)blockIdx.y * kFc2PartialStride;
 #pragma unroll
-  for (int n = 0; n < 10; ++n) dw4[k * 10 + n] = dw[n];
-  db3[k] = bsum;
+  for (int n = 0; n < 10; ++n) p[k * 10 + n] = dw[n];
+  p[10240 + k] = bsum;
+}
+
+__global__ void __launch_bounds__(256)
+fc2_bwd_reduce_kernel(const float* __restrict__ partial, const float* __restrict__ dlogits,
+                      float* __restrict__ dw4, float* __restrict__ db3, float* __restrict__ db4, int chunks,
+                      int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < kFc2PartialStride) {
+    float s = 0.f;
+    for (int c = 0; c < chunks; ++c) s += partial[(size_t)c * kFc2PartialStride + i];
+    if (i < 10240) dw4[i] = s; else db3[i - 10240] = s;
+  } else if (i < kFc2PartialStride + 10) {
+    const int n = i - kFc2PartialStride;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dlogits[b * 10 + n];
+    db4[n] = s;
+  }
 }
 
 // ===== masked column sums with enough blocks to fill the chip ==============================
@@ -531,7 +547,7 @@ static int sgemm(tfg_job* j, const char* name, const float* A, bool a_kcontig, l
 
 static int colsum(tfg_job* j, const float* in, const float* mask, float* out, int R, int C, float* partial) {
   const int col_blocks = (C + 63) / 64;
-  int chunks = std::max(1, std::min((R + 15) / 16, 2 * kNumSMs / col_blocks));
+  int chunks = std::max(1, std::min((R + 63) / 64, 32));   // few chunks: stage 2 walks them serially
   const int rows_per_chunk = (R + chunks - 1) / chunks;
   chunks = (R + rows_per_chunk - 1) / rows_per_chunk;
   cudaStream_t s = j->stream;
@@ -589,7 +605,7 @@ int mnist_build(tfg_job* j, int batch, int math) {
     A_(g1m, B * 6272, float);
     // scratch for deterministic reductions: split-K partials of dW2 (32 x 800 x 64), the
     // per-image conv1 partials (B x 832) and column-sum chunks
-    size_t sc = std::max<size_t>({(size_t)kSplitW2 * 800 * 64, B * 832,
+    size_t sc = std::max<size_t>({(size_t)kSplitW2 * 800 * 64, 2 * B * 832, ((B + 15) / 16) * (size_t)(1024 * 11),
                                   ((B * 49 + 63) / 64) * 1024, (size_t)3136 * 1024});
     sl.scratch_floats = sc;
     A_(scratch, sc, float);
@@ -672,15 +688,21 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
   }
   // logits = h1 * W4 + b4, softmax cross-entropy and dlogits in one warp-shuffle kernel
-  head_fwd_kernel<<<(B + 7) / 8, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B);
+  head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B);
   LAUNCH_OK(j, "head_fwd_kernel");
   loss_mean_kernel<<<1, 256, 0, st>>>(s.loss_vec, j->loss + j->local_replicas[slot], B);
   LAUNCH_OK(j, "loss_mean_kernel");
 
   // ---------------- backward ----------------
   // dW4, db4, dh1 (masked by h1 > 0) and db3 in one pass over the batch
-  fc2_bwd_kernel<<<1024 / 128 + 1, 128, 0, st>>>(s.h1, s.dlogits, par(6), grd(6), grd(7), s.dh1, grd(5), B);
-  LAUNCH_OK(j, "fc2_bwd_kernel");
+  {
+    const int chunks = (B + kFc2Chunk - 1) / kFc2Chunk;
+    fc2_bwd_kernel<<<dim3(1024 / 128, chunks), 128, 0, st>>>(s.h1, s.dlogits, par(6), s.scratch, s.dh1, B);
+    LAUNCH_OK(j, "fc2_bwd_kernel");
+    fc2_bwd_reduce_kernel<<<(kFc2PartialStride + 10 + 255) / 256, 256, 0, st>>>(s.scratch, s.dlogits, grd(6), grd(5),
+                                                                               grd(7), chunks, B);
+    LAUNCH_OK(j, "fc2_bwd_reduce_kernel");
+  }
   if (tc) {
     if ((rc = mnist_tc_backward(j, slot))) return rc;  // dW3, da2, dcol, dW2 on the tensor path
   } else {
@@ -704,10 +726,10 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   if ((rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
   col2im_mask_kernel<<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
   LAUNCH_OK(j, "col2im_mask_kernel");
-  conv1_bwd_kernel<<<B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
+  conv1_bwd_kernel<<<2 * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  conv1_reduce_kernel<<<(832 + 255) / 256, 256, 0, st>>>(s.scratch, grd(0), grd(1), B);
+  conv1_reduce_kernel<<<(832 + 255) / 256, 256, 0, st>>>(s.scratch, grd(0), grd(1), 2 * B);
   LAUNCH_OK(j, "conv1_reduce_kernel");
   return TFG_OK;
 }

@@ -41,7 +41,7 @@ def test_gemm_tc_matches_float64(lib, math, majors, M, N, K, block_n, splits):
     lda, ldb = (M if a_mn else K), (N if b_mn else K)
     c = torch.full((M, N), float("nan"), device="cuda")
     partial = torch.empty(max(splits, 1) * M * N, device="cuda")
-    bias = torch.randn(N, generator=g).cuda() if splits == 1 else None
+    bias = torch.randn(N, generator=g).cuda()                    # with split-K the reduce pass adds it
     rc = lib.gemm_tc(L.MATH_MODES[math], da.data_ptr(), int(a_mn), db.data_ptr(), int(b_mn), c.data_ptr(), M, N, K,
                      lda, ldb, block_n, splits, partial.data_ptr(), bias.data_ptr() if bias is not None else None, 0, 0)
     lib.check(rc)
