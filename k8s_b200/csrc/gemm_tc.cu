@@ -75,21 +75,29 @@ splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out,
   out[i] = s;
 }
 
-template <int BN, int KIND, bool A_MN, bool B_MN>
-static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
-                               tc::Epilogue epi, cudaStream_t s) {
+template <int BN, int KIND, bool A_MN, bool B_MN, int STAGES>
+static cudaError_t launch_stage(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                                tc::Epilogue epi, cudaStream_t s) {
   static bool attr_set = false;
-  constexpr size_t smem = tc::smem_bytes<BN>();
+  constexpr size_t smem = tc::smem_bytes<BN, STAGES>();
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN>,
+    cudaError_t e = cudaFuncSetAttribute(tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN, STAGES>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   dim3 grid((g.N + BN - 1) / BN, (g.M + tc::kBlockM - 1) / tc::kBlockM, splits);
-  tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, dst, g.M, g.N, ldc, k_blocks,
-                                                                              kps, epi);
+  tc::gemm_tc_kernel<BN, KIND, A_MN, B_MN, STAGES><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, dst, g.M, g.N, ldc,
+                                                                                      k_blocks, kps, epi);
   return cudaGetLastError();
+}
+
+template <int BN, int KIND, bool A_MN, bool B_MN>
+static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                               tc::Epilogue epi, cudaStream_t s) {
+  if (kps <= 1) return launch_stage<BN, KIND, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (kps <= 3) return launch_stage<BN, KIND, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  return launch_stage<BN, KIND, A_MN, B_MN, 4>(g, dst, ldc, k_blocks, kps, splits, epi, s);
 }
 
 template <int BN, int KIND>

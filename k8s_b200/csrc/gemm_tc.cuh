@@ -24,7 +24,7 @@ namespace tc {
 
 constexpr int kBlockM = 128;
 constexpr int kBlockKBytes = 128;      // one 128-B swizzle row of K per stage row
-constexpr int kStages = 4;
+constexpr int kMaxStages = 4;
 constexpr int kThreads = 192;
 constexpr long long kWaitLimitCycles = 4000000000ll;   // ~2 s: a wait that long is a bug -> trap, never hang
 
@@ -121,14 +121,17 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                :: "r"(smem_u32(bar)) : "memory");
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int STAGES>
 constexpr size_t smem_bytes() {
-  return 1024 /*alignment slack*/ + static_cast<size_t>(kStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kStages + 1) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+  return 1024 /*alignment slack*/ + static_cast<size_t>(STAGES) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
+         (2 * STAGES + 1) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
 }
 
-template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 1)
+// STAGES = depth of the TMA ring.  Short-K GEMMs (one or two K blocks per CTA) take 1 or 2
+// stages so that several CTAs fit on an SM (shared memory and TMEM columns permitting) and one
+// CTA's epilogue overlaps its neighbours' loads.
+template <int BLOCK_N, int KIND, bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(kThreads)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
                Epilogue epi) {
@@ -142,6 +145,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   constexpr uint32_t kStepA = A_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
   constexpr uint32_t kStepB = B_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
   static_assert(BLOCK_N == 64 || BLOCK_N == 128, "TMEM columns must be a power of two >= 32");
+  constexpr int kStages = STAGES;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));

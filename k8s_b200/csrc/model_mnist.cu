@@ -495,14 +495,26 @@ colsum_wide_kernel(const float* __restrict__ in, const float* __restrict__ mask,
   if (ry == 0 && c < C) partial[(size_t)blockIdx.y * C + c] = ((red[0][cx] + red[1][cx]) + red[2][cx]) + red[3][cx];
 }
 
-// [B][832] per-image conv1 partials -> dW1 (columns 0..799) and db1 (800..831), image order
+// out[c] = sum over rows r of in[r*stride + c], rows added in a fixed order (lane ty takes rows
+// ty, ty+8, ...; the 8 lane sums are then added 0..7).  Columns below split_c go to out0, the
+// rest to out1.  Block = 32 columns x 8 row lanes, so reads stay 128-byte coalesced.
 __global__ void __launch_bounds__(256)
-conv1_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw1, float* __restrict__ db1, int B) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 832) return;
+reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long stride, float* __restrict__ out0,
+                   int split_c, float* __restrict__ out1) {
+  __shared__ float red[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float s = 0.f;
-  for (int b = 0; b < B; ++b) s += partial[(size_t)b * 832 + c];
-  if (c < 800) dw1[c] = s; else db1[c - 800] = s;
+  if (c < C)
+    for (int r = ty; r < R; r += 8) s += in[(size_t)r * stride + c];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+    float t = red[0][tx];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) t += red[k][tx];
+    if (c < split_c) out0[c] = t; else out1[c - split_c] = t;
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -547,14 +559,14 @@ static int sgemm(tfg_job* j, const char* name, const float* A, bool a_kcontig, l
 
 static int colsum(tfg_job* j, const float* in, const float* mask, float* out, int R, int C, float* partial) {
   const int col_blocks = (C + 63) / 64;
-  int chunks = std::max(1, std::min((R + 63) / 64, 32));   // few chunks: stage 2 walks them serially
+  int chunks = std::max(1, std::min((R + 31) / 32, 128));
   const int rows_per_chunk = (R + chunks - 1) / chunks;
   chunks = (R + rows_per_chunk - 1) / rows_per_chunk;
   cudaStream_t s = j->stream;
   colsum_wide_kernel<<<dim3(col_blocks, chunks), 256, 0, s>>>(in, mask, partial, R, C, rows_per_chunk);
   LAUNCH_OK(j, "colsum_wide_kernel");
-  colsum_stage2_kernel<<<(C + 255) / 256, 256, 0, s>>>(partial, out, chunks, C, C);
-  LAUNCH_OK(j, "colsum_stage2_kernel");
+  reduce_rows_kernel<<<(C + 31) / 32, 256, 0, s>>>(partial, chunks, C, C, out, C, nullptr);
+  LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
 
@@ -729,8 +741,8 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   conv1_bwd_kernel<<<2 * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  conv1_reduce_kernel<<<(832 + 255) / 256, 256, 0, st>>>(s.scratch, grd(0), grd(1), 2 * B);
-  LAUNCH_OK(j, "conv1_reduce_kernel");
+  reduce_rows_kernel<<<(832 + 31) / 32, 256, 0, st>>>(s.scratch, 2 * B, 832, 832, grd(0), 800, grd(1));
+  LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
 
