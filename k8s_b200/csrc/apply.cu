@@ -6,6 +6,8 @@
 // (+4 accum).  Single GPU, SGD: 12 B/param; momentum: 20 B/param.
 #include <type_traits>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace tfg {
@@ -16,6 +18,7 @@ constexpr int kChunk = 4096;            // elements per work chunk = 4 float4 pe
 struct ApplyArgs {
   const float* grads[TFG_MAX_REPLICAS];
   float* pull[TFG_MAX_GPUS];
+  __nv_bfloat16* lp[TFG_MAX_GPUS];   // bf16 shadows of the parameter buffers (own + peers), n_lp of them
   const float* loss_src[TFG_MAX_REPLICAS];
   float* var;
   float* accum;
@@ -23,7 +26,7 @@ struct ApplyArgs {
   const Segment* segs;   // NULL: the single inline segment `seg0`
   Segment seg0;
   int n_segs;
-  int n_grads, n_pull, n_loss, kind;
+  int n_grads, n_pull, n_lp, n_loss, kind;
   long long n_chunks;
   float divisor, lr, mu;
 };
@@ -112,6 +115,13 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
         if (KIND != TFG_OPT_SGD) *reinterpret_cast<float4*>(a.accum + idx[u]) = m[u];
         if (a.var) *reinterpret_cast<float4*>(a.var + idx[u]) = v[u];
         for (int p = 0; p < a.n_pull; ++p) *reinterpret_cast<float4*>(a.pull[p] + idx[u]) = v[u];
+        if (a.n_lp > 0) {   // the tensor path reads its weights from this bf16 copy: no cast kernels per step
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<uint2*>(a.lp[p] + idx[u]) = pk;
+        }
       }
   }
 }
@@ -157,6 +167,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
     a.var = j->params;
     a.n_pull = 0;
     a.n_loss = 0;
+    if (j->params_lp) a.lp[a.n_lp++] = static_cast<__nv_bfloat16*>(j->params_lp);   // owned ranges only
   } else {
     for (int r = 0; r < j->n_replicas; ++r) a.grads[r] = j->peer_grads[r];
     a.n_grads = j->n_replicas;
@@ -165,6 +176,8 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
     a.n_pull = 0;
     for (int g = 0; g < j->n_gpus; ++g)
       if (g != j->gpu_rank) a.pull[a.n_pull++] = j->peer_params[g];
+    if (j->params_lp)
+      for (int g = 0; g < j->n_gpus; ++g) a.lp[a.n_lp++] = static_cast<__nv_bfloat16*>(j->peer_params_lp[g]);
     a.n_loss = j->model ? j->n_replicas : 0;
     for (int r = 0; r < a.n_loss; ++r) a.loss_src[r] = j->peer_loss[r % j->n_gpus] + r;
   }
@@ -239,6 +252,20 @@ int launch_dense_apply(int kind, float* var, float* accum, const float* const* g
     if (e != cudaSuccess) return fail_cuda(nullptr, e, "apply_scalar_kernel");
   }
   return TFG_OK;
+}
+
+__global__ void __launch_bounds__(256)
+cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+int launch_cast_bf16(const float* src, void* dst, long long n, cudaStream_t s) {
+  if (n <= 0) return TFG_OK;
+  long long blocks = (n + 255) / 256;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  cast_bf16_kernel<<<(int)blocks, 256, 0, s>>>(src, static_cast<__nv_bfloat16*>(dst), n);
+  return cudaGetLastError() == cudaSuccess ? TFG_OK : TFG_ECUDA;
 }
 
 // ---- cross-rank barrier ----------------------------------------------------------------

@@ -58,6 +58,7 @@ struct tfg_job {
   cudaStream_t stream = nullptr;
   float* params = nullptr;
   float* accum = nullptr;
+  void* params_lp = nullptr;           // bf16 shadow of `params`, kept current by the apply kernel (bf16 math only)
   std::vector<float*> grads;           // one flat buffer per local replica slot
   float* loss = nullptr;               // [TFG_MAX_REPLICAS + 1]; [r] = replica r, last = mean
   uint32_t* flags = nullptr;           // [TFG_MAX_GPUS] barrier epochs written by peers
@@ -67,6 +68,7 @@ struct tfg_job {
   int* h_err = nullptr;                // pinned
   // peers (index = GPU rank / global replica id); own entries point at own buffers
   float* peer_params[TFG_MAX_GPUS] = {};
+  void* peer_params_lp[TFG_MAX_GPUS] = {};
   float* peer_loss[TFG_MAX_GPUS] = {};
   uint32_t* peer_flags[TFG_MAX_GPUS] = {};
   float* peer_grads[TFG_MAX_REPLICAS] = {};
@@ -125,6 +127,8 @@ void mnist_destroy(tfg_job* j);
 int mnist_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels);
 int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes);
 int mnist_batch(const tfg_job* j);
+int mnist_math(const tfg_job* j);
+int launch_cast_bf16(const float* src, void* dst, long long n, cudaStream_t s);   // apply.cu
 float* mnist_stage_images(tfg_job* j, int slot);
 int32_t* mnist_stage_labels(tfg_job* j, int slot);
 

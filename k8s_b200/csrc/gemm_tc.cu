@@ -146,13 +146,6 @@ template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-template <typename T>
-__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ src, T* __restrict__ dst, long long n4) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
-       i += (long long)gridDim.x * blockDim.x)
-    store4(dst + 4 * i, *reinterpret_cast<const float4*>(src + 4 * i));
-}
-
 // row-major im2col of a1[B,14,14,32] in operand precision: col[m, (kh*5+kw)*32 + c]
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -207,13 +200,13 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
 //   fc1   dgrad da2[B,3136]   = dh1[B,1024] (K)   x W3[3136,1024] (K)
 //   conv2 wgrad dW2[800,64]   = col[M2,800] (MN)  x dy2[M2,64]   (MN)      K = M2, split-K
 //   conv2 dgrad dcol[M2,800]  = dy2[M2,64]  (K)   x W2[800,64]   (K)
-struct TcShared {          // per job: operand-precision copies of the weights
-  void* w2_lp = nullptr;   // [800, 64]
-  void* w3_lp = nullptr;   // [3136, 1024]
-};
+// Weights: bf16 math reads the job's bf16 shadow of the parameter buffer, which the apply
+// kernel (and tfg_var_set) keeps current; tf32 math reads the fp32 parameters themselves.
+// Activations: a2 / dh1 get their bf16 copies from the kernels that produce them
+// (pool_relu_kernel, fc2_bwd_kernel); tf32 reads the fp32 tensors in place.
 
 struct TcSlot {            // per replica slot: operand copies of activations + GEMM descriptors
-  void *col_lp = nullptr, *a2_lp = nullptr, *dh1_lp = nullptr, *dy2_lp = nullptr;
+  void *col_lp = nullptr, *a2_lp = nullptr, *dh1_lp = nullptr, *dy2_lp = nullptr;   // a2/dh1: bf16 math only
   float* partial = nullptr;
   TcGemm conv2_fwd, fc1_fwd, fc1_wgrad, fc1_dgrad, conv2_wgrad, conv2_dgrad;
 };
@@ -238,12 +231,6 @@ static inline int blocks_for(long long n, int per = 256) {
 void mnist_tc_destroy(tfg_job* j) {
   MnistModel* m = j->model;
   if (!m) return;
-  if (m->tc) {
-    TcShared* sh = static_cast<TcShared*>(m->tc);
-    cudaFree(sh->w2_lp); cudaFree(sh->w3_lp);
-    delete sh;
-    m->tc = nullptr;
-  }
   for (auto& sl : m->slots) {
     if (!sl.tc) continue;
     TcSlot* t = static_cast<TcSlot*>(sl.tc);
@@ -254,25 +241,30 @@ void mnist_tc_destroy(tfg_job* j) {
   }
 }
 
+void* mnist_tc_dh1_bf16(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  if (!m || m->math != TFG_MATH_BF16 || !m->slots[slot].tc) return nullptr;
+  return static_cast<TcSlot*>(m->slots[slot].tc)->dh1_lp;
+}
+
 // Allocations only; tensor maps need the flat parameter/gradient buffers, which exist after
 // tfg_vars_finalize, so they are encoded lazily on the first forward (mnist_tc_prepare).
 int mnist_tc_build(tfg_job* j) {
   MnistModel* m = j->model;
-  const size_t es = m->math == TFG_MATH_BF16 ? 2 : 4;
+  const bool bf = m->math == TFG_MATH_BF16;
+  const size_t es = bf ? 2 : 4;
   const long long B = m->B, M2 = B * 196;
-  TcShared* sh = new TcShared();
-  m->tc = sh;
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16); };
-  alloc(&sh->w2_lp, 800 * 64 * es);
-  alloc(&sh->w3_lp, (size_t)3136 * 1024 * es);
   for (auto& sl : m->slots) {
     TcSlot* t = new TcSlot();
     sl.tc = t;
     alloc(&t->col_lp, (size_t)M2 * 800 * es);
-    alloc(&t->a2_lp, (size_t)B * 3136 * es);
-    alloc(&t->dh1_lp, (size_t)B * 1024 * es);
     alloc(&t->dy2_lp, (size_t)M2 * 64 * es);
+    if (bf) {
+      alloc(&t->a2_lp, (size_t)B * 3136 * es);
+      alloc(&t->dh1_lp, (size_t)B * 1024 * es);
+    }
     alloc((void**)&t->partial, sizeof(float) * std::max<size_t>({(size_t)kSplitW2Tc * 800 * 64,
                                                                   (size_t)kSplitFc1Fwd * B * 1024,
                                                                   (size_t)kSplitFc1Dgrad * B * 3136}));
@@ -285,9 +277,19 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
   TcSlot* t = static_cast<TcSlot*>(s.tc);
-  TcShared* sh = static_cast<TcShared*>(m->tc);
   if (t->conv2_fwd.C) return TFG_OK;
   const int kind = m->math;
+  const bool bf = kind == TFG_MATH_BF16;
+  if (bf && !j->params_lp) return fail(j, TFG_ESTATE, "bf16 math needs the bf16 parameter shadow");
+  auto wgt = [&](int v) -> const void* {   // weight operand of variable v
+    const int64_t off = j->vars[m->var[v]].offset;
+    return bf ? static_cast<const void*>(static_cast<const char*>(j->params_lp) + 2 * off)
+              : static_cast<const void*>(j->params + off);
+  };
+  const void* w2 = wgt(2);
+  const void* w3 = wgt(4);
+  const void* a2 = bf ? t->a2_lp : static_cast<const void*>(s.a2);
+  const void* dh1 = bf ? t->dh1_lp : static_cast<const void*>(s.dh1);
   const int B = m->B, M2 = B * 196;
   const float* P = j->params;
   float* G = j->grads[slot];
@@ -304,17 +306,17 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
     if ((rc = make_map(&g.a, kind, A, M, K, lda, tc::kBlockM, a_mn))) return rc;
     return make_map(&g.b, kind, Bp, N, K, ldb, block_n, b_mn);
   };
-  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, sh->w2_lp, 64, true, s.y2, 64, 1,
+  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, w2, 64, true, s.y2, 64, 1,
                tc::Epilogue{par(3), nullptr, 0}))) return rc;
-  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, t->a2_lp, 3136, false, sh->w3_lp, 1024, true, s.h1, 64,
+  if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, a2, 3136, false, w3, 1024, true, s.h1, 64,
                kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1}))) return rc;
-  if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, t->a2_lp, 3136, true, t->dh1_lp, 1024, true, grd(4),
+  if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, a2, 3136, true, dh1, 1024, true, grd(4),
                128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
-  if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, t->dh1_lp, 1024, false, sh->w3_lp, 1024, false, s.da2,
+  if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
                64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
                64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
-  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, sh->w2_lp, 64, false, s.dcol,
+  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
                128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
   return TFG_OK;
 }
@@ -324,25 +326,15 @@ static int tc_forward_t(tfg_job* j, int slot) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
   TcSlot* t = static_cast<TcSlot*>(s.tc);
-  TcShared* sh = static_cast<TcShared*>(m->tc);
   cudaStream_t st = j->stream;
   const int B = m->B, M2 = B * 196;
-  const float* W2 = j->params + j->vars[m->var[2]].offset;
-  const float* W3 = j->params + j->vars[m->var[4]].offset;
   int rc = mnist_tc_prepare(j, slot);
   if (rc) return rc;
-  // weights in operand precision (they change every step)
-  cast_kernel<T><<<blocks_for(800 * 64 / 4), 256, 0, st>>>(W2, (T*)sh->w2_lp, 800 * 64 / 4);
-  TC_LAUNCH_OK(j, "cast W2");
-  cast_kernel<T><<<blocks_for(3136 * 1024 / 4), 256, 0, st>>>(W3, (T*)sh->w3_lp, 3136 * 1024 / 4);
-  TC_LAUNCH_OK(j, "cast W3");
   // conv2 as im2col GEMM
   im2col_lp_kernel<T><<<blocks_for((long long)M2 * 200), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
   TC_LAUNCH_OK(j, "im2col_lp_kernel");
   if ((rc = launch_tc(j, t->conv2_fwd, m->math, st))) return rc;
-  if ((rc = mnist_pool2(j, slot))) return rc;
-  cast_kernel<T><<<blocks_for((long long)B * 3136 / 4), 256, 0, st>>>(s.a2, (T*)t->a2_lp, (long long)B * 3136 / 4);
-  TC_LAUNCH_OK(j, "cast a2");
+  if ((rc = mnist_pool2(j, slot, t->a2_lp))) return rc;     // also drops the bf16 copy of a2
   return launch_tc(j, t->fc1_fwd, m->math, st);
 }
 
@@ -354,9 +346,7 @@ static int tc_backward_t(tfg_job* j, int slot) {
   cudaStream_t st = j->stream;
   const int B = m->B;
   int rc;
-  cast_kernel<T><<<blocks_for((long long)B * 1024 / 4), 256, 0, st>>>(s.dh1, (T*)t->dh1_lp, (long long)B * 1024 / 4);
-  TC_LAUNCH_OK(j, "cast dh1");
-  if ((rc = launch_tc(j, t->fc1_wgrad, m->math, st))) return rc;
+  if ((rc = launch_tc(j, t->fc1_wgrad, m->math, st))) return rc;   // dh1 (bf16) came from fc2_bwd_kernel
   if ((rc = launch_tc(j, t->fc1_dgrad, m->math, st))) return rc;
   unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, B, 7, 64);
   TC_LAUNCH_OK(j, "unpool_lp_kernel");

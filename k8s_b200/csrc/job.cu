@@ -172,6 +172,7 @@ int tfg_job_destroy(tfg_job* j) {
     for (void* p : j->ipc_opened) cudaIpcCloseMemHandle(p);
     cudaFree(j->params);
     cudaFree(j->accum);
+    cudaFree(j->params_lp);
     for (float* g : j->grads) cudaFree(g);
     cudaFree(j->loss);
     cudaFree(j->flags);
@@ -347,6 +348,11 @@ int tfg_vars_finalize(tfg_job* j, int layout) {
     j->peer_grads[j->local_replicas[s]] = g;
   }
   j->peer_params[j->gpu_rank] = j->params;
+  if (j->model && mnist_math(j) == TFG_MATH_BF16) {
+    TFG_CUDA(j, cudaMalloc(&j->params_lp, bytes / 2));
+    TFG_CUDA(j, cudaMemsetAsync(j->params_lp, 0, bytes / 2, j->stream));
+    j->peer_params_lp[j->gpu_rank] = j->params_lp;
+  }
   build_segments(j);
   if (!j->segs.empty()) {
     TFG_CUDA(j, cudaMalloc(&j->d_segs, sizeof(Segment) * j->segs.size()));
@@ -389,7 +395,14 @@ static int var_copy(tfg_job* j, float* base, int var, void* host_out, const void
 }
 
 int tfg_var_set(tfg_job* j, int var, const void* host, size_t bytes) {
-  return var_copy(j, j ? j->params : nullptr, var, nullptr, host, bytes);
+  int rc = var_copy(j, j ? j->params : nullptr, var, nullptr, host, bytes);
+  if (rc == TFG_OK && j->params_lp) {   // keep the bf16 shadow current
+    const VarInfo& v = j->vars[var];
+    if (launch_cast_bf16(j->params + v.offset, static_cast<char*>(j->params_lp) + 2 * v.offset, v.count, j->stream))
+      return fail(j, TFG_ECUDA, "bf16 shadow cast failed");
+    TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+  }
+  return rc;
 }
 int tfg_var_get(tfg_job* j, int var, void* host, size_t bytes) {
   return var_copy(j, j ? j->params : nullptr, var, host, nullptr, bytes);
@@ -446,13 +459,14 @@ int tfg_job_ipc_export(tfg_job* j, void* blob_out, size_t cap, size_t* bytes_out
   if (!j || !blob_out) return fail(j, TFG_EINVAL, "NULL argument");
   if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   size_t nl = j->local_replicas.size();
-  size_t need = 4 + 4 * nl + TFG_IPC_HANDLE_BYTES * (3 + nl);
+  const size_t has_lp = j->params_lp ? 1 : 0;
+  size_t need = 4 + 4 * nl + TFG_IPC_HANDLE_BYTES * (3 + nl + has_lp);
   if (bytes_out) *bytes_out = need;
   if (cap < need) return fail(j, TFG_ELIMIT, "blob_out too small");
   static_assert(sizeof(cudaIpcMemHandle_t) == TFG_IPC_HANDLE_BYTES, "IPC handle size");
   TFG_CUDA(j, cudaSetDevice(j->device));
   char* p = (char*)blob_out;
-  int32_t n32 = (int32_t)nl;
+  int32_t n32 = (int32_t)nl | (has_lp ? 0x10000 : 0);   // bit 16: a bf16 shadow handle follows the gradients
   memcpy(p, &n32, 4); p += 4;
   for (size_t s = 0; s < nl; ++s) { int32_t r = j->local_replicas[s]; memcpy(p, &r, 4); p += 4; }
   void* bufs[3] = {j->params, j->loss, j->flags};
@@ -466,6 +480,11 @@ int tfg_job_ipc_export(tfg_job* j, void* blob_out, size_t cap, size_t* bytes_out
     TFG_CUDA(j, cudaIpcGetMemHandle(&h, j->grads[s]));
     memcpy(p, &h, sizeof h); p += sizeof h;
   }
+  if (has_lp) {
+    cudaIpcMemHandle_t h;
+    TFG_CUDA(j, cudaIpcGetMemHandle(&h, j->params_lp));
+    memcpy(p, &h, sizeof h); p += sizeof h;
+  }
   return TFG_OK;
 }
 
@@ -477,8 +496,12 @@ int tfg_job_ipc_open(tfg_job* j, int peer, const void* blob, size_t bytes) {
   if (bytes < 4) return fail(j, TFG_EINVAL, "short blob");
   int32_t nl;
   memcpy(&nl, p, 4); p += 4;
-  if (nl < 0 || nl > TFG_MAX_REPLICAS || bytes < 4 + 4 * (size_t)nl + TFG_IPC_HANDLE_BYTES * (3 + (size_t)nl))
+  const bool has_lp = (nl & 0x10000) != 0;
+  nl &= 0xffff;
+  if (nl < 0 || nl > TFG_MAX_REPLICAS ||
+      bytes < 4 + 4 * (size_t)nl + TFG_IPC_HANDLE_BYTES * (3 + (size_t)nl + (has_lp ? 1 : 0)))
     return fail(j, TFG_EINVAL, "malformed blob");
+  if (has_lp != (j->params_lp != nullptr)) return fail(j, TFG_EINVAL, "peer runs a different math mode");
   std::vector<int32_t> reps(nl);
   for (int s = 0; s < nl; ++s) { memcpy(&reps[s], p, 4); p += 4; }
   TFG_CUDA(j, cudaSetDevice(j->device));
@@ -502,6 +525,10 @@ int tfg_job_ipc_open(tfg_job* j, int peer, const void* blob, size_t bytes) {
     if ((e = open(&q)) != cudaSuccess) { fail_cuda(j, e, "cudaIpcOpenMemHandle(grads)"); return TFG_EPEER; }
     j->peer_grads[reps[s]] = (float*)q;
   }
+  if (has_lp) {
+    if ((e = open(&q)) != cudaSuccess) { fail_cuda(j, e, "cudaIpcOpenMemHandle(params_lp)"); return TFG_EPEER; }
+    j->peer_params_lp[peer] = q;
+  }
   return TFG_OK;
 }
 
@@ -512,6 +539,8 @@ int tfg_job_attach_local_peer(tfg_job* j, int peer_rank, tfg_job* peer) {
   if (!j->finalized || !peer->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   if (peer->flat_count != j->flat_count) return fail(j, TFG_EINVAL, "peer has a different flat space");
   j->peer_params[peer_rank] = peer->params;
+  j->peer_params_lp[peer_rank] = peer->params_lp;
+  if ((peer->params_lp != nullptr) != (j->params_lp != nullptr)) return fail(j, TFG_EINVAL, "peer runs a different math mode");
   j->peer_loss[peer_rank] = peer->loss;
   j->peer_flags[peer_rank] = peer->flags;
   for (size_t s = 0; s < peer->local_replicas.size(); ++s)
@@ -521,7 +550,7 @@ int tfg_job_attach_local_peer(tfg_job* j, int peer_rank, tfg_job* peer) {
 
 static int check_peers(tfg_job* j) {
   for (int g = 0; g < j->n_gpus; ++g)
-    if (!j->peer_params[g] || !j->peer_flags[g] || !j->peer_loss[g])
+    if (!j->peer_params[g] || !j->peer_flags[g] || !j->peer_loss[g] || (j->params_lp && !j->peer_params_lp[g]))
       return fail(j, TFG_ESTATE, "GPU rank " + std::to_string(g) + " is not mapped (tfg_job_ipc_open)");
   for (int r = 0; r < j->n_replicas; ++r)
     if (!j->peer_grads[r])
