@@ -193,8 +193,14 @@ int tfg_sparse_gather(const float* table_dev, int64_t vocab, int dim, int n_shar
                       float* out_dev, int* bad_dev, void* stream);
 /* [TF1.3] scatter_sub(var, ids, lr*rows): table[local(ids[i]),:] -= scale*rows[i,:],
  * duplicates applied one after another in order of i (bit-exact with the sequential
- * CPU loop).  Needs scratch_dev of at least tfg_sparse_scratch_bytes(n) bytes. */
+ * CPU loop).  Needs scratch_dev of at least tfg_sparse_scratch_bytes(n) bytes.
+ * With tfg_sparse_scratch_bytes_fast(n, dim) bytes or more, rows hit by more than 64 ids
+ * (heavy-tailed id distributions) are handled chunk-parallel instead of by one warp: their
+ * updates are summed in blocks of 128 ids, in order, and the block sums subtracted in order --
+ * deterministic, as accurate as the one-by-one loop, but not bit-identical to it.  Rows hit
+ * by at most 64 ids are bit-exact either way. */
 size_t tfg_sparse_scratch_bytes(int64_t n);
+size_t tfg_sparse_scratch_bytes_fast(int64_t n, int dim);
 int tfg_sparse_scatter_sub(float* table_dev, int64_t vocab, int dim, int n_shards,
                            int shard, int strategy, const int64_t* ids_dev, int64_t n,
                            const float* rows_dev, float scale,
@@ -211,7 +217,8 @@ int tfg_sparse_scatter_sub(float* table_dev, int64_t vocab, int dim, int n_shard
  * imply.  For them the scratch lives inside the library image, in a fixed device array of
  * TFG_SPARSE_STATIC_SCRATCH_BYTES (about 1.03 MiB) that every GPU using the library keeps
  * until the process exits.  The caller still passes table, ids and rows; results are
- * identical to tfg_sparse_scatter_sub.
+ * identical to tfg_sparse_scatter_sub given tfg_sparse_scratch_bytes(n) of scratch (every
+ * duplicate applied in order).
  *   - n > TFG_SPARSE_STATIC_MAX_IDS is rejected with TFG_ELIMIT (split the batch: applying
  *     consecutive slices of ids in order gives the same table).
  *   - The first call on each device looks up the array's device address, once, with that

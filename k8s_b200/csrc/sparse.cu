@@ -259,6 +259,168 @@ scatter_sub_runs_kernel(float* __restrict__ table, int dim, const uint32_t* __re
   }
 }
 
+// ---- long runs (heavy-tailed ids) ------------------------------------------------------------
+// A row hit by more than kLongRun ids would serialise one warp for the whole run.  With enough
+// scratch such a run is cut into chunks of kRunChunk positions: one warp per chunk sums
+// fl(scale * rows[i]) in position order into carry[chunk], then one warp per run subtracts the
+// chunk sums from the table row in chunk order.  Deterministic (fixed chunking, fixed order),
+// but rounded differently from the one-by-one definition, which short runs still follow
+// exactly.
+constexpr int kLongRun = 64;
+constexpr int kRunChunk = 128;
+
+struct LongRun { uint32_t start, len, key, chunk_base; };
+struct ChunkDesc { uint32_t pos, len; };
+
+template <int VEC>
+__device__ __forceinline__ void load_vec(const float* p, float (&v)[VEC]) {
+  if (VEC == 4) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1 % VEC] = t.y; v[2 % VEC] = t.z; v[3 % VEC] = t.w;
+  } else {
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) v[u] = p[u];
+  }
+}
+template <int VEC>
+__device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
+  if (VEC == 4) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1 % VEC], v[2 % VEC], v[3 % VEC]);
+  } else {
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) p[u] = v[u];
+  }
+}
+
+// One warp per sorted position; only run heads act.  Runs of at most kLongRun ids are applied
+// here, one id after another; longer runs are registered for the two kernels below.
+template <int VEC>
+__global__ void __launch_bounds__(256)
+scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
+                         const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
+                         const float* __restrict__ rows, float scale, LongRun* __restrict__ runs,
+                         ChunkDesc* __restrict__ chunks, uint32_t* __restrict__ counters) {
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long p = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
+    const uint32_t k = keys[p];
+    if (k == sentinel) continue;
+    if (p > 0 && keys[p - 1] == k) continue;  // not the head of its run
+    // run length, probing kLongRun positions ahead
+    long long len = 1;
+    bool is_long = true;
+    for (int blk = 0; blk < kLongRun / 32; ++blk) {
+      const long long q = p + 1 + blk * 32 + lane;
+      const uint32_t same = __ballot_sync(0xffffffffu, q < n && keys[q] == k);
+      if (same != 0xffffffffu) { len += __ffs(~same) - 1; is_long = false; break; }
+      len += 32;
+    }
+    float* trow = table + (long long)k * dim;
+    if (!is_long) {
+      for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {  // column panel kept in registers
+        const int c = c0 + lane * VEC;
+        float acc[VEC], gv[VEC];
+        if (c < dim) load_vec<VEC>(trow + c, acc);
+        for (long long q = p; q < p + len; ++q) {
+          const float* g = rows + (long long)vals[q] * dim;
+          if (c < dim) {
+            load_vec<VEC>(g + c, gv);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) acc[u] = __fsub_rn(acc[u], __fmul_rn(scale, gv[u]));
+          }
+        }
+        if (c < dim) store_vec<VEC>(trow + c, acc);
+      }
+      continue;
+    }
+    // long run: its end is the first position whose key differs (keys are sorted)
+    uint32_t base = 0;
+    if (lane == 0) {
+      long long lo = p + kLongRun, hi = n;          // keys[lo] == k is known; answer in (lo, n]
+      while (lo + 1 < hi) {
+        const long long mid = (lo + hi) >> 1;
+        if (keys[mid] == k) lo = mid; else hi = mid;
+      }
+      len = hi - p;
+      const uint32_t nch = (uint32_t)((len + kRunChunk - 1) / kRunChunk);
+      const uint32_t r = atomicAdd(&counters[0], 1u);
+      base = atomicAdd(&counters[1], nch);
+      runs[r] = LongRun{(uint32_t)p, (uint32_t)len, k, base};
+    }
+    len = __shfl_sync(0xffffffffu, len, 0);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    const uint32_t nch = (uint32_t)((len + kRunChunk - 1) / kRunChunk);
+    for (uint32_t jc = lane; jc < nch; jc += 32) {
+      const long long off = (long long)jc * kRunChunk;
+      chunks[base + jc] = ChunkDesc{(uint32_t)(p + off), (uint32_t)min((long long)kRunChunk, len - off)};
+    }
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+long_chunk_sum_kernel(int dim, const uint32_t* __restrict__ vals, const float* __restrict__ rows, float scale,
+                      const ChunkDesc* __restrict__ chunks, const uint32_t* __restrict__ counters,
+                      float* __restrict__ carry) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t n_chunks = counters[1];
+  const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+  for (uint32_t slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); slot < n_chunks; slot += warps) {
+    const ChunkDesc d = chunks[slot];
+    for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {
+      const int c = c0 + lane * VEC;
+      float acc[VEC];
+#pragma unroll
+      for (int u = 0; u < VEC; ++u) acc[u] = 0.f;
+      for (uint32_t i0 = 0; i0 < d.len; i0 += 8) {       // 8 independent row loads in flight
+        float gv[8][VEC];
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (i0 + t < d.len && c < dim) load_vec<VEC>(rows + (long long)vals[d.pos + i0 + t] * dim + c, gv[t]);
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (i0 + t < d.len && c < dim) {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) acc[u] = __fadd_rn(acc[u], __fmul_rn(scale, gv[t][u]));
+          }
+      }
+      if (c < dim) store_vec<VEC>(carry + (long long)slot * dim + c, acc);
+    }
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+long_run_apply_kernel(float* __restrict__ table, int dim, const LongRun* __restrict__ runs,
+                      const uint32_t* __restrict__ counters, const float* __restrict__ carry) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t n_runs = counters[0];
+  const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+  for (uint32_t r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_runs; r += warps) {
+    const LongRun run = runs[r];
+    const uint32_t nch = (run.len + kRunChunk - 1) / kRunChunk;
+    float* trow = table + (long long)run.key * dim;
+    for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {
+      const int c = c0 + lane * VEC;
+      float acc[VEC];
+      if (c < dim) load_vec<VEC>(trow + c, acc);
+      for (uint32_t j0 = 0; j0 < nch; j0 += 8) {
+        float cv[8][VEC];
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (j0 + t < nch && c < dim) load_vec<VEC>(carry + (long long)(run.chunk_base + j0 + t) * dim + c, cv[t]);
+#pragma unroll
+        for (int t = 0; t < 8; ++t)
+          if (j0 + t < nch && c < dim) {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) acc[u] = __fsub_rn(acc[u], cv[t][u]);
+          }
+      }
+      if (c < dim) store_vec<VEC>(trow + c, acc);
+    }
+  }
+}
+
 static int bits_for(uint32_t v) {
   int b = 0;
   while (b < 32 && (v >> b) != 0) ++b;
@@ -309,6 +471,21 @@ size_t tfg_sparse_scratch_bytes(int64_t n) {
   return 4 * arr + ((nb * 256 * 4 + 255) / 256 * 256) + 256;
 }
 
+// scratch for the chunk-parallel treatment of long runs, on top of tfg_sparse_scratch_bytes(n)
+static size_t long_run_extra_bytes(int64_t n, int dim, size_t* max_runs, size_t* max_chunks) {
+  const size_t runs = (size_t)(n / (kLongRun + 1)) + 1;
+  const size_t chunks = (size_t)(n / kRunChunk) + runs + 1;
+  if (max_runs) *max_runs = runs;
+  if (max_chunks) *max_chunks = chunks;
+  auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+  return 256 + up(runs * sizeof(LongRun)) + up(chunks * sizeof(ChunkDesc)) + up(chunks * (size_t)dim * sizeof(float));
+}
+
+size_t tfg_sparse_scratch_bytes_fast(int64_t n, int dim) {
+  if (n < 0 || dim < 1) return 0;
+  return tfg_sparse_scratch_bytes(n) + long_run_extra_bytes(n, dim, nullptr, nullptr);
+}
+
 int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
                            const int64_t* ids, int64_t n, const float* rows, float scale,
                            void* scratch, size_t scratch_bytes, void* stream) {
@@ -344,7 +521,32 @@ int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, i
   }
   long long blocks = (n + 7) / 8;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  if ((dim & 3) == 0)
+  const size_t base_bytes = tfg_sparse_scratch_bytes(n);
+  size_t max_runs = 0, max_chunks = 0;
+  const size_t extra = long_run_extra_bytes(n, dim, &max_runs, &max_chunks);
+  if (scratch_bytes >= base_bytes + extra) {
+    // enough scratch: long runs go through the chunk-parallel kernels
+    auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+    char* x = base + base_bytes;
+    uint32_t* counters = (uint32_t*)x;                       x += 256;
+    LongRun* runs = (LongRun*)x;                             x += up(max_runs * sizeof(LongRun));
+    ChunkDesc* chunks = (ChunkDesc*)x;                       x += up(max_chunks * sizeof(ChunkDesc));
+    float* carry = (float*)x;
+    cudaError_t em = cudaMemsetAsync(counters, 0, 8, s);     // the two counters must start at zero
+    if (em != cudaSuccess) return fail_cuda(nullptr, em, "cudaMemsetAsync(counters)");
+    const int gl = kNumSMs * 8;
+    if ((dim & 3) == 0) {
+      scatter_sub_heads_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel, rows,
+                                                              scale, runs, chunks, counters);
+      long_chunk_sum_kernel<4><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
+      long_run_apply_kernel<4><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
+    } else {
+      scatter_sub_heads_kernel<1><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel, rows,
+                                                              scale, runs, chunks, counters);
+      long_chunk_sum_kernel<1><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
+      long_run_apply_kernel<1><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
+    }
+  } else if ((dim & 3) == 0)
     scatter_sub_runs_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel,
                                                            rows, scale);
   else
@@ -386,8 +588,11 @@ int tfg_sparse_scatter_sub_static(float* table, int64_t vocab, int dim, int n_sh
     if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetSymbolAddress(g_static_scratch)");
     g_static_scratch_addr[dev] = scratch;
   }
+  // Hand over exactly the sort scratch this n needs: every duplicate is then applied in order,
+  // whatever n is (with more scratch tfg_sparse_scatter_sub would switch long runs to its
+  // chunk-parallel path, which rounds differently).
   return tfg_sparse_scatter_sub(table, vocab, dim, n_shards, shard, strategy, ids, n, rows, scale, scratch,
-                                TFG_SPARSE_STATIC_SCRATCH_BYTES, stream);
+                                tfg_sparse_scratch_bytes(n), stream);
 }
 
 }  // extern "C"

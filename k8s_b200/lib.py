@@ -91,6 +91,7 @@ _SIGS = {
     "tfg_sparse_gather": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
                                     C.c_int64, _p, _p, _p]),
     "tfg_sparse_scratch_bytes": (C.c_size_t, [C.c_int64]),
+    "tfg_sparse_scratch_bytes_fast": (C.c_size_t, [C.c_int64, C.c_int]),
     "tfg_sparse_scatter_sub": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
                                          C.c_int64, _p, C.c_float, _p, C.c_size_t, _p]),
     "tfg_sparse_scatter_sub_static": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,

@@ -80,7 +80,7 @@ def main():
                 ids = torch.from_numpy(ids_np).cuda()
                 rows = torch.randn(B, D, device="cuda")
                 outb = torch.empty(B, D, device="cuda")
-                scratch = torch.empty(lib.sparse_scratch_bytes(B), dtype=torch.uint8, device="cuda")
+                scratch = torch.empty(lib.sparse_scratch_bytes_fast(B, D), dtype=torch.uint8, device="cuda")
                 s = stream.cuda_stream
                 ms_g = timed(lambda: lib.check(lib.sparse_gather(table.data_ptr(), V, D, 1, 0, L.PART_MOD, ids.data_ptr(),
                                                                  B, outb.data_ptr(), None, s)), stream)

@@ -57,6 +57,43 @@ def test_gather_and_scatter_sub_bit_exact(lib, strategy, vocab, dim, n_shards, n
     assert not np.isnan(out_cpu).any() and int(bad.item()) == 0
 
 
+@pytest.mark.parametrize("vocab,dim,n,dist", [(1000, 64, 20000, "zipf"), (300, 33, 5000, "one"), (5000, 128, 65536, "zipf"),
+                                              (100000, 128, 200000, "uniform")])
+def test_scatter_sub_chunk_parallel_long_runs(lib, vocab, dim, n, dist):
+    """With tfg_sparse_scratch_bytes_fast() of scratch, rows hit by more than 64 ids are summed
+    chunk-parallel.  Rows hit <= 64 times stay bit-exact with the sequential oracle; the others
+    must be deterministic and as accurate as the oracle is (both measured against float64)."""
+    rng = np.random.default_rng(vocab + n)
+    ids = make_ids(rng, vocab, n, dist)
+    grads = rng.standard_normal((n, dim)).astype(np.float32)
+    table0 = rng.standard_normal((vocab, dim)).astype(np.float32)
+    want = table0.copy()
+    O.sparse_scatter_sub(want, vocab, 1, 0, O.MOD, ids, grads, 0.05)
+    exact = table0.astype(np.float64)
+    np.subtract.at(exact, ids, (np.float32(0.05) * grads).astype(np.float64))
+    d_ids, d_grads = dev(ids), dev(grads)
+    scratch = torch.empty(lib.sparse_scratch_bytes_fast(n, dim), dtype=torch.uint8, device="cuda")
+    assert scratch.numel() > lib.sparse_scratch_bytes(n)
+    outs = []
+    for rep in range(2):
+        d_table = dev(table0)
+        lib.check(lib.sparse_scatter_sub(d_table.data_ptr(), vocab, dim, 1, 0, L.PART_MOD, d_ids.data_ptr(), n,
+                                         d_grads.data_ptr(), 0.05, scratch.data_ptr(), scratch.numel(), 0))
+        torch.cuda.synchronize()
+        outs.append(d_table.cpu().numpy())
+    np.testing.assert_array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))      # deterministic
+    mult = np.bincount(ids, minlength=vocab)
+    short, long_ = mult <= 64, mult > 64
+    np.testing.assert_array_equal(outs[0][short].view(np.uint32), want[short].view(np.uint32))
+    if dist != "uniform":
+        assert long_.any()
+    if long_.any():
+        err_gpu = np.abs(outs[0][long_] - exact[long_]).max(axis=1)
+        err_seq = np.abs(want[long_] - exact[long_]).max(axis=1)
+        scale = np.abs(exact[long_]).max(axis=1) + 1.0
+        assert np.all(err_gpu <= 2.0 * err_seq + 4e-7 * scale), (err_gpu.max(), err_seq.max())
+
+
 def test_out_of_range_ids_are_counted_and_skipped(lib):
     vocab, dim = 100, 16
     ids = np.array([5, -1, 100, 99, 1 << 40, 5], dtype=np.int64)
