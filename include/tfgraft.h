@@ -122,6 +122,10 @@ int tfg_var_register(tfg_job* job, const char* name, const char* op_type, int dt
                      const int64_t* shape, int rank, int trainable,
                      int* var_out, int* ps_task_out);
 int tfg_num_vars(const tfg_job* job);
+/* name (NUL-terminated, truncated to name_cap), shape (up to 8 dims), rank and trainable flag
+ * of a registered variable -- what a model-building host needs to seed weights by name. */
+int tfg_var_info(const tfg_job* job, int var, char* name_out, size_t name_cap, int64_t* shape_out,
+                 int* rank_out, int* trainable_out);
 /* allocate the flat parameter / gradient / slot buffers in HBM for the registered
  * trainable fp32 variables.  After this no variable can be registered. */
 int tfg_vars_finalize(tfg_job* job, int layout);
@@ -241,6 +245,19 @@ int tfg_sparse_scatter_sub_static(float* table_dev, int64_t vocab, int dim, int 
  * W_fc2,b_fc2,global_step in that creation order and allocates activations for
  * batch_per_replica examples per local replica. */
 int tfg_model_mnist_cnn(tfg_job* job, int batch_per_replica, int math);
+/* ResNet-50 v1.5 for BASELINE config 4 (tf_cnn_benchmarks-style synthetic ImageNet): bf16
+ * activations and operands on the tcgen05 path, fp32 master weights, batch-norm with batch
+ * statistics.  image_hw: input height = width, a multiple of 32 (224 for ImageNet); classes a
+ * multiple of 8 (1000).  Registers conv / bn / fc variables in creation order (moving
+ * statistics included, as non-trainable PS ops) and allocates one replica's activations per
+ * local slot.  Inputs of tfg_forward_backward / tfg_step_dense are then images
+ * [B,image_hw,image_hw,3] fp32 NHWC and labels [B] int32.  The model is build-defined: the
+ * reference tree holds no model code (SURVEY.md par. 0.2). */
+int tfg_model_resnet50(tfg_job* job, int batch_per_replica, int image_hw, int classes);
+/* Host copy (fp32) of an activation of the last forward of `slot`, by name ("conv1/z",
+ * "stage2/block1/c/y", "pool1", ...), or of its gradient with a "grad:" prefix; parity tests. */
+int tfg_tensor_get(tfg_job* job, int slot, const char* name, float* host, size_t cap_floats, size_t* n_out);
+
 /* forward + backward of local replica `slot` on device-resident inputs:
  * images [B,28,28,1] fp32 NHWC, labels [B] int32.  Gradients land in the replica's
  * gradient buffer, the mean loss in the job's loss buffer. */

@@ -178,7 +178,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
       if (g != j->gpu_rank) a.pull[a.n_pull++] = j->peer_params[g];
     if (j->params_lp)
       for (int g = 0; g < j->n_gpus; ++g) a.lp[a.n_lp++] = static_cast<__nv_bfloat16*>(j->peer_params_lp[g]);
-    a.n_loss = j->model ? j->n_replicas : 0;
+    a.n_loss = (j->model || j->resnet) ? j->n_replicas : 0;
     for (int r = 0; r < a.n_loss; ++r) a.loss_src[r] = j->peer_loss[r % j->n_gpus] + r;
   }
   a.loss_dst = j->loss + TFG_MAX_REPLICAS;

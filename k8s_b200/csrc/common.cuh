@@ -35,6 +35,7 @@ struct Segment {         // a range of the flat space whose update this rank app
 };
 
 struct MnistModel;       // model_mnist.cu
+struct ResnetModel;      // resnet.cu
 
 }  // namespace tfg
 
@@ -80,6 +81,7 @@ struct tfg_job {
   int64_t global_step = 0;
   // model
   tfg::MnistModel* model = nullptr;
+  tfg::ResnetModel* resnet = nullptr;
   int64_t launches = 0;
   // optional per-kernel timing: one event after every launch (see prof_mark)
   bool prof_on = false;
@@ -126,6 +128,16 @@ int mnist_build(tfg_job* j, int batch, int math);
 void mnist_destroy(tfg_job* j);
 int mnist_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels);
 int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes);
+// resnet.cu
+int resnet_build(tfg_job* j, int batch, int image_hw, int classes);
+void resnet_destroy(tfg_job* j);
+int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels);
+int resnet_logits(tfg_job* j, int slot, float* host, size_t bytes);
+int resnet_batch(const tfg_job* j);
+size_t resnet_image_floats(const tfg_job* j);
+float* resnet_stage_images(tfg_job* j, int slot);
+int32_t* resnet_stage_labels(tfg_job* j, int slot);
+int resnet_tensor_get(tfg_job* j, int slot, const char* name, float* host, size_t cap_floats, size_t* n_out);
 int mnist_batch(const tfg_job* j);
 int mnist_math(const tfg_job* j);
 int launch_cast_bf16(const float* src, void* dst, long long n, cudaStream_t s);   // apply.cu

@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "gemm_tc.cuh"
 #include "model_mnist.cuh"
+#include "tc_host.cuh"
 
 namespace tfg {
 
@@ -27,8 +28,8 @@ static PFN_cuTensorMapEncodeTiled get_encode() {
 
 // Operand with `rows` (M or N) and `cols` (K).  K-major: stored [rows, K], pitch ld, box = 128 B
 // of K x box_rows.  MN-major: stored [K, rows], pitch ld, box = 128 B of rows x one stage of K.
-static int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t cols, int64_t ld,
-                    int box_rows, bool mn_major = false) {
+int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t cols, int64_t ld,
+             int box_rows, bool mn_major) {
   PFN_cuTensorMapEncodeTiled enc = get_encode();
   if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
   const int esize = kind == TFG_MATH_BF16 ? 2 : 4;
@@ -52,16 +53,6 @@ static int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, i
     return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
   return TFG_OK;
 }
-
-struct TcGemm {
-  CUtensorMap a, b;
-  float* C = nullptr;          // [M, ldc]
-  float* partial = nullptr;    // [splits][M][N] when splits > 1
-  int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
-  bool a_mn = false, b_mn = false;
-  tc::Epilogue epi = {nullptr, nullptr, 0};
-  const char* name = "gemm";
-};
 
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, long long mn,
@@ -110,7 +101,7 @@ static cudaError_t launch_major(const TcGemm& g, float* dst, int ldc, int k_bloc
 }
 
 // j may be NULL (stateless test entry point)
-static int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
+int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
   const int block_k = tc::kBlockKBytes / (kind == TFG_MATH_BF16 ? 2 : 4);
   const int k_blocks = (g.K + block_k - 1) / block_k;
   int splits = std::max(1, std::min(g.splits, k_blocks));
@@ -118,7 +109,8 @@ static int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
   splits = (k_blocks + kps - 1) / kps;                 // no empty split
   float* dst = splits > 1 ? g.partial : g.C;
   const int ldc = splits > 1 ? g.N : g.ldc;
-  tc::Epilogue epi = splits > 1 ? tc::Epilogue{nullptr, nullptr, 0} : g.epi;
+  tc::Epilogue epi = splits > 1 ? tc::Epilogue{nullptr, nullptr, 0, nullptr} : g.epi;
+  if (splits > 1 && g.epi.out_bf16) return fail(j, TFG_EINVAL, "split-K writes fp32 only");
   if (splits > 1 && (!g.partial || g.ldc != g.N))
     return fail(j, TFG_EINVAL, "split-K needs a partial buffer and a dense output");
   cudaError_t e;
@@ -307,17 +299,17 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
     return make_map(&g.b, kind, Bp, N, K, ldb, block_n, b_mn);
   };
   if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, w2, 64, true, s.y2, 64, 1,
-               tc::Epilogue{par(3), nullptr, 0}))) return rc;
+               tc::Epilogue{par(3), nullptr, 0, nullptr}))) return rc;
   if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, a2, 3136, false, w3, 1024, true, s.h1, 64,
-               kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1}))) return rc;
+               kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1, nullptr}))) return rc;
   if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, a2, 3136, true, dh1, 1024, true, grd(4),
-               128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr}))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
-               64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+               64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr}))) return rc;
   if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
-               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr}))) return rc;
   if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
-               128, 1, tc::Epilogue{nullptr, nullptr, 0}))) return rc;
+               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr}))) return rc;
   return TFG_OK;
 }
 
@@ -376,7 +368,7 @@ extern "C" int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const vo
   g.M = M; g.N = N; g.K = K; g.C = c_dev; g.ldc = N; g.block_n = block_n; g.splits = splits < 1 ? 1 : splits;
   g.partial = partial_dev;
   g.a_mn = a_mn_major != 0; g.b_mn = b_mn_major != 0;
-  g.epi = tc::Epilogue{bias_dev, nullptr, relu};
+  g.epi = tc::Epilogue{bias_dev, nullptr, relu, nullptr};
   int rc = make_map(&g.a, math, a_dev, M, K, lda, tc::kBlockM, g.a_mn);
   if (rc) return rc;
   if ((rc = make_map(&g.b, math, b_dev, N, K, ldb, block_n, g.b_mn))) return rc;

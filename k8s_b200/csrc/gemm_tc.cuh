@@ -16,6 +16,7 @@
 // warps 2..5 = epilogue (warp w owns TMEM lanes 32*(w%4) .. +31).
 #pragma once
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -32,6 +33,7 @@ struct Epilogue {
   const float* bias;    // [N] added to every row, or NULL
   const float* mask;    // [M, ldc]: keep the value where mask > 0, else 0; or NULL
   int relu;
+  void* out_bf16;       // when set, the result is stored as bf16 [M, ldc] here instead of fp32 in C
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -292,7 +294,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             v.x = k.x > 0.f ? v.x : 0.f; v.y = k.y > 0.f ? v.y : 0.f;
             v.z = k.z > 0.f ? v.z : 0.f; v.w = k.w > 0.f ? v.w : 0.f;
           }
-          *reinterpret_cast<float4*>(dst) = v;
+          if (epi.out_bf16) {
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(epi.out_bf16) +
+                                      (static_cast<size_t>(blockIdx.z) * M + row) * static_cast<size_t>(ldc) + col) = pk;
+          } else {
+            *reinterpret_cast<float4*>(dst) = v;
+          }
         } else {
           const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -302,7 +313,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             if (epi.bias) x += epi.bias[col + u];
             if (epi.relu) x = fmaxf(x, 0.f);
             if (epi.mask) x = epi.mask[static_cast<size_t>(row) * ldc + col + u] > 0.f ? x : 0.f;
-            dst[u] = x;
+            if (epi.out_bf16)
+              static_cast<__nv_bfloat16*>(epi.out_bf16)[(static_cast<size_t>(blockIdx.z) * M + row) *
+                                                            static_cast<size_t>(ldc) + col + u] = __float2bfloat16_rn(x);
+            else
+              dst[u] = x;
           }
         }
       }

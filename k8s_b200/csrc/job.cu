@@ -168,6 +168,7 @@ int tfg_job_destroy(tfg_job* j) {
     cudaSetDevice(j->device);
     cudaStreamSynchronize(j->stream);
     mnist_destroy(j);
+    resnet_destroy(j);
     for (auto& pe : j->prof_ev) cudaEventDestroy(pe.second);
     for (void* p : j->ipc_opened) cudaIpcCloseMemHandle(p);
     cudaFree(j->params);
@@ -318,6 +319,22 @@ int tfg_var_register(tfg_job* j, const char* name, const char* op_type, int dtyp
 
 int tfg_num_vars(const tfg_job* j) { return j ? (int)j->vars.size() : -1; }
 
+int tfg_var_info(const tfg_job* j, int var, char* name_out, size_t name_cap, int64_t* shape_out, int* rank_out,
+                 int* trainable_out) {
+  if (!j || var < 0 || var >= (int)j->vars.size()) return fail(nullptr, TFG_EINVAL, "bad variable index");
+  const VarInfo& v = j->vars[var];
+  if (name_out && name_cap) {
+    const size_t n = std::min(name_cap - 1, v.name.size());
+    memcpy(name_out, v.name.data(), n);
+    name_out[n] = 0;
+  }
+  if (rank_out) *rank_out = (int)v.shape.size();
+  if (shape_out)
+    for (size_t i = 0; i < v.shape.size() && i < 8; ++i) shape_out[i] = v.shape[i];
+  if (trainable_out) *trainable_out = (v.trainable && v.dtype == TFG_DT_F32) ? 1 : 0;
+  return TFG_OK;
+}
+
 int tfg_vars_finalize(tfg_job* j, int layout) {
   if (!j) return fail(nullptr, TFG_EINVAL, "job is NULL");
   if (j->finalized) return fail(j, TFG_ESTATE, "variables are already finalized");
@@ -348,7 +365,7 @@ int tfg_vars_finalize(tfg_job* j, int layout) {
     j->peer_grads[j->local_replicas[s]] = g;
   }
   j->peer_params[j->gpu_rank] = j->params;
-  if (j->model && mnist_math(j) == TFG_MATH_BF16) {
+  if ((j->model && mnist_math(j) == TFG_MATH_BF16) || j->resnet) {
     TFG_CUDA(j, cudaMalloc(&j->params_lp, bytes / 2));
     TFG_CUDA(j, cudaMemsetAsync(j->params_lp, 0, bytes / 2, j->stream));
     j->peer_params_lp[j->gpu_rank] = j->params_lp;
@@ -606,9 +623,38 @@ int tfg_dense_apply(int kind, float* var, float* accum, const float* const* grad
 }
 
 // ---- model + step --------------------------------------------------------------------
+static bool has_model(const tfg_job* j) { return j->model || j->resnet; }
+static int model_fb(tfg_job* j, int slot, const float* x, const int32_t* y) {
+  return j->resnet ? resnet_forward_backward(j, slot, x, y) : mnist_forward_backward(j, slot, x, y);
+}
+static int model_batch(const tfg_job* j) { return j->resnet ? resnet_batch(j) : mnist_batch(j); }
+static size_t model_image_floats(const tfg_job* j) { return j->resnet ? resnet_image_floats(j) : 784; }
+static float* model_stage_images(tfg_job* j, int s) { return j->resnet ? resnet_stage_images(j, s) : mnist_stage_images(j, s); }
+static int32_t* model_stage_labels(tfg_job* j, int s) { return j->resnet ? resnet_stage_labels(j, s) : mnist_stage_labels(j, s); }
+
+int tfg_model_resnet50(tfg_job* j, int batch, int image_hw, int classes) {
+  if (!j) return fail(nullptr, TFG_EINVAL, "job is NULL");
+  if (has_model(j)) return fail(j, TFG_ESTATE, "a model is already built");
+  if (j->finalized) return fail(j, TFG_ESTATE, "variables are already finalized");
+  if (batch < 1 || batch > 4096) return fail(j, TFG_EINVAL, "batch_per_replica out of range");
+  if (image_hw < 32 || image_hw % 32 != 0 || image_hw > 512)
+    return fail(j, TFG_EINVAL, "image size must be a multiple of 32 in [32, 512]");
+  if (classes < 2 || classes % 8 != 0) return fail(j, TFG_EINVAL, "classes must be a multiple of 8");
+  int rc = ensure_bound(j);
+  if (rc) return rc;
+  return resnet_build(j, batch, image_hw, classes);
+}
+
+int tfg_tensor_get(tfg_job* j, int slot, const char* name, float* host, size_t cap_floats, size_t* n_out) {
+  if (!j || !j->resnet) return fail(j, TFG_ESTATE, "no ResNet model is built");
+  if (slot < 0 || slot >= (int)j->grads.size() || !name || !host) return fail(j, TFG_EINVAL, "bad argument");
+  TFG_CUDA(j, cudaSetDevice(j->device));
+  return resnet_tensor_get(j, slot, name, host, cap_floats, n_out);
+}
+
 int tfg_model_mnist_cnn(tfg_job* j, int batch, int math) {
   if (!j) return fail(nullptr, TFG_EINVAL, "job is NULL");
-  if (j->model) return fail(j, TFG_ESTATE, "a model is already built");
+  if (has_model(j)) return fail(j, TFG_ESTATE, "a model is already built");
   if (j->finalized) return fail(j, TFG_ESTATE, "variables are already finalized");
   if (batch < 1 || batch > 65536) return fail(j, TFG_EINVAL, "batch_per_replica out of range");
   if (math != TFG_MATH_FP32 && math != TFG_MATH_BF16 && math != TFG_MATH_TF32)
@@ -619,19 +665,19 @@ int tfg_model_mnist_cnn(tfg_job* j, int batch, int math) {
 }
 
 int tfg_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels) {
-  if (!j || !j->model) return fail(j, TFG_ESTATE, "no model is built");
+  if (!j || !has_model(j)) return fail(j, TFG_ESTATE, "no model is built");
   if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   if (slot < 0 || slot >= (int)j->grads.size()) return fail(j, TFG_EINVAL, "bad replica slot");
   if (!images || !labels) return fail(j, TFG_EINVAL, "NULL input");
   TFG_CUDA(j, cudaSetDevice(j->device));
-  return mnist_forward_backward(j, slot, images, labels);
+  return model_fb(j, slot, images, labels);
 }
 
 int tfg_logits_get(tfg_job* j, int slot, float* host, size_t bytes) {
-  if (!j || !j->model) return fail(j, TFG_ESTATE, "no model is built");
+  if (!j || !has_model(j)) return fail(j, TFG_ESTATE, "no model is built");
   if (slot < 0 || slot >= (int)j->grads.size()) return fail(j, TFG_EINVAL, "bad replica slot");
   TFG_CUDA(j, cudaSetDevice(j->device));
-  return mnist_logits(j, slot, host, bytes);
+  return j->resnet ? resnet_logits(j, slot, host, bytes) : mnist_logits(j, slot, host, bytes);
 }
 
 // Device work of one step: forward/backward of every hosted replica, then barrier, fused
@@ -639,7 +685,7 @@ int tfg_logits_get(tfg_job* j, int slot, float* host, size_t bytes) {
 static int step_device_work(tfg_job* j, const float* const* images, const int32_t* const* labels) {
   int rc;
   for (size_t s = 0; s < j->grads.size(); ++s)
-    if ((rc = mnist_forward_backward(j, (int)s, images[s], labels[s]))) return rc;
+    if ((rc = model_fb(j, (int)s, images[s], labels[s]))) return rc;
   if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
   if ((rc = launch_job_apply(j, false, j->n_replicas))) return rc;
   if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
@@ -705,7 +751,7 @@ static int step_finish(tfg_job* j, float* loss_out) {
 
 int tfg_step_dense_dev(tfg_job* j, const float* const* images, const int32_t* const* labels,
                        float* loss_out) {
-  if (!j || !j->model) return fail(j, TFG_ESTATE, "no model is built");
+  if (!j || !has_model(j)) return fail(j, TFG_ESTATE, "no model is built");
   if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   if (!images || !labels) return fail(j, TFG_EINVAL, "NULL input");
   TFG_CUDA(j, cudaSetDevice(j->device));
@@ -718,18 +764,19 @@ int tfg_step_dense_dev(tfg_job* j, const float* const* images, const int32_t* co
 
 int tfg_step_dense(tfg_job* j, const float* const* images_host, const int32_t* const* labels_host,
                    float* loss_out) {
-  if (!j || !j->model) return fail(j, TFG_ESTATE, "no model is built");
+  if (!j || !has_model(j)) return fail(j, TFG_ESTATE, "no model is built");
   if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
   if (!images_host || !labels_host || !loss_out) return fail(j, TFG_EINVAL, "NULL argument");
   TFG_CUDA(j, cudaSetDevice(j->device));
-  const int B = mnist_batch(j);
+  const int B = model_batch(j);
+  const size_t img = model_image_floats(j);
   std::vector<const float*> di(j->grads.size());
   std::vector<const int32_t*> dl(j->grads.size());
   for (size_t s = 0; s < j->grads.size(); ++s) {
     if (!images_host[s] || !labels_host[s]) return fail(j, TFG_EINVAL, "NULL input for a replica slot");
-    di[s] = mnist_stage_images(j, (int)s);
-    dl[s] = mnist_stage_labels(j, (int)s);
-    TFG_CUDA(j, cudaMemcpyAsync(const_cast<float*>(di[s]), images_host[s], sizeof(float) * 784 * (size_t)B,
+    di[s] = model_stage_images(j, (int)s);
+    dl[s] = model_stage_labels(j, (int)s);
+    TFG_CUDA(j, cudaMemcpyAsync(const_cast<float*>(di[s]), images_host[s], sizeof(float) * img * (size_t)B,
                                 cudaMemcpyHostToDevice, j->stream));
     TFG_CUDA(j, cudaMemcpyAsync(const_cast<int32_t*>(dl[s]), labels_host[s], sizeof(int32_t) * (size_t)B,
                                 cudaMemcpyHostToDevice, j->stream));

@@ -1,0 +1,355 @@
+// HBM-bound kernels around the contractions of the ResNet-50 step (BASELINE config 4):
+// im2col / col2im for NHWC bf16 activations, batch-norm statistics and apply (forward and
+// backward), 3x3/2 max-pool, global average pool, 1000-way softmax cross-entropy.
+// Activations and their gradients are bf16; statistics, reductions and parameters fp32.
+// Every reduction runs in a fixed order (two-stage, no floating-point atomics).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tfg {
+namespace rn {
+
+typedef __nv_bfloat16 bf16;
+
+struct ConvGeom {
+  int N, H, W, C;        // input
+  int R, S, stride, pad;
+  int OH, OW;
+  int Kp;                // R*S*C rounded up to a multiple of 8 (16-byte row pitch for TMA)
+};
+
+__device__ __forceinline__ float b2f(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ bf16 f2b(float v) { return __float2bfloat16_rn(v); }
+
+// images fp32 NHWC -> bf16
+__global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = f2b(src[i]);
+}
+
+// ---- im2col: in[N,H,W,C] -> col[N*OH*OW, Kp], k = (r*S + s)*C + c ---------------------------
+// VEC = 8 channels (16 B) per thread when C % 8 == 0, else 1.
+template <int VEC>
+__global__ void __launch_bounds__(256)
+im2col_kernel(const bf16* __restrict__ in, bf16* __restrict__ col, ConvGeom g) {
+  const int cv = g.C / VEC;
+  const long long M = (long long)g.N * g.OH * g.OW;
+  const long long total = M * g.R * g.S * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv) * VEC;
+    long long t = i / cv;
+    const int s = (int)(t % g.S); t /= g.S;
+    const int r = (int)(t % g.R); t /= g.R;
+    const long long m = t;
+    const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH);
+    const long long n = m / ((long long)g.OW * g.OH);
+    const int ih = oh * g.stride + r - g.pad, iw = ow * g.stride + s - g.pad;
+    const bool ok = ih >= 0 && ih < g.H && iw >= 0 && iw < g.W;
+    bf16* dst = col + m * g.Kp + (r * g.S + s) * g.C + c;
+    const bf16* src = in + ((n * g.H + ih) * g.W + iw) * g.C + c;
+    if (VEC == 8) {
+      *reinterpret_cast<uint4*>(dst) = ok ? *reinterpret_cast<const uint4*>(src) : make_uint4(0, 0, 0, 0);
+    } else {
+      dst[0] = ok ? src[0] : f2b(0.f);
+    }
+  }
+}
+
+// zero the pad columns [R*S*C, Kp) of col (only the stem has any)
+__global__ void __launch_bounds__(256) zero_pad_cols_kernel(bf16* __restrict__ col, long long M, int K, int Kp) {
+  const int padw = Kp - K;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < M * padw; i += (long long)gridDim.x * blockDim.x)
+    col[(i / padw) * Kp + K + (i % padw)] = f2b(0.f);
+}
+
+// ---- col2im (gather form): din[n,h,w,c] (+)= sum over taps of dcol[(n,oh,ow), (r*S+s)*C + c] ---
+template <int VEC>
+__global__ void __launch_bounds__(256)
+col2im_kernel(const bf16* __restrict__ dcol, bf16* __restrict__ din, ConvGeom g, int accumulate) {
+  const int cv = g.C / VEC;
+  const long long total = (long long)g.N * g.H * g.W * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv) * VEC;
+    const long long pix = i / cv;
+    const int w = (int)(pix % g.W), h = (int)((pix / g.W) % g.H);
+    const long long n = pix / ((long long)g.W * g.H);
+    float acc[VEC];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) acc[u] = 0.f;
+    for (int r = 0; r < g.R; ++r) {
+      const int th = h + g.pad - r;
+      if (th < 0 || th % g.stride) continue;
+      const int oh = th / g.stride;
+      if (oh >= g.OH) continue;
+      for (int s = 0; s < g.S; ++s) {
+        const int tw = w + g.pad - s;
+        if (tw < 0 || tw % g.stride) continue;
+        const int ow = tw / g.stride;
+        if (ow >= g.OW) continue;
+        const bf16* src = dcol + ((n * g.OH + oh) * g.OW + ow) * g.Kp + (r * g.S + s) * g.C + c;
+        if (VEC == 8) {
+          const uint4 v = *reinterpret_cast<const uint4*>(src);
+          const bf16* e = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+          for (int u = 0; u < VEC; ++u) acc[u] += b2f(e[u]);
+        } else {
+          acc[0] += b2f(src[0]);
+        }
+      }
+    }
+    bf16* dst = din + pix * g.C + c;
+    if (accumulate) {
+#pragma unroll
+      for (int u = 0; u < VEC; ++u) acc[u] += b2f(dst[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) dst[u] = f2b(acc[u]);
+  }
+}
+
+// dst (+)= src, bf16
+__global__ void __launch_bounds__(256)
+add_bf16_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long n, int accumulate) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = accumulate ? f2b(b2f(dst[i]) + b2f(src[i])) : src[i];
+}
+
+// ---- batch norm ----------------------------------------------------------------------------
+// stage 1 of per-channel sums over rows: partial[chunk][2][C] = (sum x, sum x^2) for forward,
+// (sum dy, sum dy * xhat) for backward.  block = 64 channels x 4 row lanes.
+__global__ void __launch_bounds__(256)
+bn_stats_kernel(const bf16* __restrict__ z, float* __restrict__ partial, long long M, int C, int rows_per_chunk) {
+  __shared__ float r1[4][64], r2[4][64];
+  const int cx = threadIdx.x & 63, ry = threadIdx.x >> 6;
+  const int c = blockIdx.x * 64 + cx;
+  const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
+  float s = 0.f, q = 0.f;
+  if (c < C)
+    for (long long r = r0 + ry; r < rend; r += 4) {
+      const float v = b2f(z[r * C + c]);
+      s += v;
+      q = fmaf(v, v, q);
+    }
+  r1[ry][cx] = s; r2[ry][cx] = q;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = ((r1[0][cx] + r1[1][cx]) + r1[2][cx]) + r1[3][cx];
+    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = ((r2[0][cx] + r2[1][cx]) + r2[2][cx]) + r2[3][cx];
+  }
+}
+
+// stage 2 forward: mean, invstd (biased variance, eps), moving statistics update
+__global__ void __launch_bounds__(256)
+bn_finalize_kernel(const float* __restrict__ partial, int chunks, int C, long long M, float eps, float decay,
+                   float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ mov_mean,
+                   float* __restrict__ mov_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f, q = 0.f;
+  for (int k = 0; k < chunks; ++k) { s += partial[((size_t)k * 2) * C + c]; q += partial[((size_t)k * 2 + 1) * C + c]; }
+  const float mu = s / (float)M;
+  const float var = fmaxf(q / (float)M - mu * mu, 0.f);
+  mean[c] = mu;
+  invstd[c] = rsqrtf(var + eps);
+  if (mov_mean) {
+    mov_mean[c] = decay * mov_mean[c] + (1.f - decay) * mu;
+    mov_var[c] = decay * mov_var[c] + (1.f - decay) * var * ((float)M / (float)max(M - 1, 1ll));
+  }
+}
+
+// y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ invstd,
+                const float* __restrict__ gamma, const float* __restrict__ beta, const bf16* __restrict__ residual,
+                bf16* __restrict__ y, long long total, int C, int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    float v = gamma[c] * (b2f(z[i]) - mean[c]) * invstd[c] + beta[c];
+    if (residual) v += b2f(residual[i]);
+    if (relu) v = fmaxf(v, 0.f);
+    y[i] = f2b(v);
+  }
+}
+
+// backward stage 1: partial[chunk][2][C] = (sum g, sum g * xhat), g = dy masked by y > 0 when relu
+__global__ void __launch_bounds__(256)
+bn_bwd_stats_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ partial,
+                    long long M, int C, int rows_per_chunk, int relu) {
+  __shared__ float r1[4][64], r2[4][64];
+  const int cx = threadIdx.x & 63, ry = threadIdx.x >> 6;
+  const int c = blockIdx.x * 64 + cx;
+  const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
+  float s = 0.f, q = 0.f;
+  if (c < C) {
+    const float mu = mean[c], is = invstd[c];
+    for (long long r = r0 + ry; r < rend; r += 4) {
+      float g = b2f(dy[r * C + c]);
+      if (relu && !(b2f(y[r * C + c]) > 0.f)) g = 0.f;
+      s += g;
+      q = fmaf(g, (b2f(z[r * C + c]) - mu) * is, q);
+    }
+  }
+  r1[ry][cx] = s; r2[ry][cx] = q;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = ((r1[0][cx] + r1[1][cx]) + r1[2][cx]) + r1[3][cx];
+    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = ((r2[0][cx] + r2[1][cx]) + r2[2][cx]) + r2[3][cx];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_finalize_kernel(const float* __restrict__ partial, int chunks, int C, float* __restrict__ dbeta,
+                       float* __restrict__ dgamma) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f, q = 0.f;
+  for (int k = 0; k < chunks; ++k) { s += partial[((size_t)k * 2) * C + c]; q += partial[((size_t)k * 2 + 1) * C + c]; }
+  dbeta[c] = s;
+  dgamma[c] = q;
+}
+
+// dz = gamma * invstd * (g - dbeta/M - xhat * dgamma/M); optionally also writes the masked g
+// (the gradient that flows into the residual branch).
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ dbeta, const float* __restrict__ dgamma, bf16* __restrict__ dz,
+                    bf16* __restrict__ g_out, int g_accumulate, long long total, int C, long long M, int relu) {
+  const float inv_m = 1.f / (float)M;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    float g = b2f(dy[i]);
+    if (relu && !(b2f(y[i]) > 0.f)) g = 0.f;
+    const float xhat = (b2f(z[i]) - mean[c]) * invstd[c];
+    dz[i] = f2b(gamma[c] * invstd[c] * (g - dbeta[c] * inv_m - xhat * dgamma[c] * inv_m));
+    if (g_out) g_out[i] = g_accumulate ? f2b(b2f(g_out[i]) + g) : f2b(g);
+  }
+}
+
+// ---- 3x3 stride-2 pad-1 max pool -------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ arg, int N, int H, int W,
+                   int C, int OH, int OW) {
+  const long long total = (long long)N * OH * OW * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int ow = (int)((i / C) % OW), oh = (int)((i / C / OW) % OH);
+    const long long n = i / C / OW / OH;
+    float best = -INFINITY;
+    int a = 0;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        const int ih = oh * 2 + r - 1, iw = ow * 2 + s - 1;
+        if (ih < 0 || ih >= H || iw < 0 || iw >= W) continue;
+        const float v = b2f(x[((n * H + ih) * W + iw) * C + c]);
+        if (v > best) { best = v; a = r * 3 + s; }
+      }
+    y[i] = f2b(best);
+    arg[i] = (uint8_t)a;
+  }
+}
+
+// gather form: dx[n,h,w,c] = sum of dy over the (up to 4) windows whose arg-max is (h,w)
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ arg, bf16* __restrict__ dx, int N, int H,
+                   int W, int C, int OH, int OW) {
+  const long long total = (long long)N * H * W * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int w = (int)((i / C) % W), h = (int)((i / C / W) % H);
+    const long long n = i / C / W / H;
+    float acc = 0.f;
+    for (int r = 0; r < 3; ++r) {
+      const int th = h + 1 - r;
+      if (th < 0 || (th & 1)) continue;
+      const int oh = th >> 1;
+      if (oh >= OH) continue;
+      for (int s = 0; s < 3; ++s) {
+        const int tw = w + 1 - s;
+        if (tw < 0 || (tw & 1)) continue;
+        const int ow = tw >> 1;
+        if (ow >= OW) continue;
+        const long long o = ((n * OH + oh) * OW + ow) * C + c;
+        if (arg[o] == r * 3 + s) acc += b2f(dy[o]);
+      }
+    }
+    dx[i] = f2b(acc);
+  }
+}
+
+// ---- global average pool ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+avgpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ p, int N, int HW, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * C) return;
+  const int c = i % C, n = i / C;
+  float s = 0.f;
+  for (int k = 0; k < HW; ++k) s += b2f(x[((long long)n * HW + k) * C + c]);
+  p[i] = f2b(s / (float)HW);
+}
+
+__global__ void __launch_bounds__(256)
+avgpool_bwd_kernel(const bf16* __restrict__ dp, bf16* __restrict__ dx, int N, int HW, int C) {
+  const long long total = (long long)N * HW * C;
+  const float inv = 1.f / (float)HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long n = i / ((long long)HW * C);
+    dx[i] = f2b(b2f(dp[n * C + c]) * inv);
+  }
+}
+
+// ---- softmax cross-entropy over `classes` logits, one warp per example ---------------------------
+__global__ void __launch_bounds__(256)
+softmax_xent_wide_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                         bf16* __restrict__ dlogits, float* __restrict__ loss_vec, int B, int classes) {
+  const int lane = threadIdx.x & 31;
+  const int ex = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (ex >= B) return;
+  const float* z = logits + (size_t)ex * classes;
+  float mx = -INFINITY;
+  for (int k = lane; k < classes; k += 32) mx = fmaxf(mx, z[k]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f;
+  for (int k = lane; k < classes; k += 32) sum += expf(z[k] - mx);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const int lab = labels[ex];
+  const float inv_b = 1.f / (float)B;
+  for (int k = lane; k < classes; k += 32)
+    dlogits[(size_t)ex * classes + k] = f2b((expf(z[k] - mx) / sum - (k == lab ? 1.f : 0.f)) * inv_b);
+  if (lane == 0) loss_vec[ex] = logf(sum) - (z[lab] - mx);
+}
+
+// column sums of a bf16 matrix [R, C] -> fp32 out[C] (R small: the FC bias gradient), fixed order
+__global__ void __launch_bounds__(256)
+colsum_bf16_kernel(const bf16* __restrict__ in, float* __restrict__ out, int R, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int r = 0; r < R; ++r) s += b2f(in[(size_t)r * C + c]);
+  out[c] = s;
+}
+
+// mean of loss_vec[B] in a fixed order -> *out
+__global__ void __launch_bounds__(256) mean_kernel(const float* __restrict__ v, float* out, int B) {
+  __shared__ float part[256];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < B; i += 256) s += v[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = part[0] / (float)B;
+}
+
+}  // namespace rn
+}  // namespace tfg

@@ -1,0 +1,26 @@
+// Host-side interface of the tcgen05 GEMM (gemm_tc.cu) for the model translation units.
+#pragma once
+#include "common.cuh"
+#include "gemm_tc.cuh"
+
+namespace tfg {
+
+struct TcGemm {
+  CUtensorMap a, b;
+  float* C = nullptr;          // [M, ldc]
+  float* partial = nullptr;    // [splits][M][N] when splits > 1
+  int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
+  bool a_mn = false, b_mn = false;
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr};
+  const char* name = "gemm";
+};
+
+
+// Operand with `rows` (M or N) and `cols` (K).  K-major: stored [rows, K], pitch ld, box = 128 B of
+// K x box_rows.  MN-major: stored [K, rows], pitch ld, box = 128 B of rows x one stage of K.
+int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows,
+             bool mn_major = false);
+// j may be NULL (stateless entry point).  Launches the GEMM (and the split-K reduce when needed).
+int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s);
+
+}  // namespace tfg

@@ -67,6 +67,10 @@ _SIGS = {
     "tfg_var_register": (C.c_int, [_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int64),
                                    C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "tfg_num_vars": (C.c_int, [_p]),
+    "tfg_var_info": (C.c_int, [_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int),
+                               C.POINTER(C.c_int)]),
+    "tfg_model_resnet50": (C.c_int, [_p, C.c_int, C.c_int, C.c_int]),
+    "tfg_tensor_get": (C.c_int, [_p, C.c_int, C.c_char_p, _p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "tfg_vars_finalize": (C.c_int, [_p, C.c_int]),
     "tfg_placement": (C.c_int, [_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                 C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

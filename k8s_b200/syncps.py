@@ -49,6 +49,34 @@ def synthetic_batch(replica: int, batch: int, step: int = 0):
     return x, y
 
 
+def resnet50_init(job: "SyncPSJob", seed: int = 0) -> Dict[int, np.ndarray]:
+    """{variable index: initial value} for every trainable variable of a built ResNet-50."""
+    rng = np.random.default_rng(seed)
+    out: Dict[int, np.ndarray] = {}
+    for v in range(job.n_vars):
+        name, shape, trainable = job.var_info(v)
+        if not trainable:
+            continue
+        if name.endswith("/weights") and len(shape) == 4:
+            fan_in = shape[0] * shape[1] * shape[2]
+            out[v] = (rng.standard_normal(size=shape) * np.sqrt(2.0 / fan_in)).astype(np.float32)
+        elif name == "fc/weights":
+            out[v] = (rng.standard_normal(size=shape) * 0.01).astype(np.float32)
+        elif name.endswith("/gamma"):
+            out[v] = np.ones(shape, dtype=np.float32)
+        else:
+            out[v] = np.zeros(shape, dtype=np.float32)
+    return out
+
+
+def synthetic_images(replica: int, batch: int, hw: int, classes: int, step: int = 0):
+    """Synthetic ImageNet-shaped batch: N(0,1) fp32 [B,hw,hw,3], labels uniform in [0, classes)."""
+    rng = np.random.default_rng([2000 + replica, step])
+    x = rng.standard_normal(size=(batch, hw, hw, 3)).astype(np.float32)
+    y = rng.integers(0, classes, size=(batch,)).astype(np.int32)
+    return x, y
+
+
 class SyncPSJob:
     def __init__(self, tf_config: str, gpu_rank: int = 0, n_gpus: int = 1,
                  cuda_device: Optional[int] = None, stream: int = 0):
@@ -167,11 +195,41 @@ class SyncPSJob:
             for v, w in enumerate(mnist_init(seed)):
                 self.set_var(v, w)
 
+    def var_info(self, var: int):
+        name = C.create_string_buffer(256)
+        shape = (C.c_int64 * 8)()
+        rank, tr = C.c_int(), C.c_int()
+        self._ck(self.lib.var_info(self.h, var, name, len(name), shape, C.byref(rank), C.byref(tr)))
+        return name.value.decode(), tuple(shape[i] for i in range(rank.value)), bool(tr.value)
+
+    def build_resnet50(self, batch_per_replica: int, image_hw: int = 224, classes: int = 1000,
+                       layout: str = "balanced", seed: Optional[int] = 0) -> None:
+        """BASELINE config 4.  Weights: He-normal convolutions, gamma 1 / beta 0, fc N(0, 0.01),
+        all from numpy with a fixed seed (resnet50_init) and uploaded."""
+        self._ck(self.lib.model_resnet50(self.h, batch_per_replica, image_hw, classes))
+        self.batch, self.classes, self.image_hw = batch_per_replica, classes, image_hw
+        self.finalize(layout)
+        if seed is not None:
+            for v, w in resnet50_init(self, seed).items():
+                self.set_var(v, w)
+
+    def tensor(self, name: str, slot: int = 0) -> np.ndarray:
+        n = C.c_size_t()
+        cap = 1 << 20
+        while True:
+            out = np.empty(cap, dtype=np.float32)
+            rc = self.lib.tensor_get(self.h, slot, name.encode(), out.ctypes.data, cap, C.byref(n))
+            if rc == 5 and n.value > cap:
+                cap = n.value
+                continue
+            self._ck(rc)
+            return out[:n.value]
+
     def forward_backward(self, slot: int, images_dev: int, labels_dev: int) -> None:
         self._ck(self.lib.forward_backward(self.h, slot, images_dev, labels_dev))
 
     def logits(self, slot: int = 0) -> np.ndarray:
-        out = np.empty((self.batch, 10), dtype=np.float32)
+        out = np.empty((self.batch, getattr(self, "classes", 10)), dtype=np.float32)
         self._ck(self.lib.logits_get(self.h, slot, out.ctypes.data, out.nbytes))
         return out
 

@@ -1,0 +1,212 @@
+"""ResNet-50 (BASELINE config 4) parity at a size the CPU reference finishes in seconds
+(batch 4, 64x64 images, 16 classes); the full 224x224 / 1000-class shape is what
+bench.py --model resnet50 runs.
+
+Method.  A 50-layer bf16 network with batch-norm over a handful of samples is chaotic: the
+CPU reference's own gradients move by more than 100 % (relative L2) between fp32 and bf16
+arithmetic at this size, so an end-to-end gradient bound would say nothing about the
+kernels.  Parity is therefore checked LAYER BY LAYER with teacher forcing: every operator is
+recomputed on the CPU (PyTorch fp32 on the very bf16 inputs the GPU operator read, downloaded
+with tfg_tensor_get) and compared with what the GPU operator wrote:
+    conv forward, batch-norm forward (+ residual, relu), max-pool, average pool, fc, loss,
+    batch-norm backward (dgamma, dbeta, dz, residual gradient), conv wgrad, conv dgrad,
+    max-pool / average-pool backward.
+Bounds are relative L2 norms: 1e-2 for bf16-stored results (one bf16 rounding is 2^-9), 2e-2
+for the batch-norm backward (sums of bf16 products), 1e-2 for fp32 parameter gradients.
+End to end only the forward is bounded (loss within 5e-2 of the emulating oracle).
+"""
+import json
+
+import numpy as np
+import pytest
+
+from k8s_b200.syncps import SyncPSJob, resnet50_init, synthetic_images
+from oracle import resnet_ref as R
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+import torch.nn.functional as F  # noqa: E402
+
+
+def rel_l2(got, ref):
+    ref = np.asarray(ref, dtype=np.float64).ravel()
+    got = np.asarray(got, dtype=np.float64).ravel()
+    return float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30))
+
+
+def cfg(n_ps=2):
+    return json.dumps({"cluster": {"master": ["m-0:2222"], "ps": ["p-%d:2222" % i for i in range(n_ps)]},
+                       "task": {"type": "master", "index": 0}, "environment": "cloud"})
+
+
+def bf(a):
+    return torch.tensor(np.asarray(a), dtype=torch.float32).bfloat16().float()
+
+
+def nchw(a, shape):
+    return torch.tensor(np.asarray(a).reshape(shape), dtype=torch.float32).permute(0, 3, 1, 2)
+
+
+def nhwc(t):
+    return t.permute(0, 2, 3, 1).contiguous().numpy()
+
+
+CHECK_UNITS = ["conv1", "stage1/block1/shortcut", "stage1/block1/a", "stage1/block1/b", "stage1/block1/c",
+               "stage1/block2/a", "stage1/block2/c", "stage2/block1/shortcut", "stage2/block1/b", "stage2/block1/c",
+               "stage3/block6/b", "stage4/block1/b", "stage4/block3/c"]
+
+
+def test_resnet50_layerwise_parity():
+    B, HW, NC = 4, 64, 16
+    j = SyncPSJob(cfg(), 0, 1, cuda_device=0)
+    j.build_resnet50(B, HW, NC)
+    info = {v: j.var_info(v) for v in range(j.n_vars)}
+    var_of = {n: v for v, (n, s, t) in info.items()}
+    assert sum(1 for n, s, t in info.values() if t) == 161            # 53 conv + 2*53 bn + fc weights, biases
+    assert sum(int(np.prod(s)) for n, s, t in info.values() if t) == 25557032 - 2048 * 1000 - 1000 + 2048 * NC + NC
+    init = resnet50_init(j, 0)
+    rng = np.random.default_rng(7)
+    for v, w in init.items():       # make gamma / beta non-trivial so their role is tested
+        n = info[v][0]
+        if n.endswith("/gamma"):
+            init[v] = (1.0 + 0.2 * rng.standard_normal(w.shape)).astype(np.float32)
+        elif n.endswith("/beta") or n == "fc/biases":
+            init[v] = (0.1 * rng.standard_normal(w.shape)).astype(np.float32)
+        j.set_var(v, init[v])
+    P = {info[v][0]: w for v, w in init.items()}
+    x, y = synthetic_images(0, B, HW, NC)
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    j.forward_backward(0, dx.data_ptr(), dy.data_ptr())
+    j.sync()
+
+    # shapes of tensors
+    shape = {"image": (B, HW, HW, 3), "pool1": (B, HW // 4, HW // 4, 64)}
+    geom = {}
+    for name, inp, Rk, stride, kout, relu, res in R.units():
+        n_, h_, w_, c_ = shape[inp]
+        oh = (h_ + 2 * (Rk // 2) - Rk) // stride + 1
+        shape[name + "/z"] = shape[name + "/y"] = (n_, oh, oh, kout)
+        geom[name] = (inp, Rk, stride, kout, relu, res)
+    consumers = {}
+    for name, (inp, Rk, stride, kout, relu, res) in geom.items():
+        consumers.setdefault(inp, []).append(name)
+        if res:
+            consumers.setdefault(res, []).append(name + "#res")
+
+    def T(name):
+        return j.tensor(name)
+
+    fails = []
+
+    def check(what, got, ref, tol):
+        e = rel_l2(got, ref)
+        if not e <= tol:
+            fails.append("%s: rel L2 %.3e > %.1e" % (what, e, tol))
+
+    for name in CHECK_UNITS:
+        inp, Rk, stride, kout, relu, res = geom[name]
+        xin = nchw(T(inp), shape[inp])
+        w = bf(P[name + "/weights"]).permute(3, 2, 0, 1)
+        z_gpu = nchw(T(name + "/z"), shape[name + "/z"])
+        y_gpu = nchw(T(name + "/y"), shape[name + "/y"])
+        # conv forward on the GPU's own input
+        z_ref = F.conv2d(xin, w, None, stride=stride, padding=Rk // 2)
+        check(name + " conv fwd", nhwc(z_gpu), nhwc(z_ref), 1e-2)
+        # batch norm forward on the GPU's own z
+        mean = z_gpu.mean(dim=(0, 2, 3), keepdim=True)
+        var = (z_gpu * z_gpu).mean(dim=(0, 2, 3), keepdim=True) - mean * mean
+        invstd = torch.rsqrt(var.clamp_min(0) + 1e-5)
+        gamma = torch.tensor(P[name + "/bn/gamma"]).view(1, -1, 1, 1)
+        beta = torch.tensor(P[name + "/bn/beta"]).view(1, -1, 1, 1)
+        xhat = (z_gpu - mean) * invstd
+        v = gamma * xhat + beta
+        if res:
+            v = v + nchw(T(res), shape[res])
+        if relu:
+            v = F.relu(v)
+        check(name + " bn fwd", nhwc(y_gpu), nhwc(v), 1e-2)
+        # batch norm backward from the GPU's own dy
+        dy_gpu = nchw(T("grad:" + name + "/y"), shape[name + "/y"])
+        g = dy_gpu * (y_gpu > 0) if relu else dy_gpu
+        M = g.numel() / kout
+        dbeta = g.sum(dim=(0, 2, 3))
+        dgamma = (g * xhat).sum(dim=(0, 2, 3))
+        dz_ref = gamma * invstd * (g - dbeta.view(1, -1, 1, 1) / M - xhat * dgamma.view(1, -1, 1, 1) / M)
+        check(name + " dbeta", j.get_grad(0, var_of[name + "/bn/beta"]), dbeta.numpy(), 2e-2)
+        check(name + " dgamma", j.get_grad(0, var_of[name + "/bn/gamma"]), dgamma.numpy(), 2e-2)
+        dz_gpu = nchw(T("grad:" + name + "/z"), shape[name + "/z"])
+        check(name + " bn bwd dz", nhwc(dz_gpu), nhwc(dz_ref), 2e-2)
+        # conv weight gradient from the GPU's own dz and input
+        dw_ref = torch.nn.grad.conv2d_weight(xin, w.shape, dz_gpu, stride=stride, padding=Rk // 2)
+        check(name + " wgrad", j.get_grad(0, var_of[name + "/weights"]).reshape(P[name + "/weights"].shape),
+              dw_ref.permute(2, 3, 1, 0).numpy(), 1e-2)
+
+    # data gradients: the gradient of a tensor is the sum over its consumers
+    def contribution(cons):
+        if cons.endswith("#res"):
+            n = cons[:-4]
+            yy = nchw(T(n + "/y"), shape[n + "/y"])
+            gg = nchw(T("grad:" + n + "/y"), shape[n + "/y"])
+            return gg * (yy > 0) if geom[n][4] else gg
+        inp, Rk, stride, kout, relu, res = geom[cons]
+        w = bf(P[cons + "/weights"]).permute(3, 2, 0, 1)
+        dz = nchw(T("grad:" + cons + "/z"), shape[cons + "/z"])
+        n_, h_, w_, c_ = shape[inp]
+        return torch.nn.grad.conv2d_input((n_, c_, h_, w_), w, dz, stride=stride, padding=Rk // 2)
+
+    for t in ["pool1", "stage1/block1/a/y", "stage1/block1/b/y", "stage1/block1/c/y", "stage1/block3/c/y",
+              "stage2/block1/a/y", "stage3/block5/c/y", "stage4/block2/c/y"]:
+        ref = sum(contribution(c) for c in consumers[t])
+        check("grad of " + t, T("grad:" + t).reshape(shape[t]), nhwc(ref), 2e-2)
+
+    # max pool forward / backward
+    y0 = nchw(T("conv1/y"), shape["conv1/y"]).requires_grad_(True)
+    p_ref = F.max_pool2d(y0, 3, 2, 1)
+    check("maxpool fwd", T("pool1").reshape(shape["pool1"]), nhwc(p_ref.detach()), 1e-6)
+    dpool = nchw(T("grad:pool1"), shape["pool1"])
+    (dy0,) = torch.autograd.grad(p_ref, y0, dpool)
+    check("maxpool bwd", T("grad:conv1/y").reshape(shape["conv1/y"]), nhwc(dy0), 1e-2)
+    # head: average pool, fc, softmax cross-entropy and their gradients
+    last = "stage4/block3/c/y"
+    yl = nchw(T(last), shape[last]).requires_grad_(True)
+    wfc = torch.tensor(P["fc/weights"]).bfloat16().float().requires_grad_(True)
+    bfc = torch.tensor(P["fc/biases"]).requires_grad_(True)
+    pooled = yl.mean(dim=(2, 3)).bfloat16().float()
+    logits = pooled @ wfc + bfc
+    check("logits", j.logits(0), logits.detach().numpy(), 1e-2)
+    logits_gpu = torch.tensor(j.logits(0), requires_grad=True)
+    loss = F.cross_entropy(logits_gpu, torch.tensor(y, dtype=torch.long))
+    assert abs(j.loss(0) - float(loss)) <= 1e-4 * abs(float(loss)) + 1e-6
+    (dlog,) = torch.autograd.grad(loss, logits_gpu)
+    dlog = dlog.bfloat16().float()
+    check("fc wgrad", j.get_grad(0, var_of["fc/weights"]).reshape(2048, NC), (pooled.detach().t() @ dlog).numpy(), 1e-2)
+    check("fc bias grad", j.get_grad(0, var_of["fc/biases"]), dlog.sum(0).numpy(), 1e-2)
+    dp = (dlog @ wfc.detach().t()).bfloat16().float()
+    hw = shape[last][1] * shape[last][2]
+    dlast = (dp / hw).view(B, 2048, 1, 1).expand(-1, -1, shape[last][1], shape[last][2])
+    check("avgpool bwd", T("grad:" + last).reshape(shape[last]), nhwc(dlast), 1e-2)
+
+    # end to end: only the forward is bounded against the emulating oracle
+    loss_ref, _, _, _ = R.forward_backward(P, x, y, emulate=True)
+    if not abs(j.loss(0) - loss_ref) <= 5e-2 * abs(loss_ref):
+        fails.append("loss %.5f vs emulating oracle %.5f" % (j.loss(0), loss_ref))
+    assert not fails, "\n".join(fails)
+    # placement: every PS op ticks the round-robin, moving statistics included (A11)
+    assert [j.placement(v)["ps_task"] for v in range(6)] == [0, 1, 0, 1, 0, 1]
+    j.close()
+
+
+def test_resnet50_step_decreases_loss_and_is_deterministic():
+    B, HW, NC = 4, 64, 16
+    outs = []
+    for _ in range(2):
+        j = SyncPSJob(cfg(), 0, 1, cuda_device=0)
+        j.build_resnet50(B, HW, NC)
+        j.optimizer("momentum", 0.01, 0.9)
+        x, y = synthetic_images(0, B, HW, NC)
+        losses = [j.step([x], [y]) for _ in range(4)]
+        outs.append((losses, j.get_var(0).copy()))
+        j.close()
+    assert outs[0][0] == outs[1][0]
+    np.testing.assert_array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
+    assert outs[0][0][-1] < outs[0][0][0]
