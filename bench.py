@@ -40,7 +40,12 @@ def parse_args(argv=None):
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
-    ap.add_argument("--batch", type=int, default=BATCH, help="examples per replica per step")
+    ap.add_argument("--model", default="mnist", choices=["mnist", "resnet50"],
+                    help="mnist = tf_sample CNN (BASELINE configs 1-3, the default headline); "
+                         "resnet50 = BASELINE config 4 (synthetic ImageNet 224x224, bf16)")
+    ap.add_argument("--batch", type=int, default=0, help="examples per replica per step (default 128 / 256)")
+    ap.add_argument("--image", type=int, default=224, help="resnet50: image height = width")
+    ap.add_argument("--classes", type=int, default=1000, help="resnet50: number of classes")
     ap.add_argument("--math", default=os.environ.get("TFGRAFT_MATH", "auto"),
                     choices=["auto", "fp32", "bf16", "tf32"])
     ap.add_argument("--layout", default="balanced", choices=["logical", "balanced"])
@@ -48,7 +53,10 @@ def parse_args(argv=None):
     ap.add_argument("--ps-params", type=int, default=256 << 20,
                     help="parameters of the PS-update roofline probe (BASELINE config 5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args(argv)
+    a = ap.parse_args(argv)
+    if a.batch <= 0:
+        a.batch = BATCH if a.model == "mnist" else 256
+    return a
 
 
 def tf_job_doc(n_gpus: int) -> dict:
@@ -183,6 +191,8 @@ def run_reference(a) -> dict:
     1.3's gRPC PS runtime launched by a Go operator: neither can be built or installed in
     this image (DESIGN.md "Oracle"), so the arm times the oracle port ("kind": "port")."""
     n = a.gpus
+    if a.model == "resnet50":
+        return run_reference_resnet(a)
     value, ms, cores = cpu_step_rate(n, a.batch, a.opt, a.steps, max(a.warmup, 1))
     return {
         "impl": "reference", "metric": "examples/sec sync-PS step", "value": value, "unit": "examples/s",
@@ -197,7 +207,59 @@ def run_reference(a) -> dict:
     }
 
 
+def cpu_resnet_rate(a, batch: int, steps: int):
+    """images/s of the oracle's ResNet-50 forward/backward (fp32 torch-CPU, all host threads) on a
+    bounded sample: `steps` steps of `batch` images of the benchmark's shape."""
+    import torch
+    from oracle import resnet_ref as R
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    rng = np.random.default_rng(0)
+    shapes, cur = {}, {"image": 3, "pool1": 64}
+    for name, inp, rk, stride, kout, relu, res in R.units():
+        shapes[name + "/weights"] = (rk, rk, cur[inp], kout)
+        shapes[name + "/bn/gamma"] = shapes[name + "/bn/beta"] = (kout,)
+        cur[name + "/y"] = kout
+    shapes["fc/weights"], shapes["fc/biases"] = (2048, a.classes), (a.classes,)
+    params = {k: (rng.standard_normal(sh) * (np.sqrt(2.0 / np.prod(sh[:3])) if len(sh) == 4 else 0.01)).astype(np.float32)
+              if k.endswith("weights") else (np.ones(sh, np.float32) if k.endswith("gamma") else np.zeros(sh, np.float32))
+              for k, sh in shapes.items()}
+    x = rng.standard_normal((batch, a.image, a.image, 3)).astype(np.float32)
+    y = rng.integers(0, a.classes, batch).astype(np.int32)
+    R.forward_backward(params, x, y, emulate=False)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        R.forward_backward(params, x, y, emulate=False)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference_resnet(a) -> dict:
+    batch = 8
+    steps = max(1, min(a.steps, 3))
+    value, ms, cores = cpu_resnet_rate(a, batch, steps)
+    return {
+        "impl": "reference", "metric": "images/sec sync-PS step (ResNet-50)", "value": value, "unit": "images/s",
+        "n_gpus": a.gpus, "steps": steps, "warmup": 1, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(a, a.gpus, "fp32"),
+        "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
+                         "sample": "%d forward+backward passes of %d images (oracle/resnet_ref.py, fp32; the parameter "
+                                   "update is not included)" % (steps, batch)},
+        "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+
+
 def config_dict(a, n: int, math: str) -> dict:
+    if a.model == "resnet50":
+        return {
+            "workload": "tf_cnn_benchmarks-style ResNet-50 v1.5, synthetic ImageNet %dx%d, %d classes, bf16, "
+                        "%d replica(s) sync-PS on %d B200 (BASELINE config 4)" % (a.image, a.image, a.classes, n, n),
+            "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
+            "optimizer": a.opt, "lr": LR, "math": "bf16", "layout": a.layout, "params": 25557032,
+            "parallelism": "dp%d + %d PS shards" % (n, n),
+            "l2": "flushed between timed steps (256 MiB write, untimed)",
+        }
     return {
         "workload": ("tf_sample MNIST CNN sync-PS step: %s" %
                      ("examples/tf_job_gpu.yaml shape, 1 MASTER on 1 B200, no PS exchange" if n == 1 else
@@ -237,6 +299,25 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
     return "hbm", None
 
 
+def resnet_work(name: str, B: int, image: int, classes: int):
+    """FLOPs per step of all ResNet-50 launches that share a profile name (conv fwd / dgrad / wgrad)."""
+    from oracle import resnet_ref as R   # the layer table only; nothing is executed
+    hw = {"image": image, "pool1": image // 4}
+    cin = {"image": 3, "pool1": 64}
+    fl = {"rn conv fwd": 0.0, "rn conv wgrad": 0.0, "rn conv dgrad": 0.0}
+    for name_, inp, rk, stride, kout, relu, res in R.units():
+        oh = (hw[inp] + 2 * (rk // 2) - rk) // stride + 1
+        hw[name_ + "/y"], cin[name_ + "/y"] = oh, kout
+        f = 2.0 * B * oh * oh * kout * rk * rk * cin[inp]
+        fl["rn conv fwd"] += f
+        fl["rn conv wgrad"] += f
+        if inp != "image":
+            fl["rn conv dgrad"] += f
+    if name in fl:
+        return "tensor", fl[name]
+    return "hbm", None
+
+
 def ps_update_probe(lib, L, torch, stream, n_params: int, opt: str, peaks: dict) -> dict:
     """PS-update GB/s of BASELINE config 5's dense shard: one fused apply launch over
     n_params fp32 parameters resident in HBM (>> L2), CUDA events on the launching stream."""
@@ -268,7 +349,7 @@ def run_graft(a) -> dict:
     import torch
     import torch.distributed as dist
     from k8s_b200 import lib as L
-    from k8s_b200.syncps import SyncPSJob, synthetic_batch
+    from k8s_b200.syncps import SyncPSJob, synthetic_batch, synthetic_images
 
     n = a.gpus
     rank = int(os.environ.get("RANK", "0"))
@@ -285,9 +366,14 @@ def run_graft(a) -> dict:
     stream = torch.cuda.Stream()
     peaks = measured_peaks()
 
+    resnet = a.model == "resnet50"
     math = a.math
     job = None
-    for cand in (["bf16", "fp32"] if math == "auto" else [math]):
+    if resnet:
+        job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
+        job.build_resnet50(a.batch, a.image, a.classes, layout=a.layout)
+        math = "bf16"
+    for cand in ([] if resnet else ["bf16", "fp32"] if math == "auto" else [math]):
         job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
         try:
             job.build_mnist(a.batch, math=cand, layout=a.layout)
@@ -308,7 +394,7 @@ def run_graft(a) -> dict:
     for s in range(N_INPUT_SETS):
         hx, hy, dx, dy = [], [], [], []
         for r in slots:
-            x, y = synthetic_batch(r, B, s)
+            x, y = synthetic_images(r, B, a.image, a.classes, s) if resnet else synthetic_batch(r, B, s)
             px, py = torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()
             hx.append(px); hy.append(py)
             dx.append(px.cuda()); dy.append(py.cuda())
@@ -375,13 +461,14 @@ def run_graft(a) -> dict:
     value = examples / (ms_dev * 1e-3)
     e2e = examples / (ms_e2e * 1e-3)
     out = {
-        "metric": "examples/sec sync-PS step", "value": value, "unit": "examples/s", "n_gpus": n,
+        "metric": "images/sec sync-PS step (ResNet-50)" if resnet else "examples/sec sync-PS step",
+        "value": value, "unit": "images/s" if resnet else "examples/s", "n_gpus": n,
         "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_dev / a.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": {"fp32": "f32", "bf16": "bf16", "tf32": "tf32"}[math], "data": "synthetic",
         "config": config_dict(a, n, math),
-        "e2e": {"value": e2e, "unit": "examples/s", "ms_per_step": ms_e2e / a.steps,
-                "h2d_bytes_per_step": n * B * (784 * 4 + 4),
+        "e2e": {"value": e2e, "unit": "images/s" if resnet else "examples/s", "ms_per_step": ms_e2e / a.steps,
+                "h2d_bytes_per_step": n * B * ((a.image * a.image * 3 if resnet else 784) * 4 + 4),
                 "d2h_bytes_per_step": 4 * n, "last_loss": losses[-1] if losses else None},
         "gpu_launches": int(launches_timed),
         "clocks": clocks,
@@ -391,6 +478,9 @@ def run_graft(a) -> dict:
         top = max(prof, key=lambda k_: prof[k_]["ms"])
         bound, amount = algorithmic_work(top, B, 3274634, a.opt, n)
         per_launch_ms = prof[top]["ms"] / prof[top]["count"]
+        if resnet:   # per-layer launches share a name: work = the sum over the 53 convolutions, per step
+            bound, amount = resnet_work(top, B, a.image, a.classes)
+            per_launch_ms = prof[top]["ms"] / a.steps
         roof = {"kernel": top, "bound": bound, "share_of_step": prof[top]["ms"] / total,
                 "ms_per_launch": per_launch_ms, "traffic": None, "peak_source": peaks["source"]}
         if amount is not None and bound == "tensor":
@@ -410,10 +500,15 @@ def run_graft(a) -> dict:
     if rank == 0:
         out["ps_update"] = ps_update_probe(lib, L, torch, stream, a.ps_params, a.opt, peaks)
         if n == 1 and not a.no_cpu_baseline:
-            v, ms, cores = cpu_step_rate(1, B, a.opt, 250, 3)
-            out["cpu_baseline"] = {"value": v, "unit": "examples/s", "cores": cores, "kind": "port",
-                                   "sample": "250 full steps of 1 replica x %d examples (oracle port, "
-                                             "torch-CPU fwd/bwd + C apply)" % B}
+            if resnet:
+                v, ms, cores = cpu_resnet_rate(a, 8, 2)
+                out["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
+                                       "sample": "2 forward+backward passes of 8 images (oracle/resnet_ref.py, fp32)"}
+            else:
+                v, ms, cores = cpu_step_rate(1, B, a.opt, 250, 3)
+                out["cpu_baseline"] = {"value": v, "unit": "examples/s", "cores": cores, "kind": "port",
+                                       "sample": "250 full steps of 1 replica x %d examples (oracle port, "
+                                                 "torch-CPU fwd/bwd + C apply)" % B}
     if n > 1:
         dist.barrier()
         dist.destroy_process_group()
