@@ -86,8 +86,22 @@ static cudaError_t launch_stage(const TcGemm& g, float* dst, int ldc, int k_bloc
 template <int BN, int KIND, bool A_MN, bool B_MN>
 static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
                                tc::Epilogue epi, cudaStream_t s) {
-  if (kps <= 1) return launch_stage<BN, KIND, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
-  if (kps <= 3) return launch_stage<BN, KIND, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  // Ring depth.  A shallow ring leaves shared memory for more CTAs per SM, whose prologues and
+  // epilogues then overlap each other's loads: that wins whenever the grid is several waves deep
+  // (measured on the ResNet-50 layers: +14 % end to end); a grid of about one wave needs the deep
+  // ring to overlap its own loads with its MMAs (the MNIST GEMMs).  TFGRAFT_STAGES=1|2|4 forces one.
+  static int forced = -1;
+  if (forced < 0) {
+    forced = 0;
+    if (const char* e = getenv("TFGRAFT_STAGES")) forced = atoi(e);
+  }
+  const long long ctas = (long long)((g.N + BN - 1) / BN) * ((g.M + tc::kBlockM - 1) / tc::kBlockM) * splits;
+  int stages = kps <= 1 ? 1 : kps <= 3 ? 2 : 4;
+  if (ctas >= 4ll * kNumSMs) stages = 1;
+  else if (ctas >= 2ll * kNumSMs) stages = std::min(stages, 2);
+  if (forced == 1 || forced == 2 || forced == 4) stages = forced;
+  if (stages == 1) return launch_stage<BN, KIND, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (stages == 2) return launch_stage<BN, KIND, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   return launch_stage<BN, KIND, A_MN, B_MN, 4>(g, dst, ldc, k_blocks, kps, splits, epi, s);
 }
 

@@ -312,7 +312,9 @@ static int run_im2col(tfg_job* j, const RnUnit& u, const bf16* in, bf16* col) {
   if (u.g.C % 8 == 0) {
     rn::im2col_kernel<8><<<grid_for(M * u.g.R * u.g.S * (u.g.C / 8)), 256, 0, j->stream>>>(in, col, u.g);
   } else {
-    rn::im2col_kernel<1><<<grid_for(M * rsc), 256, 0, j->stream>>>(in, col, u.g);
+    rn::im2col_rows_kernel<<<grid_for(M * 32), 256, 0, j->stream>>>(in, col, u.g);
+    RN_OK(j, "rn im2col (thin)");
+    return TFG_OK;
   }
   RN_OK(j, "rn im2col");
   if (u.g.Kp != rsc) {
@@ -361,14 +363,14 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
                                                                s.invstd[i], update_moving ? u.mov_mean : nullptr,
                                                                update_moving ? u.mov_var : nullptr);
     RN_OK(j, "rn bn finalize");
-    rn::bn_apply_kernel<<<grid_for(M * u.kout), 256, 0, st>>>(s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma),
+    rn::bn_apply_kernel<<<grid_for(M * u.kout / 8), 256, 0, st>>>(s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma),
                                                              par(u.v_beta), u.res >= 0 ? s.data[u.res] : nullptr,
                                                              s.data[u.y], M * u.kout, u.kout, u.relu ? 1 : 0);
     RN_OK(j, "rn bn apply");
     if (u.y == m->t_pool_in) {
       const RnTensor& ti = m->tensors[m->t_pool_in];
       const RnTensor& to = m->tensors[m->t_pool_out];
-      rn::maxpool_fwd_kernel<<<grid_for(to.elems()), 256, 0, st>>>(s.data[m->t_pool_in], s.data[m->t_pool_out], s.pool_arg,
+      rn::maxpool_fwd_kernel<<<grid_for(to.elems() / 8), 256, 0, st>>>(s.data[m->t_pool_in], s.data[m->t_pool_out], s.pool_arg,
                                                                   (int)ti.n, (int)ti.h, (int)ti.w, (int)ti.c, (int)to.h,
                                                                   (int)to.w);
       RN_OK(j, "rn maxpool fwd");
@@ -400,7 +402,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     if (u.y == m->t_pool_in) {   // gradient arrives through the max pool
       const RnTensor& ti = m->tensors[m->t_pool_in];
       const RnTensor& to = m->tensors[m->t_pool_out];
-      rn::maxpool_bwd_kernel<<<grid_for(ti.elems()), 256, 0, st>>>(s.grad[m->t_pool_out], s.pool_arg, s.grad[m->t_pool_in],
+      rn::maxpool_bwd_kernel<<<grid_for(ti.elems() / 8), 256, 0, st>>>(s.grad[m->t_pool_out], s.pool_arg, s.grad[m->t_pool_in],
                                                                   (int)ti.n, (int)ti.h, (int)ti.w, (int)ti.c, (int)to.h,
                                                                   (int)to.w);
       RN_OK(j, "rn maxpool bwd");
@@ -418,7 +420,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     bf16* g_out = nullptr;
     int g_acc = 0;
     if (u.res >= 0) { g_out = s.grad[u.res]; g_acc = written[u.res]; written[u.res] = 1; }
-    rn::bn_bwd_apply_kernel<<<grid_for(M * u.kout), 256, 0, st>>>(
+    rn::bn_bwd_apply_kernel<<<grid_for(M * u.kout / 8), 256, 0, st>>>(
         s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma),
         s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M, u.relu ? 1 : 0);
     RN_OK(j, "rn bn bwd apply");
@@ -436,7 +438,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
       } else {
         d.epi.out_bf16 = s.dcol;
         if ((rc = launch_tc(j, d, TFG_MATH_BF16, st))) return rc;
-        rn::add_bf16_kernel<<<grid_for(in_elems), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
+        rn::add_bf16_kernel<<<grid_for(in_elems / 8), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
         RN_OK(j, "rn grad add");
       }
     } else {

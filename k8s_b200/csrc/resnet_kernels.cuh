@@ -23,6 +23,25 @@ struct ConvGeom {
 __device__ __forceinline__ float b2f(bf16 v) { return __bfloat162float(v); }
 __device__ __forceinline__ bf16 f2b(float v) { return __float2bfloat16_rn(v); }
 
+// 8 bf16 <-> 8 floats through one 16-byte access
+__device__ __forceinline__ void ld8(const bf16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
+}
+__device__ __forceinline__ void st8(bf16* p, const float (&v)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ void ldf8(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
 // images fp32 NHWC -> bf16
 __global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
@@ -54,6 +73,33 @@ im2col_kernel(const bf16* __restrict__ in, bf16* __restrict__ col, ConvGeom g) {
       *reinterpret_cast<uint4*>(dst) = ok ? *reinterpret_cast<const uint4*>(src) : make_uint4(0, 0, 0, 0);
     } else {
       dst[0] = ok ? src[0] : f2b(0.f);
+    }
+  }
+}
+
+// Thin-channel variant (the 7x7x3 stem): one warp per output pixel; lane l writes elements
+// l, l+32, ... of the pixel's col row, so every store instruction covers 64 contiguous bytes
+// (pad columns [R*S*C, Kp) included), and the gathered reads stay inside a 7x7 neighbourhood.
+__global__ void __launch_bounds__(256)
+im2col_rows_kernel(const bf16* __restrict__ in, bf16* __restrict__ col, ConvGeom g) {
+  const long long M = (long long)g.N * g.OH * g.OW;
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  const int K = g.R * g.S * g.C, SC = g.S * g.C;
+  for (long long m = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); m < M; m += warps) {
+    const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH);
+    const long long n = m / ((long long)g.OW * g.OH);
+    const int ih0 = oh * g.stride - g.pad, iw0 = ow * g.stride - g.pad;
+    const bf16* base = in + n * g.H * g.W * g.C;
+    for (int k = lane; k < g.Kp; k += 32) {
+      bf16 v = f2b(0.f);
+      if (k < K) {
+        const int r = k / SC, sc = k - r * SC;
+        const int s = sc / g.C;
+        const int ih = ih0 + r, iw = iw0 + s;
+        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) v = base[((long long)ih * g.W + iw0) * g.C + sc];
+      }
+      col[m * g.Kp + k] = v;
     }
   }
 }
@@ -102,44 +148,73 @@ col2im_kernel(const bf16* __restrict__ dcol, bf16* __restrict__ din, ConvGeom g,
       }
     }
     bf16* dst = din + pix * g.C + c;
-    if (accumulate) {
+    if (VEC == 8) {
+      float o[8];
 #pragma unroll
-      for (int u = 0; u < VEC; ++u) acc[u] += b2f(dst[u]);
+      for (int u = 0; u < 8; ++u) o[u] = acc[u % VEC];
+      if (accumulate) {
+        float prev[8];
+        ld8(dst, prev);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) o[u] += prev[u];
+      }
+      st8(dst, o);
+    } else {
+      if (accumulate) acc[0] += b2f(dst[0]);
+      dst[0] = f2b(acc[0]);
     }
-#pragma unroll
-    for (int u = 0; u < VEC; ++u) dst[u] = f2b(acc[u]);
   }
 }
 
 // dst (+)= src, bf16
 __global__ void __launch_bounds__(256)
 add_bf16_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long n, int accumulate) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    dst[i] = accumulate ? f2b(b2f(dst[i]) + b2f(src[i])) : src[i];
+  const long long n8 = n >> 3;   // every activation tensor of the net has a multiple of 8 elements
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float a[8], b[8];
+    ld8(src + (i << 3), a);
+    if (accumulate) {
+      ld8(dst + (i << 3), b);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] += b[k];
+    }
+    st8(dst + (i << 3), a);
+  }
 }
 
 // ---- batch norm ----------------------------------------------------------------------------
 // stage 1 of per-channel sums over rows: partial[chunk][2][C] = (sum x, sum x^2) for forward,
-// (sum dy, sum dy * xhat) for backward.  block = 64 channels x 4 row lanes.
+// (sum dy, sum dy * xhat) for backward.  block = 8 channel groups (8 channels = 16 B each) x 32
+// row lanes; C is a multiple of 64 for every layer of the net.
+__device__ __forceinline__ void bn_block_reduce(float (&s)[8], float (&q)[8], float* partial, int C, int cg, int rl) {
+  __shared__ float r1[32][65], r2[32][65];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { r1[rl][cg * 8 + k] = s[k]; r2[rl][cg * 8 + k] = q[k]; }
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < 64) {
+    float a = 0.f, b = 0.f;
+    for (int l = 0; l < 32; ++l) { a += r1[l][t]; b += r2[l][t]; }   // fixed order
+    const int c = blockIdx.x * 64 + t;
+    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = a;
+    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = b;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const bf16* __restrict__ z, float* __restrict__ partial, long long M, int C, int rows_per_chunk) {
-  __shared__ float r1[4][64], r2[4][64];
-  const int cx = threadIdx.x & 63, ry = threadIdx.x >> 6;
-  const int c = blockIdx.x * 64 + cx;
+  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const int c0 = blockIdx.x * 64 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s = 0.f, q = 0.f;
-  if (c < C)
-    for (long long r = r0 + ry; r < rend; r += 4) {
-      const float v = b2f(z[r * C + c]);
-      s += v;
-      q = fmaf(v, v, q);
-    }
-  r1[ry][cx] = s; r2[ry][cx] = q;
-  __syncthreads();
-  if (ry == 0 && c < C) {
-    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = ((r1[0][cx] + r1[1][cx]) + r1[2][cx]) + r1[3][cx];
-    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = ((r2[0][cx] + r2[1][cx]) + r2[2][cx]) + r2[3][cx];
+  float s[8], q[8], v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  for (long long r = r0 + rl; r < rend; r += 32) {
+    ld8(z + r * C + c0, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
   }
+  bn_block_reduce(s, q, partial, C, cg, rl);
 }
 
 // stage 2 forward: mean, invstd (biased variance, eps), moving statistics update
@@ -161,17 +236,26 @@ bn_finalize_kernel(const float* __restrict__ partial, int chunks, int C, long lo
   }
 }
 
-// y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out
+// y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out, 8 channels per thread
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ invstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta, const bf16* __restrict__ residual,
                 bf16* __restrict__ y, long long total, int C, int relu) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    float v = gamma[c] * (b2f(z[i]) - mean[c]) * invstd[c] + beta[c];
-    if (residual) v += b2f(residual[i]);
-    if (relu) v = fmaxf(v, 0.f);
-    y[i] = f2b(v);
+  const long long total8 = total >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)((i << 3) % C);
+    float v[8], mu[8], is[8], ga[8], be[8], rs[8];
+    ld8(z + (i << 3), v);
+    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(beta + c, be);
+    if (residual) ld8(residual + (i << 3), rs);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float o = ga[k] * (v[k] - mu[k]) * is[k] + be[k];
+      if (residual) o += rs[k];
+      if (relu) o = fmaxf(o, 0.f);
+      v[k] = o;
+    }
+    st8(y + (i << 3), v);
   }
 }
 
@@ -180,26 +264,26 @@ __global__ void __launch_bounds__(256)
 bn_bwd_stats_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
                     const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ partial,
                     long long M, int C, int rows_per_chunk, int relu) {
-  __shared__ float r1[4][64], r2[4][64];
-  const int cx = threadIdx.x & 63, ry = threadIdx.x >> 6;
-  const int c = blockIdx.x * 64 + cx;
+  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const int c0 = blockIdx.x * 64 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s = 0.f, q = 0.f;
-  if (c < C) {
-    const float mu = mean[c], is = invstd[c];
-    for (long long r = r0 + ry; r < rend; r += 4) {
-      float g = b2f(dy[r * C + c]);
-      if (relu && !(b2f(y[r * C + c]) > 0.f)) g = 0.f;
-      s += g;
-      q = fmaf(g, (b2f(z[r * C + c]) - mu) * is, q);
+  float s[8], q[8], mu[8], is[8], g[8], yy[8], zz[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  ldf8(mean + c0, mu);
+  ldf8(invstd + c0, is);
+  for (long long r = r0 + rl; r < rend; r += 32) {
+    ld8(dy + r * C + c0, g);
+    ld8(z + r * C + c0, zz);
+    if (relu) ld8(y + r * C + c0, yy);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float gg = (relu && !(yy[k] > 0.f)) ? 0.f : g[k];
+      s[k] += gg;
+      q[k] = fmaf(gg, (zz[k] - mu[k]) * is[k], q[k]);
     }
   }
-  r1[ry][cx] = s; r2[ry][cx] = q;
-  __syncthreads();
-  if (ry == 0 && c < C) {
-    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = ((r1[0][cx] + r1[1][cx]) + r1[2][cx]) + r1[3][cx];
-    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = ((r2[0][cx] + r2[1][cx]) + r2[2][cx]) + r2[3][cx];
-  }
+  bn_block_reduce(s, q, partial, C, cg, rl);
 }
 
 __global__ void __launch_bounds__(256)
@@ -214,20 +298,36 @@ bn_bwd_finalize_kernel(const float* __restrict__ partial, int chunks, int C, flo
 }
 
 // dz = gamma * invstd * (g - dbeta/M - xhat * dgamma/M); optionally also writes the masked g
-// (the gradient that flows into the residual branch).
+// (the gradient that flows into the residual branch).  8 channels per thread.
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ dbeta, const float* __restrict__ dgamma, bf16* __restrict__ dz,
                     bf16* __restrict__ g_out, int g_accumulate, long long total, int C, long long M, int relu) {
   const float inv_m = 1.f / (float)M;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    float g = b2f(dy[i]);
-    if (relu && !(b2f(y[i]) > 0.f)) g = 0.f;
-    const float xhat = (b2f(z[i]) - mean[c]) * invstd[c];
-    dz[i] = f2b(gamma[c] * invstd[c] * (g - dbeta[c] * inv_m - xhat * dgamma[c] * inv_m));
-    if (g_out) g_out[i] = g_accumulate ? f2b(b2f(g_out[i]) + g) : f2b(g);
+  const long long total8 = total >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)((i << 3) % C);
+    float g[8], yy[8], zz[8], mu[8], is[8], ga[8], db[8], dg[8], o[8], prev[8];
+    ld8(dy + (i << 3), g);
+    ld8(z + (i << 3), zz);
+    if (relu) ld8(y + (i << 3), yy);
+    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(dbeta + c, db); ldf8(dgamma + c, dg);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (relu && !(yy[k] > 0.f)) g[k] = 0.f;
+      const float xhat = (zz[k] - mu[k]) * is[k];
+      o[k] = ga[k] * is[k] * (g[k] - db[k] * inv_m - xhat * dg[k] * inv_m);
+    }
+    st8(dz + (i << 3), o);
+    if (g_out) {
+      if (g_accumulate) {
+        ld8(g_out + (i << 3), prev);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] += prev[k];
+      }
+      st8(g_out + (i << 3), g);
+    }
   }
 }
 
@@ -235,22 +335,31 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, con
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ arg, int N, int H, int W,
                    int C, int OH, int OW) {
-  const long long total = (long long)N * OH * OW * C;
+  const int cv = C >> 3;   // 8 channels per thread
+  const long long total = (long long)N * OH * OW * cv;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const int ow = (int)((i / C) % OW), oh = (int)((i / C / OW) % OH);
-    const long long n = i / C / OW / OH;
-    float best = -INFINITY;
-    int a = 0;
+    const int c = (int)(i % cv) << 3;
+    const int ow = (int)((i / cv) % OW), oh = (int)((i / cv / OW) % OH);
+    const long long n = i / cv / OW / OH;
+    float best[8], v[8];
+    int a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { best[k] = -INFINITY; a[k] = 0; }
     for (int r = 0; r < 3; ++r)
       for (int s = 0; s < 3; ++s) {
         const int ih = oh * 2 + r - 1, iw = ow * 2 + s - 1;
         if (ih < 0 || ih >= H || iw < 0 || iw >= W) continue;
-        const float v = b2f(x[((n * H + ih) * W + iw) * C + c]);
-        if (v > best) { best = v; a = r * 3 + s; }
+        ld8(x + ((n * H + ih) * W + iw) * C + c, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (v[k] > best[k]) { best[k] = v[k]; a[k] = r * 3 + s; }
       }
-    y[i] = f2b(best);
-    arg[i] = (uint8_t)a;
+    const long long o = (((n * OH + oh) * OW + ow) * C) + c;
+    st8(y + o, best);
+    uint2 pk;
+    pk.x = (uint32_t)a[0] | ((uint32_t)a[1] << 8) | ((uint32_t)a[2] << 16) | ((uint32_t)a[3] << 24);
+    pk.y = (uint32_t)a[4] | ((uint32_t)a[5] << 8) | ((uint32_t)a[6] << 16) | ((uint32_t)a[7] << 24);
+    *reinterpret_cast<uint2*>(arg + o) = pk;
   }
 }
 
@@ -258,12 +367,15 @@ maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ arg, bf16* __restrict__ dx, int N, int H,
                    int W, int C, int OH, int OW) {
-  const long long total = (long long)N * H * W * C;
+  const int cv = C >> 3;
+  const long long total = (long long)N * H * W * cv;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const int w = (int)((i / C) % W), h = (int)((i / C / W) % H);
-    const long long n = i / C / W / H;
-    float acc = 0.f;
+    const int c = (int)(i % cv) << 3;
+    const int w = (int)((i / cv) % W), h = (int)((i / cv / W) % H);
+    const long long n = i / cv / W / H;
+    float acc[8], g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
     for (int r = 0; r < 3; ++r) {
       const int th = h + 1 - r;
       if (th < 0 || (th & 1)) continue;
@@ -275,10 +387,16 @@ maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ arg,
         const int ow = tw >> 1;
         if (ow >= OW) continue;
         const long long o = ((n * OH + oh) * OW + ow) * C + c;
-        if (arg[o] == r * 3 + s) acc += b2f(dy[o]);
+        const uint2 pk = *reinterpret_cast<const uint2*>(arg + o);
+        ld8(dy + o, g);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t a = ((k < 4 ? pk.x : pk.y) >> (8 * (k & 3))) & 0xffu;
+          if (a == (uint32_t)(r * 3 + s)) acc[k] += g[k];
+        }
       }
     }
-    dx[i] = f2b(acc);
+    st8(dx + (((n * H + h) * W + w) * C) + c, acc);
   }
 }
 
