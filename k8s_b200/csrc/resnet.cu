@@ -4,7 +4,7 @@
 //
 // Every convolution is a tcgen05 GEMM (gemm_tc.cuh): 1x1 stride-1 convolutions read the NHWC
 // activation as the [pixels, C] operand in place; the others go through an explicit bf16
-// im2col (`col`, recomputed in backward rather than kept).  For a conv with input x, filter W
+// im2col (`col`, one buffer per layer, kept from forward for the weight gradient: 7 GB at batch 256).  For a conv with input x, filter W
 // (HWIO) and output gradient dz:
 //     forward  z[M, Kout]     = col[M, RSC] (K-major)  x W[RSC, Kout] (MN-major)  -> bf16
 //     wgrad    dW[RSC, Kout]  = col[M, RSC] (MN-major) x dz[M, Kout]  (MN-major)  -> fp32, split-K
@@ -45,7 +45,8 @@ struct RnSlot {
   int32_t* lab_stage = nullptr;
   std::vector<bf16*> data, grad;     // per tensor
   std::vector<float*> mean, invstd;  // per unit
-  bf16 *col = nullptr, *dcol = nullptr;
+  std::vector<bf16*> col;            // per unit: im2col of its input, kept from forward to backward (NULL if direct)
+  bf16* dcol = nullptr;              // shared staging of data gradients
   uint8_t* pool_arg = nullptr;
   float *bn_partial = nullptr, *splitk = nullptr;
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
@@ -192,7 +193,11 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
       alloc((void**)&s.mean[u], sizeof(float) * m->units[u].kout);
       alloc((void**)&s.invstd[u], sizeof(float) * m->units[u].kout);
     }
-    alloc((void**)&s.col, sizeof(bf16) * m->col_elems);
+    s.col.assign(m->units.size(), nullptr);
+    for (size_t u = 0; u < m->units.size(); ++u) {
+      const RnUnit& un = m->units[u];
+      if (!un.direct) alloc((void**)&s.col[u], sizeof(bf16) * (size_t)un.g.N * un.g.OH * un.g.OW * un.g.Kp);
+    }
     alloc((void**)&s.dcol, sizeof(bf16) * m->col_elems);
     alloc((void**)&s.pool_arg, (size_t)m->tensors[m->t_pool_out].elems());
     alloc((void**)&s.bn_partial, sizeof(float) * 128 * 2 * (size_t)m->cmax);
@@ -224,7 +229,8 @@ void resnet_destroy(tfg_job* j) {
     for (auto p : s.grad) cudaFree(p);
     for (auto p : s.mean) cudaFree(p);
     for (auto p : s.invstd) cudaFree(p);
-    cudaFree(s.col); cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.splitk);
+    for (auto p : s.col) cudaFree(p);
+    cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.splitk);
     cudaFree(s.logits); cudaFree(s.loss_vec); cudaFree(s.pooled); cudaFree(s.dpooled); cudaFree(s.dlogits);
   }
   delete m;
@@ -254,7 +260,7 @@ static int prepare_maps(tfg_job* j, int slot) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
     const int rsc = u.g.R * u.g.S * u.g.C;
-    const void* a_ptr = u.direct ? static_cast<const void*>(s.data[u.in]) : static_cast<const void*>(s.col);
+    const void* a_ptr = u.direct ? static_cast<const void*>(s.data[u.in]) : static_cast<const void*>(s.col[i]);
     const long long a_ld = u.direct ? u.g.C : u.g.Kp;
     const int bn = u.kout >= 128 ? 128 : 64;
     // forward: z = col x W
@@ -353,7 +359,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
   for (size_t i = 0; i < m->units.size(); ++i) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
-    if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col))) return rc;
+    if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col[i]))) return rc;
     if ((rc = launch_tc(j, s.fwd[i], TFG_MATH_BF16, st))) return rc;
     int chunks, rows;
     bn_chunks(M, &chunks, &rows);
@@ -424,8 +430,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
         s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma),
         s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M, u.relu ? 1 : 0);
     RN_OK(j, "rn bn bwd apply");
-    // weight gradient (im2col recomputed: `col` is shared by all layers)
-    if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col))) return rc;
+    // weight gradient: the im2col operand is the one the forward pass built
     if ((rc = launch_tc(j, s.wgrad[i], TFG_MATH_BF16, st))) return rc;
     if (u.in == m->t_image) continue;
     // data gradient
