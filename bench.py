@@ -50,6 +50,9 @@ def parse_args(argv=None):
                     choices=["auto", "fp32", "bf16", "tf32"])
     ap.add_argument("--layout", default="balanced", choices=["logical", "balanced"])
     ap.add_argument("--opt", default="momentum", choices=["sgd", "momentum", "nesterov"])
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="peer = fused push+apply+pull over peer memory (the product); nccl = all-reduce of the flat "
+                         "gradient through torch.distributed + full local apply (the baseline it is compared with)")
     ap.add_argument("--ps-params", type=int, default=256 << 20,
                     help="parameters of the PS-update roofline probe (BASELINE config 5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -258,7 +261,7 @@ def config_dict(a, n: int, math: str) -> dict:
             "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
             "optimizer": a.opt, "lr": LR, "math": "bf16", "layout": a.layout, "params": 25557032,
             "parallelism": "dp%d + %d PS shards" % (n, n),
-            "l2": "flushed between timed steps (256 MiB write, untimed)",
+            "l2": "flushed between timed steps (256 MiB write, untimed)", "exchange": a.exchange,
         }
     return {
         "workload": ("tf_sample MNIST CNN sync-PS step: %s" %
@@ -267,7 +270,7 @@ def config_dict(a, n: int, math: str) -> dict:
         "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
         "optimizer": a.opt, "lr": LR, "math": math, "layout": a.layout,
         "params": 3274634, "parallelism": "dp%d + %d PS shards" % (n, n),
-        "l2": "flushed between timed steps (256 MiB write, untimed)",
+        "l2": "flushed between timed steps (256 MiB write, untimed)", "exchange": a.exchange,
     }
 
 
@@ -430,7 +433,11 @@ def run_graft(a) -> dict:
 
     def step_dev(k):
         dx, dy = dev[k % N_INPUT_SETS]
-        job.step_dev(dx, dy)
+        if a.exchange == "nccl":
+            with torch.cuda.stream(stream):     # NCCL work must land on the job's stream
+                job.step_nccl(dx, dy, dist)
+        else:
+            job.step_dev(dx, dy)
 
     losses = []
 
@@ -446,9 +453,12 @@ def run_graft(a) -> dict:
     sampler.start()
     ms_dev = timed(step_dev, a.steps)
     launches_timed = job.launches - launches0
-    for k in range(3):
-        step_e2e(k)
-    ms_e2e = timed(step_e2e, a.steps)
+    if a.exchange == "nccl":
+        ms_e2e = float("nan")      # the baseline arm is timed device-resident only
+    else:
+        for k in range(3):
+            step_e2e(k)
+        ms_e2e = timed(step_e2e, a.steps)
     clocks = sampler.stop()
 
     # per-kernel device time over another K steps (events behind every launch)

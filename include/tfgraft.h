@@ -173,6 +173,10 @@ int tfg_push_apply_pull(tfg_job* job, int with_barriers);
 /* split variant for the NCCL baseline: apply on this rank's owned ranges from an
  * already-reduced (summed) gradient in local replica slot 0, writing only locally. */
 int tfg_apply_owned(tfg_job* job, int n_summed);
+/* the all-reduce baseline: the gradient in local replica slot 0 already holds the sum over all
+ * n_summed replicas (e.g. after an NCCL all-reduce); every rank applies the whole flat space
+ * to its own copy, no pull.  bench.py --exchange nccl times this against the fused kernel. */
+int tfg_apply_all(tfg_job* job, int n_summed);
 
 /* stateless form of the same kernel over caller buffers (PS shard sweep, tests):
  * var/accum [count] fp32 updated in place from n_grads gradient buffers (host array of

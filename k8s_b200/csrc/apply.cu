@@ -158,7 +158,7 @@ static cudaError_t launch_kind(int kind, K&& f) {
   return cudaGetLastError();
 }
 
-int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole) {
   ApplyArgs a = {};
   if (summed_local) {
     a.grads[0] = j->grads[0];
@@ -186,6 +186,12 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed) {
   a.segs = j->d_segs;
   a.n_segs = (int)j->segs.size();
   a.n_chunks = j->n_chunks;
+  if (whole) {   // every rank applies the whole flat space (the all-reduce baseline)
+    a.segs = nullptr;
+    a.seg0 = Segment{0, j->flat_count, 0};
+    a.n_segs = 1;
+    a.n_chunks = (j->flat_count + kChunk - 1) / kChunk;
+  }
   a.kind = j->opt_kind;
   a.lr = j->lr;
   a.mu = j->mu;

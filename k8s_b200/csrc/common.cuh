@@ -116,7 +116,7 @@ int fail_cuda(tfg_job* j, cudaError_t e, const char* what);
 void prof_mark(tfg_job* j, const char* what);
 
 // apply.cu
-int launch_job_apply(tfg_job* j, bool summed_local, int n_summed);
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole = false);
 int launch_barrier(tfg_job* j);
 int launch_dense_apply(int kind, float* var, float* accum, const float* const* grads, int n_grads,
                        float divisor, int64_t count, float lr, float mu, float* const* pull,

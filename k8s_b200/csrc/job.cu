@@ -607,6 +607,17 @@ int tfg_apply_owned(tfg_job* j, int n_summed) {
   return TFG_OK;
 }
 
+int tfg_apply_all(tfg_job* j, int n_summed) {
+  if (!j || !j->finalized) return fail(j, TFG_ESTATE, "job is not finalized");
+  if (n_summed < 1) return fail(j, TFG_EINVAL, "n_summed must be >= 1");
+  if (j->grads.empty()) return fail(j, TFG_ESTATE, "this rank hosts no replica");
+  TFG_CUDA(j, cudaSetDevice(j->device));
+  int rc = launch_job_apply(j, true, n_summed, true);
+  if (rc) return rc;
+  j->global_step += 1;
+  return TFG_OK;
+}
+
 int tfg_dense_apply(int kind, float* var, float* accum, const float* const* grads, int n_grads,
                     float divisor, int64_t count, float lr, float mu, float* const* pull, int n_pull,
                     void* stream) {

@@ -89,6 +89,7 @@ _SIGS = {
     "tfg_job_barrier": (C.c_int, [_p]),
     "tfg_push_apply_pull": (C.c_int, [_p, C.c_int]),
     "tfg_apply_owned": (C.c_int, [_p, C.c_int]),
+    "tfg_apply_all": (C.c_int, [_p, C.c_int]),
     "tfg_dense_apply": (C.c_int, [C.c_int, _p, _p, C.POINTER(_p), C.c_int, C.c_float, C.c_int64,
                                   C.c_float, C.c_float, C.POINTER(_p), C.c_int, _p]),
     "tfg_sparse_shard_rows": (C.c_int64, [C.c_int64, C.c_int, C.c_int, C.c_int]),

@@ -250,6 +250,31 @@ class SyncPSJob:
     def push_apply_pull(self, with_barriers: bool = True) -> None:
         self._ck(self.lib.push_apply_pull(self.h, int(with_barriers)))
 
+    def apply_all(self, n_summed: int) -> None:
+        self._ck(self.lib.apply_all(self.h, n_summed))
+
+    def grads_tensor(self, slot: int = 0):
+        """The flat gradient buffer of a slot as a torch tensor view (no copy), for handing it to
+        torch.distributed collectives in the NCCL baseline."""
+        import torch
+        ptr, nbytes = self.buffer(L.BUF_GRADS, slot)
+
+        class _View:
+            __cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<f4", "data": (ptr, False), "version": 3,
+                                        "strides": None}
+        return torch.as_tensor(_View(), device="cuda")
+
+    def step_nccl(self, images_dev, labels_dev, dist) -> None:
+        """Baseline exchange: forward/backward here, NCCL all-reduce of the flat gradient, then every
+        rank applies the whole parameter vector (no peer-memory kernel, no CUDA graph)."""
+        for s in range(len(images_dev)):
+            self.forward_backward(s, L.ptr(images_dev[s]), L.ptr(labels_dev[s]))
+        if not hasattr(self, "_gt"):
+            self._gt = self.grads_tensor(0)
+        if self.n_gpus > 1:
+            dist.all_reduce(self._gt)
+        self.apply_all(self.n_replicas)
+
     def apply_owned(self, n_summed: int) -> None:
         self._ck(self.lib.apply_owned(self.h, n_summed))
 
