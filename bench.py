@@ -282,6 +282,7 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
     gemm = {"gemm conv2 fwd": (M2, 64, 800), "gemm conv2 dgrad": (M2, 800, 64), "gemm conv2 wgrad": (800, 64, M2),
             "gemm fc1 fwd": (B, 1024, 3136), "gemm fc1 dgrad": (B, 3136, 1024), "gemm fc1 wgrad": (3136, 1024, B),
             "gemm fc2 fwd": (B, 10, 1024), "gemm fc2 dgrad": (B, 1024, 10), "gemm fc2 wgrad": (1024, 10, B)}
+    name = name[3:] if name.startswith("tc ") else name     # the tensor-path GEMMs carry a "tc " prefix
     if name in gemm:
         m, n, k = gemm[name]
         return "tensor", 2.0 * m * n * k

@@ -34,6 +34,7 @@ struct Epilogue {
   const float* mask;    // [M, ldc]: keep the value where mask > 0, else 0; or NULL
   int relu;
   void* out_bf16;       // when set, the result is stored as bf16 [M, ldc] here instead of fp32 in C
+  int direct;           // 1: store straight from registers (thread = row), 0: via the smem transpose
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -127,6 +128,140 @@ template <int BLOCK_N, int STAGES>
 constexpr size_t smem_bytes() {
   return 1024 /*alignment slack*/ + static_cast<size_t>(STAGES) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
          (2 * STAGES + 1) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+}
+
+// Epilogue of one 128 x BLOCK_N tile by the four epilogue warps.  tcgen05.ld hands thread t row t
+// of its lane quarter and 32 consecutive columns per pass.  Default (epi.direct): each thread
+// stores its 64 B (bf16) / 128 B (fp32) row piece straight from registers with 16-byte stores --
+// measured faster than the alternative kept for ragged tails, which bounces 32x32 blocks through a
+// per-warp shared-memory tile so that 8 lanes write one 128-byte row segment.
+// `have_acc` = the accumulator holds a product (false: an empty K range writes zeros).
+template <int BLOCK_N>
+__device__ __forceinline__ void drain_tile(uint32_t tmem_acc, bool have_acc, float* stage_base, int warp, int lane,
+                                           float* __restrict__ C, int M, int N, int ldc, int m0, int n0, int z,
+                                           const Epilogue& epi) {
+  const int q = warp & 3;                            // TMEM lane quarter this warp may touch
+  float (*stage)[33] = reinterpret_cast<float (*)[33]>(stage_base + (warp - 2) * 32 * 33);
+  float* cbase = C + static_cast<size_t>(z) * M * static_cast<size_t>(ldc);
+  // 128-bit accesses need 16-B aligned rows (C, bias and mask come from cudaMalloc / 128-B
+  // aligned variable offsets; the leading dimension decides the rest)
+  const bool vec_ok = (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                      (!epi.bias || (reinterpret_cast<uintptr_t>(epi.bias) & 15) == 0) &&
+                      (!epi.mask || (reinterpret_cast<uintptr_t>(epi.mask) & 15) == 0);
+#pragma unroll 1
+  for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+    uint32_t r[32];
+    if (have_acc) {
+      const uint32_t taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+          : "r"(taddr) : "memory");
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+            "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+            "=r"(r[30]), "=r"(r[31])
+          : "r"(taddr + 16) : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    } else {
+#pragma unroll
+      for (int u = 0; u < 32; ++u) r[u] = 0u;
+    }
+    if (epi.direct && vec_ok && n0 + c0 + 32 <= N && (!epi.out_bf16 || (ldc & 7) == 0)) {
+      // thread t owns row t of the quarter and 32 consecutive columns: 64 B (bf16) or 128 B (fp32)
+      const int row = m0 + q * 32 + lane;
+      if (row < M) {
+        const int colb = n0 + c0;
+#pragma unroll
+        for (int u = 0; u < 32; u += 8) {
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[u + k]);
+          if (epi.bias) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] += epi.bias[colb + u + k];
+          }
+          if (epi.relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+          }
+          if (epi.mask) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              v[k] = epi.mask[static_cast<size_t>(row) * ldc + colb + u + k] > 0.f ? v[k] : 0.f;
+          }
+          if (epi.out_bf16) {
+            uint4 pk;
+            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+            *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(epi.out_bf16) +
+                                      (static_cast<size_t>(z) * M + row) * static_cast<size_t>(ldc) + colb + u) = pk;
+          } else {
+            float* dst = cbase + static_cast<size_t>(row) * ldc + colb + u;
+            *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+          }
+        }
+      }
+      continue;
+    }
+#pragma unroll
+    for (int u = 0; u < 32; ++u) stage[lane][u] = __uint_as_float(r[u]);   // bank (lane + u) % 32
+    __syncwarp();
+    const int cc = (lane & 7) * 4;
+    const int col = n0 + c0 + cc;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int rr = i * 4 + (lane >> 3);
+      const int row = m0 + q * 32 + rr;
+      float4 v = make_float4(stage[rr][cc], stage[rr][cc + 1], stage[rr][cc + 2], stage[rr][cc + 3]);
+      if (row >= M || col >= N) continue;
+      float* dst = cbase + static_cast<size_t>(row) * ldc + col;
+      if (vec_ok && col + 3 < N) {
+        if (epi.bias) {
+          const float4 b = *reinterpret_cast<const float4*>(epi.bias + col);
+          v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+        }
+        if (epi.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+        if (epi.mask) {
+          const float4 k = *reinterpret_cast<const float4*>(epi.mask + static_cast<size_t>(row) * ldc + col);
+          v.x = k.x > 0.f ? v.x : 0.f; v.y = k.y > 0.f ? v.y : 0.f;
+          v.z = k.z > 0.f ? v.z : 0.f; v.w = k.w > 0.f ? v.w : 0.f;
+        }
+        if (epi.out_bf16) {
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+          *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(epi.out_bf16) +
+                                    (static_cast<size_t>(z) * M + row) * static_cast<size_t>(ldc) + col) = pk;
+        } else {
+          *reinterpret_cast<float4*>(dst) = v;
+        }
+      } else {
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (col + u >= N) break;
+          float x = vv[u];
+          if (epi.bias) x += epi.bias[col + u];
+          if (epi.relu) x = fmaxf(x, 0.f);
+          if (epi.mask) x = epi.mask[static_cast<size_t>(row) * ldc + col + u] > 0.f ? x : 0.f;
+          if (epi.out_bf16)
+            static_cast<__nv_bfloat16*>(epi.out_bf16)[(static_cast<size_t>(z) * M + row) * static_cast<size_t>(ldc) +
+                                                      col + u] = __float2bfloat16_rn(x);
+          else
+            dst[u] = x;
+        }
+      }
+    }
+    __syncwarp();
+  }
 }
 
 // STAGES = depth of the TMA ring.  Short-K GEMMs (one or two K blocks per CTA) take 1 or 2
@@ -232,103 +367,165 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       umma_commit(tmem_full);                          // accumulator complete
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =====
-    // tcgen05.ld hands thread t row t of its lane quarter.  Storing that directly would make
-    // every store instruction touch 32 different rows; instead each warp bounces a 32x32 block
-    // through its private staging tile so that 8 lanes write one 128-byte row segment.
-    const int q = warp & 3;                            // TMEM lane quarter this warp may touch
-    float (*stage)[33] = reinterpret_cast<float (*)[33]>(stage_base + (warp - 2) * 32 * 33);
+    // ===== epilogue =====
     if (n_kb > 0) {
       mbar_wait(tmem_full, 0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
-    float* cbase = C + static_cast<size_t>(blockIdx.z) * M * static_cast<size_t>(ldc);
-    // 128-bit accesses need 16-B aligned rows (C, bias and mask come from cudaMalloc / 128-B
-    // aligned variable offsets; the leading dimension decides the rest)
-    const bool vec_ok = (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
-                        (!epi.bias || (reinterpret_cast<uintptr_t>(epi.bias) & 15) == 0) &&
-                        (!epi.mask || (reinterpret_cast<uintptr_t>(epi.mask) & 15) == 0);
-#pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-      uint32_t r[32];
-      if (n_kb > 0) {
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-            : "r"(taddr) : "memory");
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-            : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
-              "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
-              "=r"(r[30]), "=r"(r[31])
-            : "r"(taddr + 16) : "memory");
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      } else {
-#pragma unroll
-        for (int u = 0; u < 32; ++u) r[u] = 0u;
-      }
-#pragma unroll
-      for (int u = 0; u < 32; ++u) stage[lane][u] = __uint_as_float(r[u]);   // bank (lane + u) % 32
-      __syncwarp();
-      const int cc = (lane & 7) * 4;
-      const int col = n0 + c0 + cc;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int rr = i * 4 + (lane >> 3);
-        const int row = m0 + q * 32 + rr;
-        float4 v = make_float4(stage[rr][cc], stage[rr][cc + 1], stage[rr][cc + 2], stage[rr][cc + 3]);
-        if (row >= M || col >= N) continue;
-        float* dst = cbase + static_cast<size_t>(row) * ldc + col;
-        if (vec_ok && col + 3 < N) {
-          if (epi.bias) {
-            const float4 b = *reinterpret_cast<const float4*>(epi.bias + col);
-            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-          }
-          if (epi.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-          if (epi.mask) {
-            const float4 k = *reinterpret_cast<const float4*>(epi.mask + static_cast<size_t>(row) * ldc + col);
-            v.x = k.x > 0.f ? v.x : 0.f; v.y = k.y > 0.f ? v.y : 0.f;
-            v.z = k.z > 0.f ? v.z : 0.f; v.w = k.w > 0.f ? v.w : 0.f;
-          }
-          if (epi.out_bf16) {
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-            uint2 pk;
-            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
-            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-            *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(epi.out_bf16) +
-                                      (static_cast<size_t>(blockIdx.z) * M + row) * static_cast<size_t>(ldc) + col) = pk;
-          } else {
-            *reinterpret_cast<float4*>(dst) = v;
-          }
-        } else {
-          const float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            if (col + u >= N) break;
-            float x = vv[u];
-            if (epi.bias) x += epi.bias[col + u];
-            if (epi.relu) x = fmaxf(x, 0.f);
-            if (epi.mask) x = epi.mask[static_cast<size_t>(row) * ldc + col + u] > 0.f ? x : 0.f;
-            if (epi.out_bf16)
-              static_cast<__nv_bfloat16*>(epi.out_bf16)[(static_cast<size_t>(blockIdx.z) * M + row) *
-                                                            static_cast<size_t>(ldc) + col + u] = __float2bfloat16_rn(x);
-            else
-              dst[u] = x;
-          }
-        }
-      }
-      __syncwarp();
-    }
+    drain_tile<BLOCK_N>(tmem_base, n_kb > 0, stage_base, warp, lane, C, M, N, ldc, m0, n0, blockIdx.z, epi);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(BLOCK_N) : "memory");
+  }
+}
+
+// ---- persistent variant ----------------------------------------------------------------------------
+// One CTA per SM walks the tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA ring keeps
+// running across tile boundaries and the accumulator is double-buffered in TMEM (2 x BLOCK_N
+// columns): while the epilogue warps drain tile i, the MMA warp already accumulates tile i + 1.
+// Used when the grid is at least two waves deep (the ResNet-50 layers); tile = (m fastest, n, z).
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+
+template <int BLOCK_N>
+constexpr size_t smem_bytes_persistent() {
+  return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
+         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+}
+
+template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                          float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
+                          int tiles_m, int tiles_n, int splits, Epilogue epi) {
+  constexpr int kStages = kMaxStages;
+  constexpr int kElemBytes = KIND == 0 ? 2 : 4;
+  constexpr int kBlockK = kBlockKBytes / kElemBytes;
+  constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
+  constexpr int kMnElems = 128 / kElemBytes;
+  constexpr int kChunkBytes = kBlockK * 128;
+  constexpr int kUmmaK = 32 / kElemBytes;
+  constexpr uint32_t kStepA = A_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
+  constexpr uint32_t kStepB = B_MN ? (kUmmaK * 128) >> 4 : 32 >> 4;
+  static_assert(BLOCK_N == 64 || BLOCK_N == 128, "two accumulators of BLOCK_N columns must fit a power-of-two allocation");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kABytes + kBBytes));
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = tiles_m * tiles_n * splits;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(smem_u32(tmem_slot)), "n"(2 * BLOCK_N) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: one continuous stream of K blocks over all of this CTA's tiles =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = (t % tiles_m) * kBlockM, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+        const int kb_begin = z * k_blocks_per_split, kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(&empty[s], phase ^ 1);
+          mbar_expect_tx(&full[s], kABytes + kBBytes);
+          const int k_elem = kb * kBlockK;
+          if (!A_MN) {
+            tma_load_2d(smem_a + s * kABytes, &map_a, &full[s], k_elem, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < kBlockM / kMnElems; ++c)
+              tma_load_2d(smem_a + s * kABytes + c * kChunkBytes, &map_a, &full[s], m0 + c * kMnElems, k_elem);
+          }
+          if (!B_MN) {
+            tma_load_2d(smem_b + s * kBBytes, &map_b, &full[s], k_elem, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BLOCK_N / kMnElems; ++c)
+              tma_load_2d(smem_b + s * kBBytes + c * kChunkBytes, &map_b, &full[s], n0 + c * kMnElems, k_elem);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: accumulator `acc` alternates between the two TMEM halves =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
+      constexpr bool kBase32 = KIND == 1;
+      uint32_t it = 0, tc = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
+        const int z = t / (tiles_m * tiles_n);
+        const int kb_begin = z * k_blocks_per_split, kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
+        const uint32_t acc = tc & 1, acc_phase = (tc >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);      // the epilogue has drained this half
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(&full[s], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), A_MN ? kChunkBytes : 16,
+                                             (A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
+          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16,
+                                             (B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma<KIND>(d_tmem, da + kStepA * k, db + kStepB * k, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tmem_full[acc]);
+      }
+    }
+  } else {
+    // ===== epilogue warps =====
+    uint32_t tc = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
+      const int m0 = (t % tiles_m) * kBlockM, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+      const uint32_t acc = tc & 1, acc_phase = (tc >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      drain_tile<BLOCK_N>(tmem_base + acc * BLOCK_N, true, stage_base, warp, lane, C, M, N, ldc, m0, n0, z, epi);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);       // 4 arrivals (one per epilogue warp) free the half
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * BLOCK_N) : "memory");
   }
 }
 

@@ -267,7 +267,7 @@ static int prepare_maps(tfg_job* j, int slot) {
     TcGemm& f = s.fwd[i];
     f.name = "rn conv fwd"; f.M = (int)M; f.N = u.kout; f.K = rsc; f.C = nullptr; f.ldc = u.kout; f.block_n = bn;
     f.splits = 1; f.a_mn = false; f.b_mn = true;
-    f.epi = tc::Epilogue{nullptr, nullptr, 0, s.data[u.z]};
+    f.epi = tc::Epilogue{nullptr, nullptr, 0, s.data[u.z], 0};
     if ((rc = make_map(&f.a, kind, a_ptr, M, rsc, a_ld, tc::kBlockM, false))) return rc;
     if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
     // wgrad: dW = col^T x dz
@@ -285,7 +285,7 @@ static int prepare_maps(tfg_job* j, int slot) {
       d.name = "rn conv dgrad"; d.M = (int)M; d.N = rsc; d.K = u.kout; d.C = nullptr; d.block_n = bnd; d.splits = 1;
       d.a_mn = false; d.b_mn = false;
       d.ldc = u.direct ? u.g.C : u.g.Kp;
-      d.epi = tc::Epilogue{nullptr, nullptr, 0, nullptr};   // out_bf16 chosen per call (grad buffer or staging)
+      d.epi = tc::Epilogue{nullptr, nullptr, 0, nullptr, 0};   // out_bf16 chosen per call (grad buffer or staging)
       if ((rc = make_map(&d.a, kind, s.grad[u.z], M, u.kout, u.kout, tc::kBlockM, false))) return rc;
       if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
     }
@@ -294,7 +294,7 @@ static int prepare_maps(tfg_job* j, int slot) {
   TcGemm& ff = s.fc_fwd;
   ff.name = "rn fc fwd"; ff.M = B; ff.N = NC; ff.K = 2048; ff.C = s.logits; ff.ldc = NC; ff.block_n = 128; ff.splits = 1;
   ff.a_mn = false; ff.b_mn = true;
-  ff.epi = tc::Epilogue{j->params + j->vars[m->v_fcb].offset, nullptr, 0, nullptr};
+  ff.epi = tc::Epilogue{j->params + j->vars[m->v_fcb].offset, nullptr, 0, nullptr, 0};
   if ((rc = make_map(&ff.a, kind, s.pooled, B, 2048, 2048, tc::kBlockM, false))) return rc;
   if ((rc = make_map(&ff.b, kind, wlp(m->v_fcw), NC, 2048, NC, 128, true))) return rc;
   TcGemm& fw = s.fc_wgrad;
@@ -305,7 +305,7 @@ static int prepare_maps(tfg_job* j, int slot) {
   TcGemm& fd = s.fc_dgrad;
   fd.name = "rn fc dgrad"; fd.M = B; fd.N = 2048; fd.K = NC; fd.C = nullptr; fd.ldc = 2048; fd.block_n = 128; fd.splits = 1;
   fd.a_mn = false; fd.b_mn = false;
-  fd.epi = tc::Epilogue{nullptr, nullptr, 0, s.dpooled};
+  fd.epi = tc::Epilogue{nullptr, nullptr, 0, s.dpooled, 0};
   if ((rc = make_map(&fd.a, kind, s.dlogits, B, NC, NC, tc::kBlockM, false))) return rc;
   if ((rc = make_map(&fd.b, kind, wlp(m->v_fcw), 2048, NC, NC, 128, false))) return rc;
   s.maps_ready = true;

@@ -11,7 +11,7 @@ struct TcGemm {
   float* partial = nullptr;    // [splits][M][N] when splits > 1
   int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
   bool a_mn = false, b_mn = false;
-  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr};
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 0};
   const char* name = "gemm";
 };
 
