@@ -1,0 +1,34 @@
+// Host-side interface of the implicit-GEMM convolutions (conv_tc.cu).
+#pragma once
+#include "common.cuh"
+#include "conv_tc.cuh"
+
+namespace tfg {
+
+struct ConvGemm {              // forward (b_mn) or stride-1 data gradient (!b_mn)
+  CUtensorMap a, b;
+  tc::ConvShape cs;
+  float* C = nullptr;          // fp32 output, or NULL when epi.out_bf16 is set
+  int N = 0, ldc = 0, block_n = 128, b_rows_per_tap = 0;
+  bool b_mn = true;
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 1};
+  const char* name = "conv";
+};
+
+struct ConvWgrad {
+  CUtensorMap x, dz;
+  tc::ConvShape cs;
+  float* C = nullptr;          // [M, N] fp32
+  float* partial = nullptr;    // [splits][M][N]
+  int M = 0, N = 0, block_n = 128, splits = 1;
+  const char* name = "conv wgrad";
+};
+
+int make_map_4d(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride);
+void pick_conv_tile(int Nimg, int OH, int OW, bool rows_mult16, int* TN, int* TH);
+void fill_conv_shape(tc::ConvShape* cs, int Nimg, int OH, int OW, int TN, int TH, int R, int S, int stride, int pad,
+                     int C, int flip);
+int launch_conv_gemm(tfg_job* j, const ConvGemm& g, cudaStream_t s);
+int launch_conv_wgrad(tfg_job* j, const ConvWgrad& g, cudaStream_t s);
+
+}  // namespace tfg

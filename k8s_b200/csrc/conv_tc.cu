@@ -1,0 +1,148 @@
+// Host side of the implicit-GEMM convolutions (conv_tc.cuh): 4-D tensor maps, tile shapes, launches.
+#include <cudaTypedefs.h>
+
+#include <algorithm>
+
+#include "conv_host.cuh"
+
+namespace tfg {
+
+static PFN_cuTensorMapEncodeTiled encode_fn() {
+  static PFN_cuTensorMapEncodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &st) == cudaSuccess &&
+        st == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+  }
+  return fn;
+}
+
+// bf16 NHWC tensor [N, H, W, C]; box = {64 channels, bw columns, bh rows, bn images} visited with
+// element strides {1, stride, stride, 1} (so the box spans bw*stride x bh*stride input positions).
+int make_map_4d(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride) {
+  PFN_cuTensorMapEncodeTiled enc = encode_fn();
+  if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (C * 2) % 16 != 0)
+    return fail(nullptr, TFG_EINVAL, "activation tensor must be 16-byte aligned with C a multiple of 8");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)(bw * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  if (box[1] > 256 || box[2] > 256 || box[3] > 256) return fail(nullptr, TFG_ELIMIT, "TMA box dimension above 256");
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled(4d) failed with CUresult " + std::to_string((int)r));
+  return TFG_OK;
+}
+
+// Tile of the pixel space: TN images x TH rows x OW columns, at most 128 pixels.  rows_mult16: the
+// pixel count must be a multiple of 16 (wgrad: pixels are the K dimension); rows past the image are
+// then allowed (the TMA unit zero-fills them).
+void pick_conv_tile(int Nimg, int OH, int OW, bool rows_mult16, int* TN, int* TH) {
+  if (!rows_mult16) {
+    if (OH * OW <= 64) { *TH = OH; *TN = std::max(1, std::min(Nimg, 128 / (OH * OW))); }
+    else { *TN = 1; *TH = std::max(1, std::min(OH, 128 / OW)); }
+    return;
+  }
+  int best = 0, btn = 1, bth = 1;
+  for (int tn = 1; tn <= 64; ++tn)
+    for (int th = 1; th <= 128; ++th) {
+      if (tn > 1 && th < OH) continue;                 // several images only when a box holds whole images
+      if (tn == 1 && th > OH + 15) continue;
+      const int p = tn * th * OW;
+      if (p > 128 || p % 16) continue;
+      // prefer more valid pixels per box, then fewer wasted rows
+      const int valid = tn * std::min(th, OH) * OW;
+      if (valid > best) { best = valid; btn = tn; bth = th; }
+    }
+  *TN = btn;
+  *TH = bth;
+}
+
+void fill_conv_shape(tc::ConvShape* cs, int Nimg, int OH, int OW, int TN, int TH, int R, int S, int stride, int pad,
+                     int C, int flip) {
+  cs->Nimg = Nimg; cs->OH = OH; cs->OW = OW; cs->TN = TN; cs->TH = TH;
+  cs->h_tiles = (OH + TH - 1) / TH;
+  cs->m_tiles = ((Nimg + TN - 1) / TN) * cs->h_tiles;
+  cs->R = R; cs->S = S; cs->stride = stride; cs->pad = pad; cs->C = C; cs->flip = flip;
+}
+
+__global__ void __launch_bounds__(256)
+conv_splitk_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, long long mn) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= mn) return;
+  float s = 0.f;
+  for (int z = 0; z < splits; ++z) s += partial[z * mn + i];   // fixed order: deterministic
+  out[i] = s;
+}
+
+template <int BN, bool B_MN>
+static cudaError_t launch_cg(const ConvGemm& g, cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_conv<BN>();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::conv_gemm_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int tiles_n = (g.N + BN - 1) / BN;
+  const long long total = (long long)g.cs.m_tiles * tiles_n;
+  const int grid = (int)std::min<long long>(total, kNumSMs);
+  tc::Epilogue epi = g.epi;
+  epi.direct = 1;
+  tc::conv_gemm_kernel<BN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, g.C, g.cs, g.N, g.ldc, tiles_n,
+                                                                  g.b_rows_per_tap, epi);
+  return cudaGetLastError();
+}
+
+int launch_conv_gemm(tfg_job* j, const ConvGemm& g, cudaStream_t s) {
+  cudaError_t e;
+  if (g.b_mn) e = g.block_n == 64 ? launch_cg<64, true>(g, s) : launch_cg<128, true>(g, s);
+  else e = g.block_n == 64 ? launch_cg<64, false>(g, s) : launch_cg<128, false>(g, s);
+  if (j) prof_mark(j, g.name);
+  if (e != cudaSuccess) return fail_cuda(j, e, g.name);
+  return TFG_OK;
+}
+
+template <int BN>
+static cudaError_t launch_cw(const ConvWgrad& g, float* dst, int splits, int k_tiles, int ktps, cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_wgrad<BN>();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::conv_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int tiles_m = (g.M + 127) / 128, tiles_n = (g.N + BN - 1) / BN;
+  const long long total = (long long)tiles_m * tiles_n * splits;
+  const int grid = (int)std::min<long long>(total, kNumSMs);
+  tc::conv_wgrad_kernel<BN><<<grid, tc::kThreads, smem, s>>>(g.x, g.dz, dst, g.cs, g.M, g.N, g.N, tiles_m, tiles_n, splits,
+                                                             k_tiles, ktps);
+  return cudaGetLastError();
+}
+
+int launch_conv_wgrad(tfg_job* j, const ConvWgrad& g, cudaStream_t s) {
+  const int k_tiles = g.cs.m_tiles;
+  int splits = std::max(1, std::min(g.splits, k_tiles));
+  const int ktps = (k_tiles + splits - 1) / splits;
+  splits = (k_tiles + ktps - 1) / ktps;
+  float* dst = splits > 1 ? g.partial : g.C;
+  cudaError_t e = g.block_n == 64 ? launch_cw<64>(g, dst, splits, k_tiles, ktps, s)
+                                  : launch_cw<128>(g, dst, splits, k_tiles, ktps, s);
+  if (j) prof_mark(j, g.name);
+  if (e != cudaSuccess) return fail_cuda(j, e, g.name);
+  if (splits > 1) {
+    const long long mn = (long long)g.M * g.N;
+    conv_splitk_reduce_kernel<<<(int)((mn + 255) / 256), 256, 0, s>>>(g.partial, g.C, splits, mn);
+    if (j) prof_mark(j, "split-K reduce");
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail_cuda(j, e, "conv_splitk_reduce_kernel");
+  }
+  return TFG_OK;
+}
+
+}  // namespace tfg

@@ -1,0 +1,315 @@
+// Implicit-GEMM convolutions on tcgen05: the im2col matrix is never materialised.  The A operand of
+// each K block is fetched by ONE 4-D TMA box over the NHWC activation -- {64 channels, TW columns,
+// TH rows, TN images} at the coordinates of filter tap (r, s), element strides = convolution
+// stride, out-of-bounds (padding) zero-filled by the TMA unit -- and lands in shared memory as the
+// K-major (forward / dgrad) or MN-major (wgrad) 128-byte-swizzled tile tcgen05.mma reads.
+//
+//   forward  z[pix, k]      = sum_{r,s,c} x[pix + (r,s), c] * W[(r,s,c), k]        A = x boxes, B = W MN-major
+//   dgrad    dx[pix, c]     = sum_{r,s,k} dz[pix - (r,s), k] * W[(r,s,c), k]       A = dz boxes, B = W K-major  (stride 1)
+//   wgrad    dW[(r,s,c), k] = sum_{pix}   x[pix + (r,s), c] * dz[pix, k]           A = x boxes (MN), B = dz boxes (MN)
+//
+// A tile of output pixels is TN images x TH rows x the full row width (TW = OW), at most 128, so its
+// rows are contiguous rows of the [pixels, channels] output and the GEMM epilogue applies unchanged.
+// Persistent CTAs, 4-stage (3 for wgrad) TMA ring, two TMEM accumulators (see gemm_tc.cuh).
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace tfg {
+namespace tc {
+
+struct ConvShape {
+  int Nimg, OH, OW;          // extent of the pixel space the tiles walk (output for fwd/wgrad, input for dgrad)
+  int TN, TH;                // tile = TN images x TH rows x OW columns
+  int h_tiles, m_tiles;      // ceil(OH / TH), img_groups * h_tiles
+  int R, S, stride, pad;
+  int C;                     // channels of the gathered tensor (K dimension per tap), multiple of 64
+  int flip;                  // 0: tap offset (+r - pad, +s - pad) scaled by stride (forward / wgrad); 1: (pad - r, pad - s) (dgrad)
+};
+
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+         "r"(c3)
+      : "memory");
+}
+
+__device__ __forceinline__ void conv_tile_origin(const ConvShape& cs, int mt, int* n0, int* h0) {
+  *n0 = (mt / cs.h_tiles) * cs.TN;
+  *h0 = (mt % cs.h_tiles) * cs.TH;
+}
+
+template <int BLOCK_N>
+constexpr size_t smem_bytes_conv() {
+  return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
+         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+}
+
+// ---- forward (B_MN = true) and stride-1 data gradient (B_MN = false) ---------------------------------
+// map_a: 4-D map over the gathered activation [Nimg_in, H_in, W_in, C], box {64, TW*stride, TH*stride, TN}.
+// map_b: 2-D map over W viewed [R*S*C_w, Kout]: forward reads it MN-major (rows = K), dgrad K-major (rows = N).
+// Output [pixels, N] row-major (bf16 through epi.out_bf16, or fp32 C), ldc = N.
+template <int BLOCK_N, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int N, int ldc, int tiles_n,
+                 int b_rows_per_tap, Epilogue epi) {
+  constexpr int kStages = kMaxStages;
+  constexpr int kBlockK = 64;                                   // bf16 elements of K per stage = one channel block
+  constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
+  constexpr int kChunkBytes = kBlockK * 128;
+  constexpr uint32_t kStepB = B_MN ? (16 * 128) >> 4 : 32 >> 4;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kABytes + kBBytes));
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = cs.m_tiles * tiles_n;
+  const int cblocks = cs.C / 64;
+  const int k_blocks = cs.R * cs.S * cblocks;
+  const int box_rows = cs.TN * cs.TH * cs.OW;                   // rows one A box writes (<= 128)
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(smem_u32(tmem_slot)), "n"(2 * BLOCK_N) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int mt = t % cs.m_tiles, n0 = (t / cs.m_tiles) * BLOCK_N;
+        int img0, h0;
+        conv_tile_origin(cs, mt, &img0, &h0);
+        for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          const int tap = kb / cblocks, cb = kb - tap * cblocks;
+          const int r = tap / cs.S, sx = tap - r * cs.S;
+          mbar_wait(&empty[s], phase ^ 1);
+          mbar_expect_tx(&full[s], box_rows * 128 + kBBytes);
+          const int ch = cs.flip ? cs.pad - r : r - cs.pad, cw = cs.flip ? cs.pad - sx : sx - cs.pad;
+          tma_load_4d(smem_a + s * kABytes, &map_a, &full[s], cb * 64, cw, h0 * cs.stride + ch, img0);
+          const int krow = tap * b_rows_per_tap;                // first row of this tap in W viewed [R*S*C_w, Kout]
+          if (B_MN) {                                           // rows = K (channel block of the tap), columns = n
+#pragma unroll
+            for (int c = 0; c < BLOCK_N / 64; ++c)
+              tma_load_2d(smem_b + s * kBBytes + c * kChunkBytes, &map_b, &full[s], n0 + c * 64, krow + cb * 64);
+          } else {                                              // rows = n (input channel c of the tap), columns = K
+            tma_load_2d(smem_b + s * kBBytes, &map_b, &full[s], cb * 64, krow + n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
+      uint32_t it = 0, tcnt = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(&full[s], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), 16);
+          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma<0>(d_tmem, da + 2 * k, db + kStepB * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tmem_full[acc]);
+      }
+    }
+  } else {
+    uint32_t tcnt = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+      const int mt = t % cs.m_tiles, n0 = (t / cs.m_tiles) * BLOCK_N;
+      int img0, h0;
+      conv_tile_origin(cs, mt, &img0, &h0);
+      const long long m_start = ((long long)img0 * cs.OH + h0) * cs.OW;
+      const int valid = (cs.TN > 1 ? min(cs.TN, cs.Nimg - img0) * cs.OH : min(cs.TH, cs.OH - h0)) * cs.OW;
+      const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      // rows of the tile are rows m_start .. m_start + valid of the [pixels, N] output
+      float* cb = Cout ? Cout + m_start * ldc : nullptr;
+      Epilogue e = epi;
+      if (e.out_bf16) e.out_bf16 = static_cast<__nv_bfloat16*>(e.out_bf16) + m_start * ldc;
+      drain_tile<BLOCK_N>(tmem_base + acc * BLOCK_N, true, stage_base, warp, lane, cb, valid, N, ldc, 0, n0, 0, e);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * BLOCK_N) : "memory");
+  }
+}
+
+// ---- weight gradient ---------------------------------------------------------------------------------
+// dW[(r,s,c), k] = sum over pixels.  The pixel tiles are the K dimension: both operands are MN-major
+// boxes of P = TN*TH*OW pixel rows (P a multiple of 16, rows past the image zero-filled):
+//   A chunk j (64 rows of dW = 64 channels of one tap): box of x at the tap's offset,
+//   B chunk j (64 output channels):                      box of dz.
+// Tiles = (128 rows of dW) x (BLOCK_N output channels) x split z over the pixel tiles; fp32 partials
+// go to C + z*M*ldc and are reduced in order by splitk_reduce_kernel.
+constexpr int kWgradStages = 3;
+
+template <int BLOCK_N>
+constexpr size_t smem_bytes_wgrad() {
+  return 1024 + static_cast<size_t>(kWgradStages) * (2 * 128 * 128 + (BLOCK_N / 64) * 128 * 128) +
+         (2 * kWgradStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+}
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dz,
+                  float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int M, int N, int ldc, int tiles_m,
+                  int tiles_n, int splits, int k_tiles, int k_tiles_per_split) {
+  constexpr int kStages = kWgradStages;
+  constexpr int kAStage = 2 * 128 * 128, kBStage = (BLOCK_N / 64) * 128 * 128;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kAStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kAStage + kBStage));
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = tiles_m * tiles_n * splits;
+  const int P = cs.TN * cs.TH * cs.OW;                 // pixel rows per box: the K extent of one stage
+  const int chunk_bytes = P * 128;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_dz)) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(smem_u32(tmem_slot)), "n"(2 * BLOCK_N) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = (t % tiles_m) * 128, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+        const int kt_begin = z * k_tiles_per_split, kt_end = min(k_tiles, kt_begin + k_tiles_per_split);
+        const int a_chunks = (m0 + 64 < M) ? 2 : 1;          // the last row tile of dW may hold one chunk only
+        for (int kt = kt_begin; kt < kt_end; ++kt, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          int img0, h0;
+          conv_tile_origin(cs, kt, &img0, &h0);
+          mbar_wait(&empty[s], phase ^ 1);
+          mbar_expect_tx(&full[s], (a_chunks + BLOCK_N / 64) * chunk_bytes);
+          for (int c = 0; c < a_chunks; ++c) {
+            const int row = m0 + c * 64;                       // flattened (tap, channel) row of dW
+            const int tap = row / cs.C, c0 = row - tap * cs.C;
+            const int r = tap / cs.S, sx = tap - r * cs.S;
+            tma_load_4d(smem_a + s * kAStage + c * chunk_bytes, &map_x, &full[s], c0, sx - cs.pad,
+                        h0 * cs.stride + r - cs.pad, img0);
+          }
+#pragma unroll
+          for (int c = 0; c < BLOCK_N / 64; ++c)
+            tma_load_4d(smem_b + s * kBStage + c * chunk_bytes, &map_dz, &full[s], n0 + c * 64, 0, h0, img0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, true, true);
+      uint32_t it = 0, tcnt = 0;
+      const int k_steps = P / 16;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+        const int z = t / (tiles_m * tiles_n);
+        const int kt_begin = z * k_tiles_per_split, kt_end = min(k_tiles, kt_begin + k_tiles_per_split);
+        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kt = kt_begin; kt < kt_end; ++kt, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(&full[s], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kAStage), chunk_bytes);
+          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBStage), chunk_bytes);
+          for (int k = 0; k < k_steps; ++k)                   // 16 pixel rows = 2048 B per instruction
+            umma<0>(d_tmem, da + 128u * k, db + 128u * k, idesc, (kt > kt_begin || k > 0) ? 1u : 0u);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tmem_full[acc]);
+      }
+    }
+  } else {
+    uint32_t tcnt = 0;
+    const Epilogue e = {nullptr, nullptr, 0, nullptr, 1};
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+      const int m0 = (t % tiles_m) * 128, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+      const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      drain_tile<BLOCK_N>(tmem_base + acc * BLOCK_N, true, stage_base, warp, lane, Cout, M, N, ldc, m0, n0, z, e);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * BLOCK_N) : "memory");
+  }
+}
+
+}  // namespace tc
+}  // namespace tfg

@@ -18,6 +18,7 @@
 
 #include "common.cuh"
 #include "resnet_kernels.cuh"
+#include "conv_host.cuh"
 #include "tc_host.cuh"
 
 namespace tfg {
@@ -35,7 +36,8 @@ struct RnUnit {                      // conv + batch norm (+ residual add) (+ re
   rn::ConvGeom g;
   int kout = 0;
   int in = -1, res = -1, z = -1, y = -1;   // tensor ids
-  bool relu = true, direct = false;        // direct: 1x1 stride 1, no im2col
+  bool relu = true, direct = false;        // direct: 1x1 stride 1, the activation itself is the GEMM operand
+  bool implicit = false;                   // implicit GEMM through 4-D TMA boxes (C % 64 == 0): no im2col either
   int v_w = -1, v_gamma = -1, v_beta = -1;
   float *mov_mean = nullptr, *mov_var = nullptr;   // per job
 };
@@ -51,7 +53,9 @@ struct RnSlot {
   float *bn_partial = nullptr, *splitk = nullptr;
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
   bf16 *pooled = nullptr, *dpooled = nullptr, *dlogits = nullptr;
-  std::vector<TcGemm> fwd, wgrad, dgrad;   // per unit
+  std::vector<TcGemm> fwd, wgrad, dgrad;   // per unit (explicit-operand GEMMs)
+  std::vector<ConvGemm> ifwd, idgrad;      // per unit (implicit GEMM)
+  std::vector<ConvWgrad> iwgrad;
   TcGemm fc_fwd, fc_wgrad, fc_dgrad;
   bool maps_ready = false;
 };
@@ -106,6 +110,7 @@ static int add_unit(tfg_job* j, ResnetModel* m, const std::string& name, int in,
   u.g.Kp = (R * R * u.g.C + 7) / 8 * 8;
   u.kout = kout; u.in = in; u.res = res; u.relu = relu;
   u.direct = (R == 1 && stride == 1);
+  u.implicit = !u.direct && (x.c % 64 == 0) && getenv("TFGRAFT_NO_IMPLICIT") == nullptr;
   u.z = add_tensor(m, name + "/z", x.n, u.g.OH, u.g.OW, kout);
   u.y = add_tensor(m, name + "/y", x.n, u.g.OH, u.g.OW, kout);
   int dummy;
@@ -196,7 +201,8 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     s.col.assign(m->units.size(), nullptr);
     for (size_t u = 0; u < m->units.size(); ++u) {
       const RnUnit& un = m->units[u];
-      if (!un.direct) alloc((void**)&s.col[u], sizeof(bf16) * (size_t)un.g.N * un.g.OH * un.g.OW * un.g.Kp);
+      if (!un.direct && !un.implicit)
+        alloc((void**)&s.col[u], sizeof(bf16) * (size_t)un.g.N * un.g.OH * un.g.OW * un.g.Kp);
     }
     alloc((void**)&s.dcol, sizeof(bf16) * m->col_elems);
     alloc((void**)&s.pool_arg, (size_t)m->tensors[m->t_pool_out].elems());
@@ -255,12 +261,51 @@ static int prepare_maps(tfg_job* j, int slot) {
   s.fwd.assign(nu, TcGemm());
   s.wgrad.assign(nu, TcGemm());
   s.dgrad.assign(nu, TcGemm());
+  s.ifwd.assign(nu, ConvGemm());
+  s.idgrad.assign(nu, ConvGemm());
+  s.iwgrad.assign(nu, ConvWgrad());
   int rc;
   for (size_t i = 0; i < nu; ++i) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
     const int rsc = u.g.R * u.g.S * u.g.C;
-    const void* a_ptr = u.direct ? static_cast<const void*>(s.data[u.in]) : static_cast<const void*>(s.col[i]);
+    if (u.implicit) {
+      const int bn = u.kout >= 128 ? 128 : 64;
+      int tn, th;
+      // forward: tiles of output pixels, A = boxes of the input at each tap
+      ConvGemm& f = s.ifwd[i];
+      pick_conv_tile(u.g.N, u.g.OH, u.g.OW, false, &tn, &th);
+      fill_conv_shape(&f.cs, u.g.N, u.g.OH, u.g.OW, tn, th, u.g.R, u.g.S, u.g.stride, u.g.pad, u.g.C, 0);
+      f.name = "rn conv fwd (implicit)"; f.N = u.kout; f.ldc = u.kout; f.block_n = bn; f.b_mn = true;
+      f.b_rows_per_tap = u.g.C; f.C = nullptr;
+      f.epi = tc::Epilogue{nullptr, nullptr, 0, s.data[u.z], 1};
+      if ((rc = make_map_4d(&f.a, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.OW, th, tn, u.g.stride))) return rc;
+      if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
+      // weight gradient: pixel tiles are the K dimension
+      ConvWgrad& w = s.iwgrad[i];
+      pick_conv_tile(u.g.N, u.g.OH, u.g.OW, true, &tn, &th);
+      fill_conv_shape(&w.cs, u.g.N, u.g.OH, u.g.OW, tn, th, u.g.R, u.g.S, u.g.stride, u.g.pad, u.g.C, 0);
+      const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
+      w.name = "rn conv wgrad (implicit)"; w.M = rsc; w.N = u.kout; w.block_n = bn; w.C = grd(u.v_w); w.partial = s.splitk;
+      w.splits = (int)std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
+      if ((rc = make_map_4d(&w.x, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.OW, th, tn, u.g.stride))) return rc;
+      if ((rc = make_map_4d(&w.dz, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.OW, th, tn, 1))) return rc;
+      // data gradient, stride 1: tiles of input pixels, A = boxes of dz at the mirrored tap offsets
+      if (u.g.stride == 1) {
+        ConvGemm& d = s.idgrad[i];
+        const int bnd = u.g.C >= 128 ? 128 : 64;
+        pick_conv_tile(u.g.N, u.g.H, u.g.W, false, &tn, &th);
+        fill_conv_shape(&d.cs, u.g.N, u.g.H, u.g.W, tn, th, u.g.R, u.g.S, 1, u.g.pad, u.kout, 1);
+        d.name = "rn conv dgrad (implicit)"; d.N = u.g.C; d.ldc = u.g.C; d.block_n = bnd; d.b_mn = false;
+        d.b_rows_per_tap = u.g.C; d.C = nullptr;
+        d.epi = tc::Epilogue{nullptr, nullptr, 0, nullptr, 1};   // out_bf16 chosen per call
+        if ((rc = make_map_4d(&d.a, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.W, th, tn, 1))) return rc;
+        if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
+      }
+    }
+    // explicit-operand descriptors: direct units, the stem, and the stride-2 data gradients
+    const void* a_ptr = u.direct ? static_cast<const void*>(s.data[u.in])
+                                 : (u.implicit ? static_cast<const void*>(s.dcol) : static_cast<const void*>(s.col[i]));
     const long long a_ld = u.direct ? u.g.C : u.g.Kp;
     const int bn = u.kout >= 128 ? 128 : 64;
     // forward: z = col x W
@@ -359,8 +404,12 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
   for (size_t i = 0; i < m->units.size(); ++i) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
-    if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col[i]))) return rc;
-    if ((rc = launch_tc(j, s.fwd[i], TFG_MATH_BF16, st))) return rc;
+    if (u.implicit) {
+      if ((rc = launch_conv_gemm(j, s.ifwd[i], st))) return rc;
+    } else {
+      if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col[i]))) return rc;
+      if ((rc = launch_tc(j, s.fwd[i], TFG_MATH_BF16, st))) return rc;
+    }
     int chunks, rows;
     bn_chunks(M, &chunks, &rows);
     rn::bn_stats_kernel<<<dim3((u.kout + 63) / 64, chunks), 256, 0, st>>>(s.data[u.z], s.bn_partial, M, u.kout, rows);
@@ -431,12 +480,24 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
         s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M, u.relu ? 1 : 0);
     RN_OK(j, "rn bn bwd apply");
     // weight gradient: the im2col operand is the one the forward pass built
-    if ((rc = launch_tc(j, s.wgrad[i], TFG_MATH_BF16, st))) return rc;
+    if (u.implicit) {
+      if ((rc = launch_conv_wgrad(j, s.iwgrad[i], st))) return rc;
+    } else if ((rc = launch_tc(j, s.wgrad[i], TFG_MATH_BF16, st))) {
+      return rc;
+    }
     if (u.in == m->t_image) continue;
     // data gradient
     TcGemm d = s.dgrad[i];
     const long long in_elems = m->tensors[u.in].elems();
-    if (u.direct) {
+    if (u.implicit && u.g.stride == 1) {
+      ConvGemm dg = s.idgrad[i];
+      dg.epi.out_bf16 = written[u.in] ? s.dcol : s.grad[u.in];
+      if ((rc = launch_conv_gemm(j, dg, st))) return rc;
+      if (written[u.in]) {
+        rn::add_bf16_kernel<<<grid_for(in_elems / 8), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
+        RN_OK(j, "rn grad add");
+      }
+    } else if (u.direct) {
       if (!written[u.in]) {
         d.epi.out_bf16 = s.grad[u.in];
         if ((rc = launch_tc(j, d, TFG_MATH_BF16, st))) return rc;
