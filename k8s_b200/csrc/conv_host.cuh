@@ -7,11 +7,13 @@ namespace tfg {
 
 struct ConvGemm {              // forward (b_mn) or stride-1 data gradient (!b_mn)
   CUtensorMap a, b;
+  CUtensorMap c;               // bf16 output [Nimg, OH, OW, N], box {64, OW, TH, TN} (make_map_4d, stride 1); used when tma_out != 0
+  int tma_out = 0;             // 1: TMA store, 2: TMA reduce-add into the output
   tc::ConvShape cs;
   float* C = nullptr;          // fp32 output, or NULL when epi.out_bf16 is set
   int N = 0, ldc = 0, block_n = 128, b_rows_per_tap = 0;
   bool b_mn = true;
-  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 1};
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 1, 0};
   const char* name = "conv";
 };
 

@@ -95,8 +95,9 @@ static cudaError_t launch_cg(const ConvGemm& g, cudaStream_t s) {
   const int grid = (int)std::min<long long>(total, kNumSMs);
   tc::Epilogue epi = g.epi;
   epi.direct = 1;
-  tc::conv_gemm_kernel<BN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, g.C, g.cs, g.N, g.ldc, tiles_n,
-                                                                  g.b_rows_per_tap, epi);
+  epi.tma_out = (g.tma_out && epi.out_bf16 && !epi.mask) ? g.tma_out : 0;
+  tc::conv_gemm_kernel<BN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, epi.tma_out ? g.c : g.a, g.C, g.cs, g.N,
+                                                                  g.ldc, tiles_n, g.b_rows_per_tap, epi);
   return cudaGetLastError();
 }
 

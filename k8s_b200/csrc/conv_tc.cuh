@@ -43,17 +43,20 @@ __device__ __forceinline__ void conv_tile_origin(const ConvShape& cs, int mt, in
 template <int BLOCK_N>
 constexpr size_t smem_bytes_conv() {
   return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float) +
+         1024 + 2 * (BLOCK_N / 64) * kOutHalfBytes;   // two bf16 output tile images for the TMA epilogue
 }
 
 // ---- forward (B_MN = true) and stride-1 data gradient (B_MN = false) ---------------------------------
 // map_a: 4-D map over the gathered activation [Nimg_in, H_in, W_in, C], box {64, TW*stride, TH*stride, TN}.
 // map_b: 2-D map over W viewed [R*S*C_w, Kout]: forward reads it MN-major (rows = K), dgrad K-major (rows = N).
-// Output [pixels, N] row-major (bf16 through epi.out_bf16, or fp32 C), ldc = N.
+// Output [pixels, N] row-major (bf16 through epi.out_bf16, or fp32 C), ldc = N; with epi.tma_out the
+// bf16 tile leaves through map_c, a 4-D map over the output tensor [Nimg, OH, OW, N] with box
+// {64, OW, TH, TN}: the same pixel tile as the A box, so rows past the image are clipped by the TMA unit.
 template <int BLOCK_N, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int N, int ldc, int tiles_n,
+                 const __grid_constant__ CUtensorMap map_c, float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int N, int ldc, int tiles_n,
                  int b_rows_per_tap, Epilogue epi) {
   constexpr int kStages = kMaxStages;
   constexpr int kBlockK = 64;                                   // bf16 elements of K per stage = one channel block
@@ -71,6 +74,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
+  uint8_t* out_stage = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(stage_base + 4 * 32 * 33) + 1023) & ~uintptr_t(1023));
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = cs.m_tiles * tiles_n;
@@ -157,6 +163,26 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const long long m_start = ((long long)img0 * cs.OH + h0) * cs.OW;
       const int valid = (cs.TN > 1 ? min(cs.TN, cs.Nimg - img0) * cs.OH : min(cs.TH, cs.OH - h0)) * cs.OW;
       const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+      if (epi.tma_out) {
+        uint8_t* img = out_stage + acc * kOutTileBytes;
+        if (warp == 2 && lane == 0) bulk_wait_read<1>();    // the store of two tiles ago has read this image
+        epi_barrier();
+        mbar_wait(&tmem_full[acc], acc_phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        drain_tile_staged<BLOCK_N>(tmem_base + acc * BLOCK_N, img, warp, lane, n0, epi);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        epi_barrier();
+        if (warp == 2 && lane == 0) {
+#pragma unroll
+          for (int h = 0; h < BLOCK_N / 64; ++h)
+            if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
+          bulk_commit();
+        }
+        continue;
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       // rows of the tile are rows m_start .. m_start + valid of the [pixels, N] output
@@ -168,6 +194,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
     }
+    if (epi.tma_out && warp == 2 && lane == 0) bulk_wait_all();   // shared memory must outlive the last store
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

@@ -98,7 +98,7 @@ static cudaError_t launch_persistent(const TcGemm& g, float* dst, int ldc, int k
   const long long total = (long long)tiles_m * tiles_n * splits;
   const int grid = (int)std::min<long long>(total, kNumSMs);
   tc::gemm_tc_persistent_kernel<BN, KIND, A_MN, B_MN><<<grid, tc::kThreads, smem, s>>>(
-      g.a, g.b, dst, g.M, g.N, ldc, k_blocks, kps, tiles_m, tiles_n, splits, epi);
+      g.a, g.b, epi.tma_out ? g.c : g.a, dst, g.M, g.N, ldc, k_blocks, kps, tiles_m, tiles_n, splits, epi);
   return cudaGetLastError();
 }
 
@@ -125,7 +125,7 @@ static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_block
     min_kps = 1;
     if (const char* e = getenv("TFGRAFT_PERSISTENT_MIN_KPS")) min_kps = atoi(e);
   }
-  if ((persistent == 1 && ctas >= 2ll * kNumSMs && kps >= min_kps) || persistent == 2)
+  if ((persistent == 1 && ctas >= 2ll * kNumSMs && kps >= min_kps) || persistent == 2 || epi.tma_out)
     return launch_persistent<BN, KIND, A_MN, B_MN>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   int stages = kps <= 1 ? 1 : kps <= 3 ? 2 : 4;
   if (ctas >= 4ll * kNumSMs) stages = 1;
@@ -161,6 +161,12 @@ int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
     if (const char* e = getenv("TFGRAFT_EPI_DIRECT")) direct = atoi(e);
   }
   epi.direct = direct;
+  epi.tma_out = 0;
+  if (g.tma_out) {
+    if (splits > 1 || !g.epi.out_bf16 || g.epi.mask || kind != TFG_MATH_BF16)
+      return fail(j, TFG_EINVAL, "the TMA output path takes a bf16 output, no mask and no split-K");
+    epi.tma_out = g.tma_out;
+  }
   if (splits > 1 && g.epi.out_bf16) return fail(j, TFG_EINVAL, "split-K writes fp32 only");
   if (splits > 1 && (!g.partial || g.ldc != g.N))
     return fail(j, TFG_EINVAL, "split-K needs a partial buffer and a dense output");

@@ -35,6 +35,8 @@ struct Epilogue {
   int relu;
   void* out_bf16;       // when set, the result is stored as bf16 [M, ldc] here instead of fp32 in C
   int direct;           // 1: store straight from registers (thread = row), 0: via the smem transpose
+  int tma_out;          // persistent kernels, bf16 output through the kernel's output tensor map:
+                        // 1 = TMA store of the staged tile, 2 = TMA reduce-add into the destination
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -382,6 +384,88 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   }
 }
 
+// ---- bf16 output through TMA -----------------------------------------------------------------------
+// The register-direct stores write 16 B per lane into 32 different rows: one L1 wavefront and one
+// L2 request per lane, which caps the output-heavy GEMMs (1x1 convolutions that widen the channel
+// count) at about 40 % of HBM bandwidth.  Here the four epilogue warps pack the tile as bf16 into a
+// 128-byte-swizzled shared-memory image (row r, 16-byte piece j at r * 128 + ((j ^ (r & 7)) << 4):
+// conflict-free for thread = row) and ONE thread hands each 64-column half to the TMA unit, which
+// writes whole lines, clips rows / columns outside the tensor and can add into the destination
+// (bf16 add, one rounding -- what a separate accumulate kernel would do).
+constexpr int kOutHalfBytes = kBlockM * 128;   // 128 rows x 64 bf16
+
+__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1, bool add) {
+  if (add)
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+  else
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2,
+                                             int c3, bool add) {
+  if (add)
+    asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+  else
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+
+// TMEM accumulator -> bf16 tile image in `out_stage` (BLOCK_N / 64 halves of kOutHalfBytes);
+// bias and relu applied on the way.  Called by the four epilogue warps.
+template <int BLOCK_N>
+__device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* out_stage, int warp, int lane, int n0,
+                                                  const Epilogue& epi) {
+  const int q = warp & 3;
+  const int row = q * 32 + lane;
+#pragma unroll 1
+  for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+    uint32_t r[32];
+    const uint32_t taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c0);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    uint8_t* half = out_stage + (c0 >> 6) * kOutHalfBytes + row * 128;
+    const int j0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[u * 8 + k]);
+      if (epi.bias) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] += epi.bias[n0 + c0 + u * 8 + k];
+      }
+      if (epi.relu) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+      }
+      uint4 pk;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+      *reinterpret_cast<uint4*>(half + (((j0 + u) ^ (row & 7)) << 4)) = pk;
+    }
+  }
+}
+
 // ---- persistent variant ----------------------------------------------------------------------------
 // One CTA per SM walks the tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA ring keeps
 // running across tile boundaries and the accumulator is double-buffered in TMEM (2 x BLOCK_N
@@ -394,13 +478,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 template <int BLOCK_N>
 constexpr size_t smem_bytes_persistent() {
   return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float);
+         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float) +
+         1024 + 2 * (BLOCK_N / 64) * kOutHalfBytes;   // two bf16 output tile images for the TMA epilogue
 }
 
 template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                          float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
+                          const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
                           int tiles_m, int tiles_n, int splits, Epilogue epi) {
   constexpr int kStages = kMaxStages;
   constexpr int kElemBytes = KIND == 0 ? 2 : 4;
@@ -423,6 +508,9 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
+  uint8_t* out_stage = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(stage_base + 4 * 32 * 33) + 1023) & ~uintptr_t(1023));
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = tiles_m * tiles_n * splits;
@@ -513,6 +601,26 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
       const int m0 = (t % tiles_m) * kBlockM, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
       const uint32_t acc = tc & 1, acc_phase = (tc >> 1) & 1;
+      if (epi.tma_out) {
+        uint8_t* img = out_stage + acc * kOutTileBytes;
+        if (warp == 2 && lane == 0) bulk_wait_read<1>();    // the store of two tiles ago has read this image
+        epi_barrier();
+        mbar_wait(&tmem_full[acc], acc_phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        drain_tile_staged<BLOCK_N>(tmem_base + acc * BLOCK_N, img, warp, lane, n0, epi);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        epi_barrier();
+        if (warp == 2 && lane == 0) {
+#pragma unroll
+          for (int h = 0; h < BLOCK_N / 64; ++h)
+            if (n0 + h * 64 < N) tma_store_2d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, m0, epi.tma_out == 2);
+          bulk_commit();
+        }
+        continue;
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       drain_tile<BLOCK_N>(tmem_base + acc * BLOCK_N, true, stage_base, warp, lane, C, M, N, ldc, m0, n0, z, epi);
@@ -520,6 +628,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);       // 4 arrivals (one per epilogue warp) free the half
     }
+    if (epi.tma_out && warp == 2 && lane == 0) bulk_wait_all();   // shared memory must outlive the last store
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

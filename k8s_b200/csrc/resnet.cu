@@ -51,6 +51,7 @@ struct RnSlot {
   bf16* dcol = nullptr;              // shared staging of data gradients
   uint8_t* pool_arg = nullptr;
   float *bn_partial = nullptr, *splitk = nullptr;
+  unsigned int* bn_done = nullptr;         // per 64-channel group: row chunks finished (self-resetting)
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
   bf16 *pooled = nullptr, *dpooled = nullptr, *dlogits = nullptr;
   std::vector<TcGemm> fwd, wgrad, dgrad;   // per unit (explicit-operand GEMMs)
@@ -77,6 +78,22 @@ static inline int grid_for(long long n, int per = 256) {
   return (int)std::max<long long>(b, 1);
 }
 
+// row chunks of the batch-norm reductions: about four resident blocks per SM over all channel
+// groups, at least 32 rows each
+constexpr int kBnTargetBlocks = kNumSMs * 4;
+constexpr size_t kBnPartialFloats = (size_t)(kBnTargetBlocks + 32) * 64;   // chunks * C never exceeds this
+
+// bf16 GEMM outputs leave through TMA stores / reduce-adds (TFGRAFT_TMA_OUT=0: register-direct stores
+// plus a separate accumulate kernel)
+static bool tma_out_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    on = 1;
+    if (const char* e = getenv("TFGRAFT_TMA_OUT")) on = atoi(e) != 0;
+  }
+  return on == 1;
+}
+
 #define RN_OK(j, what)                                           \
   do {                                                           \
     prof_mark((j), what);                                        \
@@ -101,6 +118,10 @@ static int reg(tfg_job* j, const std::string& name, std::vector<int64_t> shape, 
 static int add_unit(tfg_job* j, ResnetModel* m, const std::string& name, int in, int R, int stride, int kout, bool relu,
                     int res, int* rc) {
   const RnTensor x = m->tensors[in];
+  if (kout % 64 != 0 || 2048 % kout != 0) {   // the batch-norm kernels keep 8 fixed channels per thread
+    *rc = fail(j, TFG_EINVAL, "internal: " + name + " has " + std::to_string(kout) + " output channels; need a divisor of 2048 >= 64");
+    return -1;
+  }
   RnUnit u;
   u.name = name;
   u.g.N = (int)x.n; u.g.H = (int)x.h; u.g.W = (int)x.w; u.g.C = (int)x.c;
@@ -206,7 +227,9 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     }
     alloc((void**)&s.dcol, sizeof(bf16) * m->col_elems);
     alloc((void**)&s.pool_arg, (size_t)m->tensors[m->t_pool_out].elems());
-    alloc((void**)&s.bn_partial, sizeof(float) * 128 * 2 * (size_t)m->cmax);
+    alloc((void**)&s.bn_partial, sizeof(float) * 2 * kBnPartialFloats);
+    alloc((void**)&s.bn_done, sizeof(unsigned int) * 64);
+    if (e == cudaSuccess) e = cudaMemset(s.bn_done, 0, sizeof(unsigned int) * 64);
     alloc((void**)&s.splitk, sizeof(float) * m->splitk_floats);
     alloc((void**)&s.logits, sizeof(float) * (size_t)batch * classes);
     alloc((void**)&s.loss_vec, sizeof(float) * batch);
@@ -236,7 +259,7 @@ void resnet_destroy(tfg_job* j) {
     for (auto p : s.mean) cudaFree(p);
     for (auto p : s.invstd) cudaFree(p);
     for (auto p : s.col) cudaFree(p);
-    cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.splitk);
+    cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.bn_done); cudaFree(s.splitk);
     cudaFree(s.logits); cudaFree(s.loss_vec); cudaFree(s.pooled); cudaFree(s.dpooled); cudaFree(s.dlogits);
   }
   delete m;
@@ -281,6 +304,10 @@ static int prepare_maps(tfg_job* j, int slot) {
       f.epi = tc::Epilogue{nullptr, nullptr, 0, s.data[u.z], 1};
       if ((rc = make_map_4d(&f.a, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.OW, th, tn, u.g.stride))) return rc;
       if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
+      if (tma_out_enabled()) {
+        f.tma_out = 1;
+        if ((rc = make_map_4d(&f.c, s.data[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.OW, th, tn, 1))) return rc;
+      }
       // weight gradient: pixel tiles are the K dimension
       ConvWgrad& w = s.iwgrad[i];
       pick_conv_tile(u.g.N, u.g.OH, u.g.OW, true, &tn, &th);
@@ -301,6 +328,10 @@ static int prepare_maps(tfg_job* j, int slot) {
         d.epi = tc::Epilogue{nullptr, nullptr, 0, nullptr, 1};   // out_bf16 chosen per call
         if ((rc = make_map_4d(&d.a, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.W, th, tn, 1))) return rc;
         if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
+        if (tma_out_enabled()) {   // store or reduce-add (chosen per call) straight into the input's gradient
+          d.tma_out = 1;
+          if ((rc = make_map_4d(&d.c, s.grad[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.W, th, tn, 1))) return rc;
+        }
       }
     }
     // explicit-operand descriptors: direct units, the stem, and the stride-2 data gradients
@@ -315,6 +346,10 @@ static int prepare_maps(tfg_job* j, int slot) {
     f.epi = tc::Epilogue{nullptr, nullptr, 0, s.data[u.z], 0};
     if ((rc = make_map(&f.a, kind, a_ptr, M, rsc, a_ld, tc::kBlockM, false))) return rc;
     if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
+    if (tma_out_enabled()) {
+      f.tma_out = 1;
+      if ((rc = make_map(&f.c, kind, s.data[u.z], M, u.kout, u.kout, tc::kBlockM, false))) return rc;
+    }
     // wgrad: dW = col^T x dz
     TcGemm& w = s.wgrad[i];
     const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
@@ -333,6 +368,10 @@ static int prepare_maps(tfg_job* j, int slot) {
       d.epi = tc::Epilogue{nullptr, nullptr, 0, nullptr, 0};   // out_bf16 chosen per call (grad buffer or staging)
       if ((rc = make_map(&d.a, kind, s.grad[u.z], M, u.kout, u.kout, tc::kBlockM, false))) return rc;
       if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
+      if (tma_out_enabled()) {   // 1x1: into the input's gradient (store or reduce-add per call); else the dcol staging
+        d.tma_out = 1;
+        if ((rc = make_map(&d.c, kind, u.direct ? s.grad[u.in] : s.dcol, M, rsc, d.ldc, tc::kBlockM, false))) return rc;
+      }
     }
   }
   const int B = m->B, NC = m->classes;
@@ -363,7 +402,7 @@ static int run_im2col(tfg_job* j, const RnUnit& u, const bf16* in, bf16* col) {
   if (u.g.C % 8 == 0) {
     rn::im2col_kernel<8><<<grid_for(M * u.g.R * u.g.S * (u.g.C / 8)), 256, 0, j->stream>>>(in, col, u.g);
   } else {
-    rn::im2col_rows_kernel<<<grid_for(M * 32), 256, 0, j->stream>>>(in, col, u.g);
+    rn::im2col_rows_kernel<<<grid_for(M * (u.g.Kp / 8)), 256, 0, j->stream>>>(in, col, u.g);
     RN_OK(j, "rn im2col (thin)");
     return TFG_OK;
   }
@@ -375,8 +414,10 @@ static int run_im2col(tfg_job* j, const RnUnit& u, const bf16* in, bf16* col) {
   return TFG_OK;
 }
 
-static void bn_chunks(long long M, int* chunks, int* rows) {
-  int c = (int)std::max<long long>(1, std::min<long long>(128, (M + 63) / 64));
+static void bn_chunks(long long M, int C, int* chunks, int* rows) {
+  const int groups = C / 64;
+  int c = (kBnTargetBlocks + groups - 1) / groups;
+  c = (int)std::max<long long>(1, std::min<long long>(c, (M + 31) / 32));
   int r = (int)((M + c - 1) / c);
   *chunks = (int)((M + r - 1) / r);
   *rows = r;
@@ -411,13 +452,11 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
       if ((rc = launch_tc(j, s.fwd[i], TFG_MATH_BF16, st))) return rc;
     }
     int chunks, rows;
-    bn_chunks(M, &chunks, &rows);
-    rn::bn_stats_kernel<<<dim3((u.kout + 63) / 64, chunks), 256, 0, st>>>(s.data[u.z], s.bn_partial, M, u.kout, rows);
+    bn_chunks(M, u.kout, &chunks, &rows);
+    rn::bn_stats_kernel<<<dim3(u.kout / 64, chunks), 256, 0, st>>>(
+        s.data[u.z], s.bn_partial, s.bn_done, M, u.kout, rows, 1e-5f, 0.997f, s.mean[i], s.invstd[i],
+        update_moving ? u.mov_mean : nullptr, update_moving ? u.mov_var : nullptr);
     RN_OK(j, "rn bn stats");
-    rn::bn_finalize_kernel<<<(u.kout + 255) / 256, 256, 0, st>>>(s.bn_partial, chunks, u.kout, M, 1e-5f, 0.997f, s.mean[i],
-                                                               s.invstd[i], update_moving ? u.mov_mean : nullptr,
-                                                               update_moving ? u.mov_var : nullptr);
-    RN_OK(j, "rn bn finalize");
     rn::bn_apply_kernel<<<grid_for(M * u.kout / 8), 256, 0, st>>>(s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma),
                                                              par(u.v_beta), u.res >= 0 ? s.data[u.res] : nullptr,
                                                              s.data[u.y], M * u.kout, u.kout, u.relu ? 1 : 0);
@@ -465,20 +504,27 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     }
     if (!written[u.y]) return fail(j, TFG_ESTATE, "internal: gradient of " + u.name + "/y was never produced");
     int chunks, rows;
-    bn_chunks(M, &chunks, &rows);
-    rn::bn_bwd_stats_kernel<<<dim3((u.kout + 63) / 64, chunks), 256, 0, st>>>(
-        s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], s.bn_partial, M, u.kout, rows, u.relu ? 1 : 0);
-    RN_OK(j, "rn bn bwd stats");
-    rn::bn_bwd_finalize_kernel<<<(u.kout + 255) / 256, 256, 0, st>>>(s.bn_partial, chunks, u.kout, grd(u.v_beta),
-                                                                   grd(u.v_gamma));
-    RN_OK(j, "rn bn bwd finalize");
+    bn_chunks(M, u.kout, &chunks, &rows);
+    const int mask = !u.relu ? rn::kBnMaskNone : (u.res >= 0 ? rn::kBnMaskFromY : rn::kBnMaskFromZ);
     bf16* g_out = nullptr;
     int g_acc = 0;
     if (u.res >= 0) { g_out = s.grad[u.res]; g_acc = written[u.res]; written[u.res] = 1; }
-    rn::bn_bwd_apply_kernel<<<grid_for(M * u.kout / 8), 256, 0, st>>>(
-        s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma),
-        s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M, u.relu ? 1 : 0);
-    RN_OK(j, "rn bn bwd apply");
+    auto bn_backward = [&](auto mask_tag) -> int {
+      constexpr int kMask = decltype(mask_tag)::value;
+      rn::bn_bwd_stats_kernel<kMask><<<dim3(u.kout / 64, chunks), 256, 0, st>>>(
+          s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), s.bn_partial,
+          s.bn_done, M, u.kout, rows, grd(u.v_beta), grd(u.v_gamma));
+      RN_OK(j, "rn bn bwd stats");
+      rn::bn_bwd_apply_kernel<kMask><<<grid_for(M * u.kout / 8), 256, 0, st>>>(
+          s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), grd(u.v_beta),
+          grd(u.v_gamma), s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M);
+      RN_OK(j, "rn bn bwd apply");
+      return TFG_OK;
+    };
+    if (mask == rn::kBnMaskNone) rc = bn_backward(std::integral_constant<int, rn::kBnMaskNone>());
+    else if (mask == rn::kBnMaskFromY) rc = bn_backward(std::integral_constant<int, rn::kBnMaskFromY>());
+    else rc = bn_backward(std::integral_constant<int, rn::kBnMaskFromZ>());
+    if (rc) return rc;
     // weight gradient: the im2col operand is the one the forward pass built
     if (u.implicit) {
       if ((rc = launch_conv_wgrad(j, s.iwgrad[i], st))) return rc;
@@ -491,14 +537,24 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     const long long in_elems = m->tensors[u.in].elems();
     if (u.implicit && u.g.stride == 1) {
       ConvGemm dg = s.idgrad[i];
-      dg.epi.out_bf16 = written[u.in] ? s.dcol : s.grad[u.in];
-      if ((rc = launch_conv_gemm(j, dg, st))) return rc;
-      if (written[u.in]) {
-        rn::add_bf16_kernel<<<grid_for(in_elems / 8), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
-        RN_OK(j, "rn grad add");
+      if (dg.tma_out) {
+        dg.epi.out_bf16 = s.grad[u.in];
+        dg.tma_out = written[u.in] ? 2 : 1;
+        if ((rc = launch_conv_gemm(j, dg, st))) return rc;
+      } else {
+        dg.epi.out_bf16 = written[u.in] ? s.dcol : s.grad[u.in];
+        if ((rc = launch_conv_gemm(j, dg, st))) return rc;
+        if (written[u.in]) {
+          rn::add_bf16_kernel<<<grid_for(in_elems / 8), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
+          RN_OK(j, "rn grad add");
+        }
       }
     } else if (u.direct) {
-      if (!written[u.in]) {
+      if (d.tma_out) {
+        d.epi.out_bf16 = s.grad[u.in];
+        d.tma_out = written[u.in] ? 2 : 1;
+        if ((rc = launch_tc(j, d, TFG_MATH_BF16, st))) return rc;
+      } else if (!written[u.in]) {
         d.epi.out_bf16 = s.grad[u.in];
         if ((rc = launch_tc(j, d, TFG_MATH_BF16, st))) return rc;
       } else {

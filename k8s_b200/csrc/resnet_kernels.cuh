@@ -77,30 +77,38 @@ im2col_kernel(const bf16* __restrict__ in, bf16* __restrict__ col, ConvGeom g) {
   }
 }
 
-// Thin-channel variant (the 7x7x3 stem): one warp per output pixel; lane l writes elements
-// l, l+32, ... of the pixel's col row, so every store instruction covers 64 contiguous bytes
-// (pad columns [R*S*C, Kp) included), and the gathered reads stay inside a 7x7 neighbourhood.
+// Thin-channel variant (the 7x7x3 stem): a thread builds 8 consecutive elements (one 16-byte
+// store) of a col row, consecutive threads consecutive pieces, so the 1 GB of stores is fully
+// coalesced (pad columns [R*S*C, Kp) included).  Within one filter row the S*C source elements
+// are contiguous in the image, so the 2-byte gathered reads stay in a few L1 lines.
 __global__ void __launch_bounds__(256)
 im2col_rows_kernel(const bf16* __restrict__ in, bf16* __restrict__ col, ConvGeom g) {
   const long long M = (long long)g.N * g.OH * g.OW;
-  const int lane = threadIdx.x & 31;
-  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  const int kv = g.Kp >> 3;
+  const long long total = M * kv;
   const int K = g.R * g.S * g.C, SC = g.S * g.C;
-  for (long long m = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); m < M; m += warps) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int piece = (int)(i % kv);
+    const long long m = i / kv;
     const int ow = (int)(m % g.OW), oh = (int)((m / g.OW) % g.OH);
     const long long n = m / ((long long)g.OW * g.OH);
     const int ih0 = oh * g.stride - g.pad, iw0 = ow * g.stride - g.pad;
-    const bf16* base = in + n * g.H * g.W * g.C;
-    for (int k = lane; k < g.Kp; k += 32) {
-      bf16 v = f2b(0.f);
-      if (k < K) {
-        const int r = k / SC, sc = k - r * SC;
-        const int s = sc / g.C;
-        const int ih = ih0 + r, iw = iw0 + s;
-        if (ih >= 0 && ih < g.H && iw >= 0 && iw < g.W) v = base[((long long)ih * g.W + iw0) * g.C + sc];
-      }
-      col[m * g.Kp + k] = v;
+    const int lo = max(0, -iw0 * g.C), hi = min(SC, (g.W - iw0) * g.C);   // in-image part of a filter row
+    const bf16* base = in + ((n * g.H + ih0) * g.W + iw0) * g.C;
+    int k = piece << 3;
+    int r = k / SC, sc = k - r * SC;
+    uint4 pk;
+    unsigned short* h = reinterpret_cast<unsigned short*>(&pk);
+#pragma unroll
+    for (int u = 0; u < 8; ++u, ++k) {
+      unsigned short x = 0;
+      const int ih = ih0 + r;
+      if (k < K && ih >= 0 && ih < g.H && sc >= lo && sc < hi)
+        x = __ldg(reinterpret_cast<const unsigned short*>(base) + (long long)r * g.W * g.C + sc);
+      h[u] = x;
+      if (++sc == SC) { sc = 0; ++r; }
     }
+    *reinterpret_cast<uint4*>(col + m * g.Kp + (piece << 3)) = pk;
   }
 }
 
@@ -183,11 +191,26 @@ add_bf16_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long 
 }
 
 // ---- batch norm ----------------------------------------------------------------------------
-// stage 1 of per-channel sums over rows: partial[chunk][2][C] = (sum x, sum x^2) for forward,
-// (sum dy, sum dy * xhat) for backward.  block = 8 channel groups (8 channels = 16 B each) x 32
-// row lanes; C is a multiple of 64 for every layer of the net.
-__device__ __forceinline__ void bn_block_reduce(float (&s)[8], float (&q)[8], float* partial, int C, int cg, int rl) {
+// Per-channel sums over rows run in two stages inside ONE launch: every block stores the sums
+// of its row chunk to partial[chunk][2][C]; the block that finishes last for a group of 64
+// channels (a counter in `done`, which it resets) folds the chunks in a fixed order and writes
+// the statistics, so the result does not depend on which block came last and no float atomics
+// are involved.  block = 8 channel groups (8 channels = 16 B each) x 32 row lanes, four rows
+// in flight per thread; C is a multiple of 64 for every layer of the net.
+constexpr int kBnRowsInFlight = 4;
+
+// the normalised activation: one instruction sequence shared by every kernel that needs it, so
+// that the relu mask recomputed in the backward pass is the one the forward pass applied
+__device__ __forceinline__ float bn_value(float z, float mu, float is, float ga, float be) {
+  return __fmaf_rn(__fmul_rn(ga, __fsub_rn(z, mu)), is, be);
+}
+
+// returns true in the block that stored the last chunk of channel group blockIdx.x; s, q then
+// hold the folded sums of channel blockIdx.x * 64 + (threadIdx.x & 63) in threads 0..63
+__device__ __forceinline__ bool bn_block_reduce(float (&s)[8], float (&q)[8], float* partial, unsigned int* done,
+                                                int chunks, int C, int cg, int rl, float* fold_s, float* fold_q) {
   __shared__ float r1[32][65], r2[32][65];
+  __shared__ bool last;
 #pragma unroll
   for (int k = 0; k < 8; ++k) { r1[rl][cg * 8 + k] = s[k]; r2[rl][cg * 8 + k] = q[k]; }
   __syncthreads();
@@ -196,133 +219,206 @@ __device__ __forceinline__ void bn_block_reduce(float (&s)[8], float (&q)[8], fl
     float a = 0.f, b = 0.f;
     for (int l = 0; l < 32; ++l) { a += r1[l][t]; b += r2[l][t]; }   // fixed order
     const int c = blockIdx.x * 64 + t;
-    partial[((size_t)blockIdx.y * 2 + 0) * C + c] = a;
-    partial[((size_t)blockIdx.y * 2 + 1) * C + c] = b;
+    __stcg(&partial[((size_t)blockIdx.y * 2 + 0) * C + c], a);
+    __stcg(&partial[((size_t)blockIdx.y * 2 + 1) * C + c], b);
+    __threadfence();
   }
+  __syncthreads();
+  if (t == 0) {
+    const unsigned int prev = atomicAdd(&done[blockIdx.x], 1u);
+    last = prev == (unsigned int)chunks - 1u;
+    if (last) done[blockIdx.x] = 0u;   // ready for the next launch on this stream
+  }
+  __syncthreads();
+  if (!last) return false;
+  __threadfence();
+  // fold: 4 strands of interleaved chunks per channel, then the strands in order 0..3
+  const int c = blockIdx.x * 64 + (t & 63), strand = t >> 6;
+  float a = 0.f, b = 0.f;
+#pragma unroll 4
+  for (int k = strand; k < chunks; k += 4) {
+    a += __ldcg(&partial[((size_t)k * 2 + 0) * C + c]);
+    b += __ldcg(&partial[((size_t)k * 2 + 1) * C + c]);
+  }
+  __syncthreads();                    // r1 / r2 are reused below
+  r1[strand][t & 63] = a;
+  r2[strand][t & 63] = b;
+  __syncthreads();
+  if (t < 64) {
+    *fold_s = ((r1[0][t] + r1[1][t]) + r1[2][t]) + r1[3][t];
+    *fold_q = ((r2[0][t] + r2[1][t]) + r2[2][t]) + r2[3][t];
+  }
+  return true;
 }
 
+// forward statistics: mean, invstd (biased variance, eps) and the moving statistics update
 __global__ void __launch_bounds__(256)
-bn_stats_kernel(const bf16* __restrict__ z, float* __restrict__ partial, long long M, int C, int rows_per_chunk) {
+bn_stats_kernel(const bf16* __restrict__ z, float* partial, unsigned int* done, long long M, int C, int rows_per_chunk,
+                float eps, float decay, float* __restrict__ mean, float* __restrict__ invstd,
+                float* __restrict__ mov_mean, float* __restrict__ mov_var) {
   const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
   const int c0 = blockIdx.x * 64 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s[8], q[8], v[8];
+  float s[8], q[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
-  for (long long r = r0 + rl; r < rend; r += 32) {
-    ld8(z + r * C + c0, v);
+  for (long long r = r0 + rl; r < rend; r += 32 * kBnRowsInFlight) {
+    float v[kBnRowsInFlight][8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
+    for (int u = 0; u < kBnRowsInFlight; ++u) {
+      const long long rr = r + 32 * u;
+      if (rr < rend) {
+        ld8(z + rr * C + c0, v[u]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[u][k] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kBnRowsInFlight; ++u)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { s[k] += v[u][k]; q[k] = fmaf(v[u][k], v[u][k], q[k]); }
   }
-  bn_block_reduce(s, q, partial, C, cg, rl);
+  float fs = 0.f, fq = 0.f;
+  if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
+  if (threadIdx.x < 64) {
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    const float mu = fs / (float)M;
+    const float var = fmaxf(fq / (float)M - mu * mu, 0.f);
+    mean[c] = mu;
+    invstd[c] = rsqrtf(var + eps);
+    if (mov_mean) {
+      mov_mean[c] = decay * mov_mean[c] + (1.f - decay) * mu;
+      mov_var[c] = decay * mov_var[c] + (1.f - decay) * var * ((float)M / (float)max(M - 1, 1ll));
+    }
+  }
 }
 
-// stage 2 forward: mean, invstd (biased variance, eps), moving statistics update
-__global__ void __launch_bounds__(256)
-bn_finalize_kernel(const float* __restrict__ partial, int chunks, int C, long long M, float eps, float decay,
-                   float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ mov_mean,
-                   float* __restrict__ mov_var) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f, q = 0.f;
-  for (int k = 0; k < chunks; ++k) { s += partial[((size_t)k * 2) * C + c]; q += partial[((size_t)k * 2 + 1) * C + c]; }
-  const float mu = s / (float)M;
-  const float var = fmaxf(q / (float)M - mu * mu, 0.f);
-  mean[c] = mu;
-  invstd[c] = rsqrtf(var + eps);
-  if (mov_mean) {
-    mov_mean[c] = decay * mov_mean[c] + (1.f - decay) * mu;
-    mov_var[c] = decay * mov_var[c] + (1.f - decay) * var * ((float)M / (float)max(M - 1, 1ll));
-  }
-}
-
-// y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out, 8 channels per thread
+// y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out.  8 channels per
+// thread; the grid stride is a multiple of C (C divides 2048 = 8 * blockDim), so a thread keeps
+// its channels and loads the per-channel values once.  Two elements in flight per thread.
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ invstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta, const bf16* __restrict__ residual,
                 bf16* __restrict__ y, long long total, int C, int relu) {
   const long long total8 = total >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)((i << 3) % C);
-    float v[8], mu[8], is[8], ga[8], be[8], rs[8];
-    ld8(z + (i << 3), v);
-    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(beta + c, be);
-    if (residual) ld8(residual + (i << 3), rs);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      float o = ga[k] * (v[k] - mu[k]) * is[k] + be[k];
-      if (residual) o += rs[k];
-      if (relu) o = fmaxf(o, 0.f);
-      v[k] = o;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int c = (int)((i << 3) % C);
+  float mu[8], is[8], ga[8], be[8];
+  ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(beta + c, be);
+  for (; i < total8; i += 2 * stride) {
+    const long long i2 = i + stride;
+    const bool two = i2 < total8;
+    float v[2][8], rs[2][8];
+    ld8(z + (i << 3), v[0]);
+    if (two) ld8(z + (i2 << 3), v[1]);
+    if (residual) {
+      ld8(residual + (i << 3), rs[0]);
+      if (two) ld8(residual + (i2 << 3), rs[1]);
     }
-    st8(y + (i << 3), v);
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float o = bn_value(v[u][k], mu[k], is[k], ga[k], be[k]);
+        if (residual) o += rs[u][k];
+        if (relu) o = fmaxf(o, 0.f);
+        v[u][k] = o;
+      }
+    st8(y + (i << 3), v[0]);
+    if (two) st8(y + (i2 << 3), v[1]);
   }
 }
 
-// backward stage 1: partial[chunk][2][C] = (sum g, sum g * xhat), g = dy masked by y > 0 when relu
-__global__ void __launch_bounds__(256)
+// relu mask of the forward pass: kBnMaskFromY reads y (units with a residual input),
+// kBnMaskFromZ recomputes bn_value(z) > 0 (no residual: y is never read in the backward pass)
+enum { kBnMaskNone = 0, kBnMaskFromY = 1, kBnMaskFromZ = 2 };
+
+// backward statistics: dbeta = sum g, dgamma = sum g * xhat, g = dy under the relu mask.
+// Three blocks per SM (<= 85 registers) hide the load latency; one row in flight per thread.
+template <int MASK>
+__global__ void __launch_bounds__(256, 3)
 bn_bwd_stats_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
-                    const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ partial,
-                    long long M, int C, int rows_per_chunk, int relu) {
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, float* partial, unsigned int* done, long long M, int C,
+                    int rows_per_chunk, float* __restrict__ dbeta, float* __restrict__ dgamma) {
   const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
   const int c0 = blockIdx.x * 64 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s[8], q[8], mu[8], is[8], g[8], yy[8], zz[8];
+  float s[8], q[8], mu[8], is[8], ga[8], be[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   ldf8(mean + c0, mu);
   ldf8(invstd + c0, is);
+  if (MASK == kBnMaskFromZ) { ldf8(gamma + c0, ga); ldf8(beta + c0, be); }
+#pragma unroll 2
   for (long long r = r0 + rl; r < rend; r += 32) {
+    float g[8], zz[8], yy[8];
     ld8(dy + r * C + c0, g);
     ld8(z + r * C + c0, zz);
-    if (relu) ld8(y + r * C + c0, yy);
+    if (MASK == kBnMaskFromY) ld8(y + r * C + c0, yy);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const float gg = (relu && !(yy[k] > 0.f)) ? 0.f : g[k];
+      bool on = true;
+      if (MASK == kBnMaskFromY) on = yy[k] > 0.f;
+      if (MASK == kBnMaskFromZ) on = bn_value(zz[k], mu[k], is[k], ga[k], be[k]) > 0.f;
+      const float gg = on ? g[k] : 0.f;
       s[k] += gg;
       q[k] = fmaf(gg, (zz[k] - mu[k]) * is[k], q[k]);
     }
   }
-  bn_block_reduce(s, q, partial, C, cg, rl);
-}
-
-__global__ void __launch_bounds__(256)
-bn_bwd_finalize_kernel(const float* __restrict__ partial, int chunks, int C, float* __restrict__ dbeta,
-                       float* __restrict__ dgamma) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f, q = 0.f;
-  for (int k = 0; k < chunks; ++k) { s += partial[((size_t)k * 2) * C + c]; q += partial[((size_t)k * 2 + 1) * C + c]; }
-  dbeta[c] = s;
-  dgamma[c] = q;
+  float fs = 0.f, fq = 0.f;
+  if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
+  if (threadIdx.x < 64) {
+    dbeta[blockIdx.x * 64 + threadIdx.x] = fs;
+    dgamma[blockIdx.x * 64 + threadIdx.x] = fq;
+  }
 }
 
 // dz = gamma * invstd * (g - dbeta/M - xhat * dgamma/M); optionally also writes the masked g
-// (the gradient that flows into the residual branch).  8 channels per thread.
-__global__ void __launch_bounds__(256)
+// (the gradient that flows into the residual branch).  8 channels per thread, per-channel
+// values loaded once (see bn_apply_kernel) and folded: dz = k1 * (g - db) - k2 * (z - mu) with
+// k1 = gamma * invstd, db = dbeta / M, k2 = k1 * invstd * dgamma / M.
+template <int MASK>
+__global__ void __launch_bounds__(256, 3)
 bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ dbeta, const float* __restrict__ dgamma, bf16* __restrict__ dz,
-                    bf16* __restrict__ g_out, int g_accumulate, long long total, int C, long long M, int relu) {
+                    const float* __restrict__ beta, const float* __restrict__ dbeta, const float* __restrict__ dgamma,
+                    bf16* __restrict__ dz, bf16* __restrict__ g_out, int g_accumulate, long long total, int C,
+                    long long M) {
   const float inv_m = 1.f / (float)M;
   const long long total8 = total >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)((i << 3) % C);
-    float g[8], yy[8], zz[8], mu[8], is[8], ga[8], db[8], dg[8], o[8], prev[8];
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int c = (int)((i << 3) % C);
+  float mu[8], is[8], ga[8], be[8], db[8], k1[8], k2[8];
+  ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga);
+  if (MASK == kBnMaskFromZ) ldf8(beta + c, be);
+  ldf8(dbeta + c, db); ldf8(dgamma + c, k2);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    k1[k] = ga[k] * is[k];
+    db[k] *= inv_m;
+    k2[k] = k1[k] * is[k] * (k2[k] * inv_m);
+  }
+  for (; i < total8; i += stride) {
+    float g[8], yy[8], zz[8], o[8], prev[8];
     ld8(dy + (i << 3), g);
     ld8(z + (i << 3), zz);
-    if (relu) ld8(y + (i << 3), yy);
-    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(dbeta + c, db); ldf8(dgamma + c, dg);
+    if (MASK == kBnMaskFromY) ld8(y + (i << 3), yy);
+    if (g_out && g_accumulate) ld8(g_out + (i << 3), prev);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      if (relu && !(yy[k] > 0.f)) g[k] = 0.f;
-      const float xhat = (zz[k] - mu[k]) * is[k];
-      o[k] = ga[k] * is[k] * (g[k] - db[k] * inv_m - xhat * dg[k] * inv_m);
+      bool on = true;
+      if (MASK == kBnMaskFromY) on = yy[k] > 0.f;
+      if (MASK == kBnMaskFromZ) on = bn_value(zz[k], mu[k], is[k], ga[k], be[k]) > 0.f;
+      if (!on) g[k] = 0.f;
+      o[k] = k1[k] * (g[k] - db[k]) - k2[k] * (zz[k] - mu[k]);
     }
     st8(dz + (i << 3), o);
     if (g_out) {
       if (g_accumulate) {
-        ld8(g_out + (i << 3), prev);
 #pragma unroll
         for (int k = 0; k < 8; ++k) g[k] += prev[k];
       }

@@ -7,11 +7,13 @@ namespace tfg {
 
 struct TcGemm {
   CUtensorMap a, b;
+  CUtensorMap c;               // bf16 output [M, ldc], box {64, 128} (make_map(.., M, N, ldc, 128)); used when tma_out != 0
+  int tma_out = 0;             // 1: TMA store, 2: TMA reduce-add into the output; forces the persistent kernel
   float* C = nullptr;          // [M, ldc]
   float* partial = nullptr;    // [splits][M][N] when splits > 1
   int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
   bool a_mn = false, b_mn = false;
-  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 0};
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 0, 0};
   const char* name = "gemm";
 };
 
