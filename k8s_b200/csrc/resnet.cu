@@ -51,6 +51,7 @@ struct RnSlot {
   bf16* dcol = nullptr;              // shared staging of data gradients
   uint8_t* pool_arg = nullptr;
   float *bn_partial = nullptr, *splitk = nullptr;
+  std::vector<uint8_t*> relu_bits;         // per relu unit: one bit per element of y, set where the relu passed
   unsigned int* bn_done = nullptr;         // per 64-channel group: row chunks finished (self-resetting)
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
   bf16 *pooled = nullptr, *dpooled = nullptr, *dlogits = nullptr;
@@ -92,6 +93,11 @@ static bool tma_out_enabled() {
     if (const char* e = getenv("TFGRAFT_TMA_OUT")) on = atoi(e) != 0;
   }
   return on == 1;
+}
+
+// element-wise kernels with a grid-stride loop and three resident blocks per SM: one full wave
+static inline int grid_resident(long long n, int per = 256) {
+  return (int)std::max<long long>(1, std::min<long long>((n + per - 1) / per, kNumSMs * 3));
 }
 
 #define RN_OK(j, what)                                           \
@@ -219,6 +225,11 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
       alloc((void**)&s.mean[u], sizeof(float) * m->units[u].kout);
       alloc((void**)&s.invstd[u], sizeof(float) * m->units[u].kout);
     }
+    s.relu_bits.assign(m->units.size(), nullptr);
+    for (size_t u = 0; u < m->units.size(); ++u) {
+      const RnUnit& un = m->units[u];
+      if (un.relu) alloc((void**)&s.relu_bits[u], (size_t)un.g.N * un.g.OH * un.g.OW * un.kout / 8);
+    }
     s.col.assign(m->units.size(), nullptr);
     for (size_t u = 0; u < m->units.size(); ++u) {
       const RnUnit& un = m->units[u];
@@ -259,6 +270,7 @@ void resnet_destroy(tfg_job* j) {
     for (auto p : s.mean) cudaFree(p);
     for (auto p : s.invstd) cudaFree(p);
     for (auto p : s.col) cudaFree(p);
+    for (auto p : s.relu_bits) cudaFree(p);
     cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.bn_done); cudaFree(s.splitk);
     cudaFree(s.logits); cudaFree(s.loss_vec); cudaFree(s.pooled); cudaFree(s.dpooled); cudaFree(s.dlogits);
   }
@@ -457,9 +469,9 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
         s.data[u.z], s.bn_partial, s.bn_done, M, u.kout, rows, 1e-5f, 0.997f, s.mean[i], s.invstd[i],
         update_moving ? u.mov_mean : nullptr, update_moving ? u.mov_var : nullptr);
     RN_OK(j, "rn bn stats");
-    rn::bn_apply_kernel<<<grid_for(M * u.kout / 8), 256, 0, st>>>(s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma),
-                                                             par(u.v_beta), u.res >= 0 ? s.data[u.res] : nullptr,
-                                                             s.data[u.y], M * u.kout, u.kout, u.relu ? 1 : 0);
+    rn::bn_apply_kernel<<<grid_resident(M * u.kout / 8), 256, 0, st>>>(
+        s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), u.res >= 0 ? s.data[u.res] : nullptr,
+        s.data[u.y], u.relu ? s.relu_bits[i] : nullptr, M * u.kout, u.kout);
     RN_OK(j, "rn bn apply");
     if (u.y == m->t_pool_in) {
       const RnTensor& ti = m->tensors[m->t_pool_in];
@@ -505,26 +517,29 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     if (!written[u.y]) return fail(j, TFG_ESTATE, "internal: gradient of " + u.name + "/y was never produced");
     int chunks, rows;
     bn_chunks(M, u.kout, &chunks, &rows);
-    const int mask = !u.relu ? rn::kBnMaskNone : (u.res >= 0 ? rn::kBnMaskFromY : rn::kBnMaskFromZ);
     bf16* g_out = nullptr;
     int g_acc = 0;
     if (u.res >= 0) { g_out = s.grad[u.res]; g_acc = written[u.res]; written[u.res] = 1; }
-    auto bn_backward = [&](auto mask_tag) -> int {
-      constexpr int kMask = decltype(mask_tag)::value;
-      rn::bn_bwd_stats_kernel<kMask><<<dim3(u.kout / 64, chunks), 256, 0, st>>>(
-          s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), s.bn_partial,
-          s.bn_done, M, u.kout, rows, grd(u.v_beta), grd(u.v_gamma));
+    const dim3 sgrid(u.kout / 64, chunks);
+    const int agrid = grid_resident(M * u.kout / 8);
+    if (u.relu) {
+      rn::bn_bwd_stats_kernel<true><<<sgrid, 256, 0, st>>>(s.grad[u.y], s.relu_bits[i], s.data[u.z], s.mean[i], s.invstd[i],
+                                                            s.bn_partial, s.bn_done, M, u.kout, rows, grd(u.v_beta),
+                                                            grd(u.v_gamma));
       RN_OK(j, "rn bn bwd stats");
-      rn::bn_bwd_apply_kernel<kMask><<<grid_for(M * u.kout / 8), 256, 0, st>>>(
-          s.grad[u.y], s.data[u.y], s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), grd(u.v_beta),
-          grd(u.v_gamma), s.grad[u.z], g_out, g_acc, M * u.kout, u.kout, M);
-      RN_OK(j, "rn bn bwd apply");
-      return TFG_OK;
-    };
-    if (mask == rn::kBnMaskNone) rc = bn_backward(std::integral_constant<int, rn::kBnMaskNone>());
-    else if (mask == rn::kBnMaskFromY) rc = bn_backward(std::integral_constant<int, rn::kBnMaskFromY>());
-    else rc = bn_backward(std::integral_constant<int, rn::kBnMaskFromZ>());
-    if (rc) return rc;
+      rn::bn_bwd_apply_kernel<true><<<agrid, 256, 0, st>>>(s.grad[u.y], s.relu_bits[i], s.data[u.z], s.mean[i], s.invstd[i],
+                                                           par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma), s.grad[u.z], g_out,
+                                                           g_acc, M * u.kout, u.kout, M);
+    } else {
+      rn::bn_bwd_stats_kernel<false><<<sgrid, 256, 0, st>>>(s.grad[u.y], nullptr, s.data[u.z], s.mean[i], s.invstd[i],
+                                                             s.bn_partial, s.bn_done, M, u.kout, rows, grd(u.v_beta),
+                                                             grd(u.v_gamma));
+      RN_OK(j, "rn bn bwd stats");
+      rn::bn_bwd_apply_kernel<false><<<agrid, 256, 0, st>>>(s.grad[u.y], nullptr, s.data[u.z], s.mean[i], s.invstd[i],
+                                                            par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma), s.grad[u.z], g_out,
+                                                            g_acc, M * u.kout, u.kout, M);
+    }
+    RN_OK(j, "rn bn bwd apply");
     // weight gradient: the im2col operand is the one the forward pass built
     if (u.implicit) {
       if ((rc = launch_conv_wgrad(j, s.iwgrad[i], st))) return rc;

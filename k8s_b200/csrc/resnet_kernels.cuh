@@ -195,18 +195,17 @@ add_bf16_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long 
 // of its row chunk to partial[chunk][2][C]; the block that finishes last for a group of 64
 // channels (a counter in `done`, which it resets) folds the chunks in a fixed order and writes
 // the statistics, so the result does not depend on which block came last and no float atomics
-// are involved.  block = 8 channel groups (8 channels = 16 B each) x 32 row lanes, four rows
-// in flight per thread; C is a multiple of 64 for every layer of the net.
+// are involved.  block = 8 channel groups (8 channels = 16 B each) x 32 row lanes; C is a
+// multiple of 64 for every layer of the net.
+//
+// These kernels move 2-byte elements at HBM speed, which leaves about ten instructions per
+// element and stream on an SM; hence the relu mask of the forward pass is kept as one bit per
+// element (written by bn_apply_kernel) instead of being re-derived from y or z in the two
+// backward kernels, and per-channel constants live in registers (a thread keeps its channels).
 constexpr int kBnRowsInFlight = 4;
 
-// the normalised activation: one instruction sequence shared by every kernel that needs it, so
-// that the relu mask recomputed in the backward pass is the one the forward pass applied
-__device__ __forceinline__ float bn_value(float z, float mu, float is, float ga, float be) {
-  return __fmaf_rn(__fmul_rn(ga, __fsub_rn(z, mu)), is, be);
-}
-
-// returns true in the block that stored the last chunk of channel group blockIdx.x; s, q then
-// hold the folded sums of channel blockIdx.x * 64 + (threadIdx.x & 63) in threads 0..63
+// returns true in the block that stored the last chunk of channel group blockIdx.x; *fold_s and
+// *fold_q then hold the folded sums of channel blockIdx.x * 64 + threadIdx.x in threads 0..63
 __device__ __forceinline__ bool bn_block_reduce(float (&s)[8], float (&q)[8], float* partial, unsigned int* done,
                                                 int chunks, int C, int cg, int rl, float* fold_s, float* fold_q) {
   __shared__ float r1[32][65], r2[32][65];
@@ -217,6 +216,7 @@ __device__ __forceinline__ bool bn_block_reduce(float (&s)[8], float (&q)[8], fl
   const int t = threadIdx.x;
   if (t < 64) {
     float a = 0.f, b = 0.f;
+#pragma unroll 8
     for (int l = 0; l < 32; ++l) { a += r1[l][t]; b += r2[l][t]; }   // fixed order
     const int c = blockIdx.x * 64 + t;
     __stcg(&partial[((size_t)blockIdx.y * 2 + 0) * C + c], a);
@@ -232,21 +232,28 @@ __device__ __forceinline__ bool bn_block_reduce(float (&s)[8], float (&q)[8], fl
   __syncthreads();
   if (!last) return false;
   __threadfence();
-  // fold: 4 strands of interleaved chunks per channel, then the strands in order 0..3
-  const int c = blockIdx.x * 64 + (t & 63), strand = t >> 6;
-  float a = 0.f, b = 0.f;
-#pragma unroll 4
-  for (int k = strand; k < chunks; k += 4) {
-    a += __ldcg(&partial[((size_t)k * 2 + 0) * C + c]);
-    b += __ldcg(&partial[((size_t)k * 2 + 1) * C + c]);
+  // fold: 16 strands of interleaved chunks x 16 channel quads (many loads in flight: the fold is
+  // the tail of every launch), then the strands in order 0..15
+  const int quad = t & 15, strand = t >> 4;
+  const float* base = partial + blockIdx.x * 64 + quad * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 8
+  for (int k = strand; k < chunks; k += 16) {
+    const float4 x = __ldcg(reinterpret_cast<const float4*>(base + ((size_t)k * 2 + 0) * C));
+    const float4 y = __ldcg(reinterpret_cast<const float4*>(base + ((size_t)k * 2 + 1) * C));
+    a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+    b.x += y.x; b.y += y.y; b.z += y.z; b.w += y.w;
   }
   __syncthreads();                    // r1 / r2 are reused below
-  r1[strand][t & 63] = a;
-  r2[strand][t & 63] = b;
+  r1[strand][quad * 4 + 0] = a.x; r1[strand][quad * 4 + 1] = a.y; r1[strand][quad * 4 + 2] = a.z; r1[strand][quad * 4 + 3] = a.w;
+  r2[strand][quad * 4 + 0] = b.x; r2[strand][quad * 4 + 1] = b.y; r2[strand][quad * 4 + 2] = b.z; r2[strand][quad * 4 + 3] = b.w;
   __syncthreads();
   if (t < 64) {
-    *fold_s = ((r1[0][t] + r1[1][t]) + r1[2][t]) + r1[3][t];
-    *fold_q = ((r2[0][t] + r2[1][t]) + r2[2][t]) + r2[3][t];
+    float fs = 0.f, fq = 0.f;
+#pragma unroll
+    for (int l = 0; l < 16; ++l) { fs += r1[l][t]; fq += r2[l][t]; }
+    *fold_s = fs;
+    *fold_q = fq;
   }
   return true;
 }
@@ -296,78 +303,76 @@ bn_stats_kernel(const bf16* __restrict__ z, float* partial, unsigned int* done, 
 
 // y = gamma * (z - mean) * invstd + beta (+ residual) (relu), bf16 in / out.  8 channels per
 // thread; the grid stride is a multiple of C (C divides 2048 = 8 * blockDim), so a thread keeps
-// its channels and loads the per-channel values once.  Two elements in flight per thread.
-__global__ void __launch_bounds__(256)
+// its channels and loads the per-channel values once.  With relu, bit k of relu_bits[i] says
+// whether element 8 i + k passed (value > 0): the mask the backward kernels apply.
+__global__ void __launch_bounds__(256, 3)
 bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ invstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta, const bf16* __restrict__ residual,
-                bf16* __restrict__ y, long long total, int C, int relu) {
+                bf16* __restrict__ y, uint8_t* __restrict__ relu_bits, long long total, int C) {
   const long long total8 = total >> 3;
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const int c = (int)((i << 3) % C);
-  float mu[8], is[8], ga[8], be[8];
-  ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(beta + c, be);
-  for (; i < total8; i += 2 * stride) {
-    const long long i2 = i + stride;
-    const bool two = i2 < total8;
-    float v[2][8], rs[2][8];
-    ld8(z + (i << 3), v[0]);
-    if (two) ld8(z + (i2 << 3), v[1]);
-    if (residual) {
-      ld8(residual + (i << 3), rs[0]);
-      if (two) ld8(residual + (i2 << 3), rs[1]);
-    }
+  float mu[8], sc[8], be[8];
+  {
+    float is[8], ga[8];
+    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga); ldf8(beta + c, be);
 #pragma unroll
-    for (int u = 0; u < 2; ++u)
+    for (int k = 0; k < 8; ++k) sc[k] = ga[k] * is[k];
+  }
+  for (; i < total8; i += stride) {
+    float v[8], rs[8];
+    ld8(z + (i << 3), v);
+    if (residual) ld8(residual + (i << 3), rs);
+    unsigned int bits = 0;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        float o = bn_value(v[u][k], mu[k], is[k], ga[k], be[k]);
-        if (residual) o += rs[u][k];
-        if (relu) o = fmaxf(o, 0.f);
-        v[u][k] = o;
+    for (int k = 0; k < 8; ++k) {
+      float o = fmaf(v[k] - mu[k], sc[k], be[k]);
+      if (residual) o += rs[k];
+      if (relu_bits) {
+        bits |= (o > 0.f ? 1u : 0u) << k;
+        o = fmaxf(o, 0.f);
       }
-    st8(y + (i << 3), v[0]);
-    if (two) st8(y + (i2 << 3), v[1]);
+      v[k] = o;
+    }
+    st8(y + (i << 3), v);
+    if (relu_bits) relu_bits[i] = (uint8_t)bits;
   }
 }
 
-// relu mask of the forward pass: kBnMaskFromY reads y (units with a residual input),
-// kBnMaskFromZ recomputes bn_value(z) > 0 (no residual: y is never read in the backward pass)
-enum { kBnMaskNone = 0, kBnMaskFromY = 1, kBnMaskFromZ = 2 };
-
 // backward statistics: dbeta = sum g, dgamma = sum g * xhat, g = dy under the relu mask.
-// Three blocks per SM (<= 85 registers) hide the load latency; one row in flight per thread.
-template <int MASK>
+// Three blocks per SM (<= 85 registers) hide the load latency.
+template <bool RELU>
 __global__ void __launch_bounds__(256, 3)
-bn_bwd_stats_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
-                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ beta, float* partial, unsigned int* done, long long M, int C,
-                    int rows_per_chunk, float* __restrict__ dbeta, float* __restrict__ dgamma) {
+bn_bwd_stats_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ relu_bits, const bf16* __restrict__ z,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, float* partial,
+                    unsigned int* done, long long M, int C, int rows_per_chunk, float* __restrict__ dbeta,
+                    float* __restrict__ dgamma) {
   const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
   const int c0 = blockIdx.x * 64 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s[8], q[8], mu[8], is[8], ga[8], be[8];
+  float s[8], q[8], mu[8], is[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   ldf8(mean + c0, mu);
   ldf8(invstd + c0, is);
-  if (MASK == kBnMaskFromZ) { ldf8(gamma + c0, ga); ldf8(beta + c0, be); }
 #pragma unroll 2
   for (long long r = r0 + rl; r < rend; r += 32) {
-    float g[8], zz[8], yy[8];
-    ld8(dy + r * C + c0, g);
-    ld8(z + r * C + c0, zz);
-    if (MASK == kBnMaskFromY) ld8(y + r * C + c0, yy);
+    float g[8], zz[8];
+    const long long e = r * C + c0;
+    ld8(dy + e, g);
+    ld8(z + e, zz);
+    unsigned int bits = 0xffu;
+    if (RELU) bits = relu_bits[e >> 3];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      bool on = true;
-      if (MASK == kBnMaskFromY) on = yy[k] > 0.f;
-      if (MASK == kBnMaskFromZ) on = bn_value(zz[k], mu[k], is[k], ga[k], be[k]) > 0.f;
-      const float gg = on ? g[k] : 0.f;
+      const float gg = (!RELU || ((bits >> k) & 1u)) ? g[k] : 0.f;
       s[k] += gg;
-      q[k] = fmaf(gg, (zz[k] - mu[k]) * is[k], q[k]);
+      q[k] = fmaf(gg, zz[k] - mu[k], q[k]);      // invstd is applied once, after the sum
     }
   }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) q[k] *= is[k];
   float fs = 0.f, fq = 0.f;
   if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
   if (threadIdx.x < 64) {
@@ -380,40 +385,39 @@ bn_bwd_stats_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, con
 // (the gradient that flows into the residual branch).  8 channels per thread, per-channel
 // values loaded once (see bn_apply_kernel) and folded: dz = k1 * (g - db) - k2 * (z - mu) with
 // k1 = gamma * invstd, db = dbeta / M, k2 = k1 * invstd * dgamma / M.
-template <int MASK>
+template <bool RELU>
 __global__ void __launch_bounds__(256, 3)
-bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ z,
+bn_bwd_apply_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ relu_bits, const bf16* __restrict__ z,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ beta, const float* __restrict__ dbeta, const float* __restrict__ dgamma,
-                    bf16* __restrict__ dz, bf16* __restrict__ g_out, int g_accumulate, long long total, int C,
-                    long long M) {
+                    const float* __restrict__ dbeta, const float* __restrict__ dgamma, bf16* __restrict__ dz,
+                    bf16* __restrict__ g_out, int g_accumulate, long long total, int C, long long M) {
   const float inv_m = 1.f / (float)M;
   const long long total8 = total >> 3;
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const int c = (int)((i << 3) % C);
-  float mu[8], is[8], ga[8], be[8], db[8], k1[8], k2[8];
-  ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga);
-  if (MASK == kBnMaskFromZ) ldf8(beta + c, be);
-  ldf8(dbeta + c, db); ldf8(dgamma + c, k2);
+  float mu[8], db[8], k1[8], k2[8];
+  {
+    float is[8], ga[8];
+    ldf8(mean + c, mu); ldf8(invstd + c, is); ldf8(gamma + c, ga);
+    ldf8(dbeta + c, db); ldf8(dgamma + c, k2);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    k1[k] = ga[k] * is[k];
-    db[k] *= inv_m;
-    k2[k] = k1[k] * is[k] * (k2[k] * inv_m);
+    for (int k = 0; k < 8; ++k) {
+      k1[k] = ga[k] * is[k];
+      db[k] *= inv_m;
+      k2[k] = k1[k] * is[k] * (k2[k] * inv_m);
+    }
   }
   for (; i < total8; i += stride) {
-    float g[8], yy[8], zz[8], o[8], prev[8];
+    float g[8], zz[8], o[8], prev[8];
     ld8(dy + (i << 3), g);
     ld8(z + (i << 3), zz);
-    if (MASK == kBnMaskFromY) ld8(y + (i << 3), yy);
+    unsigned int bits = 0xffu;
+    if (RELU) bits = relu_bits[i];
     if (g_out && g_accumulate) ld8(g_out + (i << 3), prev);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      bool on = true;
-      if (MASK == kBnMaskFromY) on = yy[k] > 0.f;
-      if (MASK == kBnMaskFromZ) on = bn_value(zz[k], mu[k], is[k], ga[k], be[k]) > 0.f;
-      if (!on) g[k] = 0.f;
+      if (RELU && !((bits >> k) & 1u)) g[k] = 0.f;
       o[k] = k1[k] * (g[k] - db[k]) - k2[k] * (zz[k] - mu[k]);
     }
     st8(dz + (i << 3), o);

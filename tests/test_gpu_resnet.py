@@ -199,19 +199,20 @@ def test_resnet50_layerwise_parity():
 def test_resnet50_step_applies_its_gradients_exactly_and_is_deterministic():
     """One synchronous step through the host-buffer entry point: the new parameters are exactly
     the C oracle's SGD apply of the step's own gradients (bit-exact), the run is reproducible, and
-    a few SGD steps on one batch reduce its loss."""
+    a few SGD steps on one batch reduce its loss (lr 0.002: the oracle's fp32 and bf16-emulated
+    runs of the same 8 steps fall from 2.7 to below 0.9; at 0.01 both oscillate)."""
     from oracle import oracle as O
     B, HW, NC = 4, 64, 16
     outs = []
     for _ in range(2):
         j = SyncPSJob(cfg(), 0, 1, cuda_device=0)
         j.build_resnet50(B, HW, NC)
-        j.optimizer("sgd", 0.01, 0.0)
+        j.optimizer("sgd", 0.002, 0.0)
         init = resnet50_init(j, 0)
         x, y = synthetic_images(0, B, HW, NC)
         losses = [j.step([x], [y])]
         for v in list(init)[:12] + list(init)[-4:]:
-            want, _ = O.dense_apply(O.SGD, init[v].reshape(-1).copy(), None, [j.get_grad(0, v)], 1.0, 0.01, 0.0)
+            want, _ = O.dense_apply(O.SGD, init[v].reshape(-1).copy(), None, [j.get_grad(0, v)], 1.0, 0.002, 0.0)
             np.testing.assert_array_equal(j.get_var(v).view(np.uint32), want.view(np.uint32))
         losses += [j.step([x], [y]) for _ in range(7)]
         outs.append((losses, j.get_var(0).copy()))
@@ -219,4 +220,4 @@ def test_resnet50_step_applies_its_gradients_exactly_and_is_deterministic():
         j.close()
     assert outs[0][0] == outs[1][0]
     np.testing.assert_array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
-    assert min(outs[0][0][1:]) < outs[0][0][0], outs[0][0]
+    assert outs[0][0][-1] < 0.6 * outs[0][0][0], outs[0][0]
