@@ -304,21 +304,36 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
 
 
 def resnet_work(name: str, B: int, image: int, classes: int):
-    """FLOPs per step of all ResNet-50 launches that share a profile name (conv fwd / dgrad / wgrad)."""
+    """Algorithmic work per STEP of all ResNet-50 launches that share a profile name: FLOPs of the
+    convolutions (explicit-operand and implicit-GEMM launches counted apart, as the profile names
+    them), bytes of the batch-norm kernels (bf16 activations read / written once, the relu mask one
+    bit per element; DESIGN.md "ResNet-50 kernels")."""
     from oracle import resnet_ref as R   # the layer table only; nothing is executed
     hw = {"image": image, "pool1": image // 4}
     cin = {"image": 3, "pool1": 64}
-    fl = {"rn conv fwd": 0.0, "rn conv wgrad": 0.0, "rn conv dgrad": 0.0}
+    fl = {k: 0.0 for k in ("rn conv fwd", "rn conv wgrad", "rn conv dgrad", "rn conv fwd (implicit)",
+                           "rn conv wgrad (implicit)", "rn conv dgrad (implicit)")}
+    by = {k: 0.0 for k in ("rn bn stats", "rn bn apply", "rn bn bwd stats", "rn bn bwd apply")}
     for name_, inp, rk, stride, kout, relu, res in R.units():
         oh = (hw[inp] + 2 * (rk // 2) - rk) // stride + 1
         hw[name_ + "/y"], cin[name_ + "/y"] = oh, kout
         f = 2.0 * B * oh * oh * kout * rk * rk * cin[inp]
-        fl["rn conv fwd"] += f
-        fl["rn conv wgrad"] += f
-        if inp != "image":
-            fl["rn conv dgrad"] += f
+        implicit = not (rk == 1 and stride == 1) and cin[inp] % 64 == 0
+        tag = " (implicit)" if implicit else ""
+        fl["rn conv fwd" + tag] += f
+        fl["rn conv wgrad" + tag] += f
+        if inp != "image":   # stride-2 data gradients stay on the explicit path (dz x W^T, then col2im)
+            fl["rn conv dgrad" + (tag if stride == 1 else "")] += f
+        act = 2.0 * B * oh * oh * kout            # one bf16 activation tensor of this unit
+        bits = act / 16 if relu else 0.0
+        by["rn bn stats"] += act
+        by["rn bn apply"] += act * (3 if res else 2) + bits
+        by["rn bn bwd stats"] += act * 2 + bits
+        by["rn bn bwd apply"] += act * (4 if res else 3) + bits
     if name in fl:
         return "tensor", fl[name]
+    if name in by:
+        return "hbm", by[name]
     return "hbm", None
 
 

@@ -41,11 +41,7 @@ __device__ __forceinline__ void conv_tile_origin(const ConvShape& cs, int mt, in
 }
 
 template <int BLOCK_N>
-constexpr size_t smem_bytes_conv() {
-  return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float) +
-         1024 + 2 * (BLOCK_N / 64) * kOutHalfBytes;   // two bf16 output tile images for the TMA epilogue
-}
+constexpr size_t smem_bytes_conv() { return smem_bytes_persistent<BLOCK_N>(); }   // same layout as the persistent GEMM
 
 // ---- forward (B_MN = true) and stride-1 data gradient (B_MN = false) ---------------------------------
 // map_a: 4-D map over the gathered activation [Nimg_in, H_in, W_in, C], box {64, TW*stride, TH*stride, TN}.
@@ -58,7 +54,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_c, float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int N, int ldc, int tiles_n,
                  int b_rows_per_tap, Epilogue epi) {
-  constexpr int kStages = kMaxStages;
+  constexpr int kStages = persistent_stages<BLOCK_N>();
   constexpr int kBlockK = 64;                                   // bf16 elements of K per stage = one channel block
   constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
   constexpr int kChunkBytes = kBlockK * 128;
@@ -68,15 +64,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kABytes + kBBytes));
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
+  uint8_t* out_stage = smem + kStages * (kABytes + kBBytes);
+  float* stage_base = reinterpret_cast<float*>(out_stage);             // fallback epilogue only
+  uint64_t* full = reinterpret_cast<uint64_t*>(out_stage + 2 * kOutTileBytes);
   uint64_t* empty = full + kStages;
   uint64_t* tmem_full = empty + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
-  uint8_t* out_stage = reinterpret_cast<uint8_t*>(
-      (reinterpret_cast<uintptr_t>(stage_base + 4 * 32 * 33) + 1023) & ~uintptr_t(1023));
-  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = cs.m_tiles * tiles_n;
@@ -108,7 +103,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (lane == 0) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int mt = t % cs.m_tiles, n0 = (t / cs.m_tiles) * BLOCK_N;
+        const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;      // n fastest: the CTAs sharing an A box run together
         int img0, h0;
         conv_tile_origin(cs, mt, &img0, &h0);
         for (int kb = 0; kb < k_blocks; ++kb, ++it) {
@@ -157,7 +152,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else {
     uint32_t tcnt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
-      const int mt = t % cs.m_tiles, n0 = (t / cs.m_tiles) * BLOCK_N;
+      const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;      // n fastest: the CTAs sharing an A box run together
       int img0, h0;
       conv_tile_origin(cs, mt, &img0, &h0);
       const long long m_start = ((long long)img0 * cs.OH + h0) * cs.OW;

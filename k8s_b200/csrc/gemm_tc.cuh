@@ -470,24 +470,33 @@ __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* ou
 // One CTA per SM walks the tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA ring keeps
 // running across tile boundaries and the accumulator is double-buffered in TMEM (2 x BLOCK_N
 // columns): while the epilogue warps drain tile i, the MMA warp already accumulates tile i + 1.
-// Used when the grid is at least two waves deep (the ResNet-50 layers); tile = (m fastest, n, z).
+// Used when the grid is at least two waves deep (the ResNet-50 layers); tile = (n fastest, m, z), so
+// the CTAs that share an A tile run at the same time and the tile comes from DRAM once.
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
 
+// Ring depth of the persistent kernels: whatever fits beside the two output tile images.  The TMA
+// round trip is 2 us and more under load, so bytes in flight per SM = stages x stage size is what
+// sets the bandwidth of the memory-bound GEMMs (1x1 convolutions): 8 x 24 KB / 5 x 32 KB.
+template <int BLOCK_N> constexpr int persistent_stages() { return BLOCK_N == 64 ? 8 : 5; }
+
+// [ring stages][2 output tile images (the fp32 transpose staging of the fallback epilogue aliases
+// them)][barriers][TMEM slot]
 template <int BLOCK_N>
 constexpr size_t smem_bytes_persistent() {
-  return 1024 + static_cast<size_t>(kMaxStages) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         (2 * kMaxStages + 4) * sizeof(uint64_t) + 16 + 4 * 32 * 33 * sizeof(float) +
-         1024 + 2 * (BLOCK_N / 64) * kOutHalfBytes;   // two bf16 output tile images for the TMA epilogue
+  return 1024 + static_cast<size_t>(persistent_stages<BLOCK_N>()) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
+         2 * (BLOCK_N / 64) * kOutHalfBytes + (2 * persistent_stages<BLOCK_N>() + 4) * sizeof(uint64_t) + 16;
 }
+static_assert(2 * kOutHalfBytes >= 4 * 32 * 33 * sizeof(float), "the fp32 staging must fit inside the output images");
+static_assert(smem_bytes_persistent<128>() <= 232448 && smem_bytes_persistent<64>() <= 232448, "shared memory budget");
 
 template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                           const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
                           int tiles_m, int tiles_n, int splits, Epilogue epi) {
-  constexpr int kStages = kMaxStages;
+  constexpr int kStages = persistent_stages<BLOCK_N>();
   constexpr int kElemBytes = KIND == 0 ? 2 : 4;
   constexpr int kBlockK = kBlockKBytes / kElemBytes;
   constexpr int kABytes = kBlockM * kBlockKBytes, kBBytes = BLOCK_N * kBlockKBytes;
@@ -502,15 +511,14 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * (kABytes + kBBytes));
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
+  uint8_t* out_stage = smem + kStages * (kABytes + kBBytes);           // 1024-aligned: every stage is
+  float* stage_base = reinterpret_cast<float*>(out_stage);             // fallback epilogue only
+  uint64_t* full = reinterpret_cast<uint64_t*>(out_stage + 2 * kOutTileBytes);
   uint64_t* empty = full + kStages;
   uint64_t* tmem_full = empty + kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* stage_base = reinterpret_cast<float*>(tmem_slot + 4);
-  uint8_t* out_stage = reinterpret_cast<uint8_t*>(
-      (reinterpret_cast<uintptr_t>(stage_base + 4 * 32 * 33) + 1023) & ~uintptr_t(1023));
-  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = tiles_m * tiles_n * splits;
@@ -540,7 +548,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     if (lane == 0) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int m0 = (t % tiles_m) * kBlockM, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+        const int n0 = (t % tiles_n) * BLOCK_N, m0 = ((t / tiles_n) % tiles_m) * kBlockM, z = t / (tiles_m * tiles_n);
         const int kb_begin = z * k_blocks_per_split, kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const int s = it % kStages;
@@ -599,7 +607,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     // ===== epilogue warps =====
     uint32_t tc = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
-      const int m0 = (t % tiles_m) * kBlockM, n0 = ((t / tiles_m) % tiles_n) * BLOCK_N, z = t / (tiles_m * tiles_n);
+      const int n0 = (t % tiles_n) * BLOCK_N, m0 = ((t / tiles_n) % tiles_m) * kBlockM, z = t / (tiles_m * tiles_n);
       const uint32_t acc = tc & 1, acc_phase = (tc >> 1) & 1;
       if (epi.tma_out) {
         uint8_t* img = out_stage + acc * kOutTileBytes;

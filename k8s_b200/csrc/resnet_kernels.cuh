@@ -30,6 +30,13 @@ __device__ __forceinline__ void ld8(const bf16* p, float (&v)[8]) {
 #pragma unroll
   for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
 }
+// the same in two steps, so that a kernel can issue several loads before it touches the first value
+__device__ __forceinline__ uint4 ldraw(const bf16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void unpack8(const uint4& u, float (&v)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
+}
 __device__ __forceinline__ void st8(bf16* p, const float (&v)[8]) {
   uint4 u;
   __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
@@ -270,21 +277,21 @@ bn_stats_kernel(const bf16* __restrict__ z, float* partial, unsigned int* done, 
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   for (long long r = r0 + rl; r < rend; r += 32 * kBnRowsInFlight) {
-    float v[kBnRowsInFlight][8];
+    uint4 raw[kBnRowsInFlight];   // all loads first (rows past the chunk re-read row r and are not added)
 #pragma unroll
     for (int u = 0; u < kBnRowsInFlight; ++u) {
       const long long rr = r + 32 * u;
-      if (rr < rend) {
-        ld8(z + rr * C + c0, v[u]);
-      } else {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[u][k] = 0.f;
-      }
+      raw[u] = ldraw(z + (rr < rend ? rr : r) * C + c0);
     }
 #pragma unroll
-    for (int u = 0; u < kBnRowsInFlight; ++u)
+    for (int u = 0; u < kBnRowsInFlight; ++u) {
+      if (r + 32 * u < rend) {
+        float v[8];
+        unpack8(raw[u], v);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) { s[k] += v[u][k]; q[k] = fmaf(v[u][k], v[u][k], q[k]); }
+        for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] = fmaf(v[k], v[k], q[k]); }
+      }
+    }
   }
   float fs = 0.f, fq = 0.f;
   if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
@@ -320,23 +327,31 @@ bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, cons
 #pragma unroll
     for (int k = 0; k < 8; ++k) sc[k] = ga[k] * is[k];
   }
-  for (; i < total8; i += stride) {
-    float v[8], rs[8];
-    ld8(z + (i << 3), v);
-    if (residual) ld8(residual + (i << 3), rs);
-    unsigned int bits = 0;
+  for (; i < total8; i += 2 * stride) {
+    const long long i2 = i + stride < total8 ? i + stride : i;   // second element (or the first again: same values rewritten)
+    const uint4 z0 = ldraw(z + (i << 3)), z1 = ldraw(z + (i2 << 3));
+    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+    if (residual) { q0 = ldraw(residual + (i << 3)); q1 = ldraw(residual + (i2 << 3)); }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      float o = fmaf(v[k] - mu[k], sc[k], be[k]);
-      if (residual) o += rs[k];
-      if (relu_bits) {
-        bits |= (o > 0.f ? 1u : 0u) << k;
-        o = fmaxf(o, 0.f);
+    for (int u = 0; u < 2; ++u) {
+      float v[8], rs[8];
+      unpack8(u ? z1 : z0, v);
+      unpack8(u ? q1 : q0, rs);
+      unsigned int bits = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float o = fmaf(v[k] - mu[k], sc[k], be[k]);
+        if (residual) o += rs[k];
+        if (relu_bits) {
+          bits |= (o > 0.f ? 1u : 0u) << k;
+          o = fmaxf(o, 0.f);
+        }
+        v[k] = o;
       }
-      v[k] = o;
+      const long long io = u ? i2 : i;
+      st8(y + (io << 3), v);
+      if (relu_bits) relu_bits[io] = (uint8_t)bits;
     }
-    st8(y + (i << 3), v);
-    if (relu_bits) relu_bits[i] = (uint8_t)bits;
   }
 }
 
@@ -356,19 +371,31 @@ bn_bwd_stats_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ rel
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   ldf8(mean + c0, mu);
   ldf8(invstd + c0, is);
-#pragma unroll 2
-  for (long long r = r0 + rl; r < rend; r += 32) {
-    float g[8], zz[8];
-    const long long e = r * C + c0;
-    ld8(dy + e, g);
-    ld8(z + e, zz);
-    unsigned int bits = 0xffu;
-    if (RELU) bits = relu_bits[e >> 3];
+  constexpr int kFlight = 2;
+  for (long long r = r0 + rl; r < rend; r += 32 * kFlight) {
+    uint4 rg[kFlight], rz[kFlight];
+    unsigned int bits[kFlight];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float gg = (!RELU || ((bits >> k) & 1u)) ? g[k] : 0.f;
-      s[k] += gg;
-      q[k] = fmaf(gg, zz[k] - mu[k], q[k]);      // invstd is applied once, after the sum
+    for (int u = 0; u < kFlight; ++u) {
+      const long long rr = r + 32 * u;
+      const long long e = (rr < rend ? rr : r) * C + c0;
+      rg[u] = ldraw(dy + e);
+      rz[u] = ldraw(z + e);
+      bits[u] = RELU ? (unsigned int)__ldg(relu_bits + (e >> 3)) : 0xffu;
+    }
+#pragma unroll
+    for (int u = 0; u < kFlight; ++u) {
+      if (r + 32 * u < rend) {
+        float g[8], zz[8];
+        unpack8(rg[u], g);
+        unpack8(rz[u], zz);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float gg = (!RELU || ((bits[u] >> k) & 1u)) ? g[k] : 0.f;
+          s[k] += gg;
+          q[k] = fmaf(gg, zz[k] - mu[k], q[k]);      // invstd is applied once, after the sum
+        }
+      }
     }
   }
 #pragma unroll
@@ -408,25 +435,40 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ rel
       k2[k] = k1[k] * is[k] * (k2[k] * inv_m);
     }
   }
-  for (; i < total8; i += stride) {
-    float g[8], zz[8], o[8], prev[8];
-    ld8(dy + (i << 3), g);
-    ld8(z + (i << 3), zz);
-    unsigned int bits = 0xffu;
-    if (RELU) bits = relu_bits[i];
-    if (g_out && g_accumulate) ld8(g_out + (i << 3), prev);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      if (RELU && !((bits >> k) & 1u)) g[k] = 0.f;
-      o[k] = k1[k] * (g[k] - db[k]) - k2[k] * (zz[k] - mu[k]);
+  for (; i < total8; i += 2 * stride) {
+    const long long i2 = i + stride < total8 ? i + stride : i;
+    const bool acc = g_out && g_accumulate;
+    const uint4 g0 = ldraw(dy + (i << 3)), g1 = ldraw(dy + (i2 << 3));
+    const uint4 z0 = ldraw(z + (i << 3)), z1 = ldraw(z + (i2 << 3));
+    unsigned int b0 = 0xffu, b1 = 0xffu;
+    if (RELU) { b0 = __ldg(relu_bits + i); b1 = __ldg(relu_bits + i2); }
+    uint4 p0 = make_uint4(0, 0, 0, 0), p1 = p0;
+    if (acc) {   // not __ldg: g_out is written below
+      p0 = *reinterpret_cast<const uint4*>(g_out + (i << 3));
+      p1 = *reinterpret_cast<const uint4*>(g_out + (i2 << 3));
     }
-    st8(dz + (i << 3), o);
-    if (g_out) {
-      if (g_accumulate) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] += prev[k];
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && i2 == i) break;   // odd tail: the accumulate must not run twice
+      float g[8], zz[8], o[8], prev[8];
+      unpack8(u ? g1 : g0, g);
+      unpack8(u ? z1 : z0, zz);
+      const unsigned int bits = u ? b1 : b0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (RELU && !((bits >> k) & 1u)) g[k] = 0.f;
+        o[k] = k1[k] * (g[k] - db[k]) - k2[k] * (zz[k] - mu[k]);
       }
-      st8(g_out + (i << 3), g);
+      const long long io = u ? i2 : i;
+      st8(dz + (io << 3), o);
+      if (g_out) {
+        if (acc) {
+          unpack8(u ? p1 : p0, prev);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) g[k] += prev[k];
+        }
+        st8(g_out + (io << 3), g);
+      }
     }
   }
 }
