@@ -92,11 +92,12 @@ static cudaError_t launch_cg(const ConvGemm& g, cudaStream_t s) {
   }
   const int tiles_n = (g.N + BN - 1) / BN;
   const long long total = (long long)g.cs.m_tiles * tiles_n;
-  const int grid = (int)std::min<long long>(total, kNumSMs);
   tc::Epilogue epi = g.epi;
   epi.direct = 1;
   epi.tma_out = (g.tma_out && epi.out_bf16 && !epi.mask) ? g.tma_out : 0;
-  tc::conv_gemm_kernel<BN, B_MN><<<grid, tc::kThreads, smem, s>>>(g.a, g.b, epi.tma_out ? g.c : g.a, g.C, g.cs, g.N,
+  if (!epi.tma_out) epi.col_stats = nullptr;
+  const int grid = tc::persistent_grid(total, tiles_n, epi.col_stats != nullptr, kNumSMs);
+  tc::conv_gemm_kernel<BN, B_MN><<<grid, tc::kThreadsPersistent, smem, s>>>(g.a, g.b, epi.tma_out ? g.c : g.a, g.C, g.cs, g.N,
                                                                   g.ldc, tiles_n, g.b_rows_per_tap, epi);
   return cudaGetLastError();
 }

@@ -50,7 +50,7 @@ constexpr size_t smem_bytes_conv() { return smem_bytes_persistent<BLOCK_N>(); } 
 // bf16 tile leaves through map_c, a 4-D map over the output tensor [Nimg, OH, OW, N] with box
 // {64, OW, TH, TN}: the same pixel tile as the A box, so rows past the image are clipped by the TMA unit.
 template <int BLOCK_N, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreadsPersistent, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_c, float* __restrict__ Cout, const __grid_constant__ ConvShape cs, int N, int ldc, int tiles_n,
                  int b_rows_per_tap, Epilogue epi) {
@@ -71,7 +71,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* empty = full + kStages;
   uint64_t* tmem_full = empty + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* img_full = tmem_empty + 2;       // [2] output tile image staged (column-sum warps may read it)
+  uint64_t* img_free = img_full + 2;         // [2] column sums of the image taken
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(img_free + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = cs.m_tiles * tiles_n;
@@ -86,7 +88,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-      for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4);
+        mbar_init(&img_full[a], 1); mbar_init(&img_free[a], kStatsThreads / 32);
+      }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -149,7 +154,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         umma_commit(&tmem_full[acc]);
       }
     }
-  } else {
+  } else if (warp < 6) {
     uint32_t tcnt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
       const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;      // n fastest: the CTAs sharing an A box run together
@@ -161,6 +166,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       if (epi.tma_out) {
         uint8_t* img = out_stage + acc * kOutTileBytes;
         if (warp == 2 && lane == 0) bulk_wait_read<1>();    // the store of two tiles ago has read this image
+        if (epi.col_stats && tcnt >= 2) mbar_wait(&img_free[acc], ((tcnt >> 1) - 1) & 1);   // ... and so have the column sums
         epi_barrier();
         mbar_wait(&tmem_full[acc], acc_phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -175,6 +181,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           for (int h = 0; h < BLOCK_N / 64; ++h)
             if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
           bulk_commit();
+          if (epi.col_stats) mbar_arrive(&img_full[acc]);
         }
         continue;
       }
@@ -190,6 +197,23 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
     }
     if (epi.tma_out && warp == 2 && lane == 0) bulk_wait_all();   // shared memory must outlive the last store
+  } else if (epi.tma_out && epi.col_stats) {
+    // ===== column-sum warps: batch-norm statistics of the staged tiles, off the epilogue's critical path =====
+    uint32_t tcnt = 0;
+    ColStats sums;
+    const int et = threadIdx.x - kThreads;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+      const int mt = t / tiles_n;
+      int img0, h0;
+      conv_tile_origin(cs, mt, &img0, &h0);
+      const int valid = (cs.TN > 1 ? min(cs.TN, cs.Nimg - img0) * cs.OH : min(cs.TH, cs.OH - h0)) * cs.OW;
+      const uint32_t acc = tcnt & 1;
+      mbar_wait(&img_full[acc], (tcnt >> 1) & 1);
+      tile_col_stats<BLOCK_N>(out_stage + acc * kOutTileBytes, et, valid, sums);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&img_free[acc]);
+    }
+    store_col_stats<BLOCK_N>(sums, et, (blockIdx.x % tiles_n) * BLOCK_N, N, blockIdx.x / tiles_n, epi.col_stats);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

@@ -96,8 +96,8 @@ static cudaError_t launch_persistent(const TcGemm& g, float* dst, int ldc, int k
   }
   const int tiles_m = (g.M + tc::kBlockM - 1) / tc::kBlockM, tiles_n = (g.N + BN - 1) / BN;
   const long long total = (long long)tiles_m * tiles_n * splits;
-  const int grid = (int)std::min<long long>(total, kNumSMs);
-  tc::gemm_tc_persistent_kernel<BN, KIND, A_MN, B_MN><<<grid, tc::kThreads, smem, s>>>(
+  const int grid = tc::persistent_grid(total, tiles_n, epi.tma_out && epi.col_stats, kNumSMs);
+  tc::gemm_tc_persistent_kernel<BN, KIND, A_MN, B_MN><<<grid, tc::kThreadsPersistent, smem, s>>>(
       g.a, g.b, epi.tma_out ? g.c : g.a, dst, g.M, g.N, ldc, k_blocks, kps, tiles_m, tiles_n, splits, epi);
   return cudaGetLastError();
 }
@@ -130,9 +130,13 @@ static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_block
   int stages = kps <= 1 ? 1 : kps <= 3 ? 2 : 4;
   if (ctas >= 4ll * kNumSMs) stages = 1;
   else if (ctas >= 2ll * kNumSMs) stages = std::min(stages, 2);
-  if (forced == 1 || forced == 2 || forced == 4) stages = forced;
+  // one wave of CTAs with a long K loop each (split-K weight gradients: K = all pixels): bandwidth is
+  // bytes in flight over the 2 us TMA round trip, so take the deepest ring that fits
+  if (stages == 4 && kps >= 48 && ctas <= kNumSMs) stages = 6;
+  if (forced == 1 || forced == 2 || forced == 4 || forced == 6) stages = forced;
   if (stages == 1) return launch_stage<BN, KIND, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   if (stages == 2) return launch_stage<BN, KIND, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (stages == 6) return launch_stage<BN, KIND, A_MN, B_MN, 6>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   return launch_stage<BN, KIND, A_MN, B_MN, 4>(g, dst, ldc, k_blocks, kps, splits, epi, s);
 }
 

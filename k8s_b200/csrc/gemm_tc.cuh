@@ -27,6 +27,8 @@ constexpr int kBlockM = 128;
 constexpr int kBlockKBytes = 128;      // one 128-B swizzle row of K per stage row
 constexpr int kMaxStages = 4;
 constexpr int kThreads = 192;
+constexpr int kStatsThreads = 256;
+constexpr int kThreadsPersistent = kThreads + kStatsThreads;   // + eight warps that take batch-norm column sums off the epilogue's path
 constexpr long long kWaitLimitCycles = 4000000000ll;   // ~2 s: a wait that long is a bug -> trap, never hang
 
 struct Epilogue {
@@ -37,6 +39,8 @@ struct Epilogue {
   int direct;           // 1: store straight from registers (thread = row), 0: via the smem transpose
   int tma_out;          // persistent kernels, bf16 output through the kernel's output tensor map:
                         // 1 = TMA store of the staged tile, 2 = TMA reduce-add into the destination
+  float* col_stats;     // with tma_out: per-tile column sums of the bf16 output and of its squares,
+                        // [m_tile * parts + slice][2][N] (parts = 256 / BLOCK_N row slices), or NULL
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -466,6 +470,61 @@ __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* ou
   }
 }
 
+// Column sums of the staged bf16 tile images (batch-norm statistics of a convolution output, taken
+// while each tile is still in shared memory) by the eight column-sum warps: thread et owns the
+// column pair et % (BLOCK_N / 2) and one of 256 / (BLOCK_N / 2) row slices, reads its two columns
+// through the swizzle (a warp reads one whole 128-byte row per instruction: conflict-free) and
+// keeps two independent chains per column.  The launch makes the grid a multiple of tiles_n, so
+// with the n-fastest tile order a CTA keeps its column block: the sums run over ALL its tiles in
+// registers and leave as one record per CTA row, stats[(blockIdx.x / tiles_n) * parts + slice][2][N].
+template <int BLOCK_N> constexpr int col_stats_parts() { return kStatsThreads / (BLOCK_N / 2); }   // 4 or 8
+
+struct ColStats {
+  float s0[2] = {0.f, 0.f}, s1[2] = {0.f, 0.f}, q0[2] = {0.f, 0.f}, q1[2] = {0.f, 0.f};
+};
+
+template <int BLOCK_N>
+__device__ __forceinline__ void tile_col_stats(const uint8_t* img, int et, int valid, ColStats& a) {
+  constexpr int kPairs = BLOCK_N / 2;
+  constexpr int kRows = kBlockM / col_stats_parts<BLOCK_N>();
+  const int c = (et % kPairs) * 2, part = et / kPairs;
+  const uint8_t* col = img + (c >> 6) * kOutHalfBytes + (c & 7) * 2;
+  const int j = (c & 63) >> 3;
+  const int r_end = min(valid, (part + 1) * kRows);
+#pragma unroll 1
+  for (int r0 = part * kRows; r0 < r_end; r0 += 8) {   // r0 is a multiple of 8: row r0 + i has swizzle phase i
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (r0 + i < r_end) {
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(col + (r0 + i) * 128 + ((j ^ i) << 4));
+        const float lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xffff0000u);
+        a.s0[i & 1] += lo; a.q0[i & 1] = fmaf(lo, lo, a.q0[i & 1]);
+        a.s1[i & 1] += hi; a.q1[i & 1] = fmaf(hi, hi, a.q1[i & 1]);
+      }
+    }
+  }
+}
+
+template <int BLOCK_N>
+__device__ __forceinline__ void store_col_stats(const ColStats& a, int et, int n0, int N, int cta_row,
+                                                float* __restrict__ stats) {
+  constexpr int kPairs = BLOCK_N / 2;
+  const int c = (et % kPairs) * 2, part = et / kPairs;
+  if (n0 + c < N) {   // N is even
+    float* dst = stats + (static_cast<size_t>(cta_row) * col_stats_parts<BLOCK_N>() + part) * 2 * N + n0 + c;
+    *reinterpret_cast<float2*>(dst) = make_float2(a.s0[0] + a.s0[1], a.s1[0] + a.s1[1]);
+    *reinterpret_cast<float2*>(dst + N) = make_float2(a.q0[0] + a.q0[1], a.q1[0] + a.q1[1]);
+  }
+}
+
+// grid of a persistent launch: one CTA per SM, rounded down to a multiple of tiles_n when column
+// statistics are taken (see above)
+inline int persistent_grid(long long total_tiles, int tiles_n, bool col_stats, int sms) {
+  long long g = total_tiles < sms ? total_tiles : sms;
+  if (col_stats && g >= tiles_n) g -= g % tiles_n;
+  return static_cast<int>(g);
+}
+
 // ---- persistent variant ----------------------------------------------------------------------------
 // One CTA per SM walks the tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The TMA ring keeps
 // running across tile boundaries and the accumulator is double-buffered in TMEM (2 x BLOCK_N
@@ -486,13 +545,13 @@ template <int BLOCK_N> constexpr int persistent_stages() { return BLOCK_N == 64 
 template <int BLOCK_N>
 constexpr size_t smem_bytes_persistent() {
   return 1024 + static_cast<size_t>(persistent_stages<BLOCK_N>()) * (kBlockM * kBlockKBytes + BLOCK_N * kBlockKBytes) +
-         2 * (BLOCK_N / 64) * kOutHalfBytes + (2 * persistent_stages<BLOCK_N>() + 4) * sizeof(uint64_t) + 16;
+         2 * (BLOCK_N / 64) * kOutHalfBytes + (2 * persistent_stages<BLOCK_N>() + 8) * sizeof(uint64_t) + 16;
 }
 static_assert(2 * kOutHalfBytes >= 4 * 32 * 33 * sizeof(float), "the fp32 staging must fit inside the output images");
 static_assert(smem_bytes_persistent<128>() <= 232448 && smem_bytes_persistent<64>() <= 232448, "shared memory budget");
 
 template <int BLOCK_N, int KIND, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreadsPersistent, 1)
 gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                           const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int ldc, int k_blocks, int k_blocks_per_split,
                           int tiles_m, int tiles_n, int splits, Epilogue epi) {
@@ -518,7 +577,9 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
   uint64_t* empty = full + kStages;
   uint64_t* tmem_full = empty + kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* img_full = tmem_empty + 2;       // [2] output tile image staged (column-sum warps may read it)
+  uint64_t* img_free = img_full + 2;         // [2] column sums of the image taken
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(img_free + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = tiles_m * tiles_n * splits;
@@ -530,7 +591,10 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-      for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4); }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4);
+        mbar_init(&img_full[a], 1); mbar_init(&img_free[a], kStatsThreads / 32);
+      }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -603,7 +667,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         umma_commit(&tmem_full[acc]);
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ===== epilogue warps =====
     uint32_t tc = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
@@ -612,6 +676,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
       if (epi.tma_out) {
         uint8_t* img = out_stage + acc * kOutTileBytes;
         if (warp == 2 && lane == 0) bulk_wait_read<1>();    // the store of two tiles ago has read this image
+        if (epi.col_stats && tc >= 2) mbar_wait(&img_free[acc], ((tc >> 1) - 1) & 1);   // ... and so have the column sums
         epi_barrier();
         mbar_wait(&tmem_full[acc], acc_phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -626,6 +691,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
           for (int h = 0; h < BLOCK_N / 64; ++h)
             if (n0 + h * 64 < N) tma_store_2d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, m0, epi.tma_out == 2);
           bulk_commit();
+          if (epi.col_stats) mbar_arrive(&img_full[acc]);
         }
         continue;
       }
@@ -637,6 +703,20 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);       // 4 arrivals (one per epilogue warp) free the half
     }
     if (epi.tma_out && warp == 2 && lane == 0) bulk_wait_all();   // shared memory must outlive the last store
+  } else if (epi.tma_out && epi.col_stats) {
+    // ===== column-sum warps: batch-norm statistics of the staged tiles, off the epilogue's critical path =====
+    uint32_t tc = 0;
+    ColStats sums;
+    const int et = threadIdx.x - kThreads;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
+      const int m0 = ((t / tiles_n) % tiles_m) * kBlockM;
+      const uint32_t acc = tc & 1;
+      mbar_wait(&img_full[acc], (tc >> 1) & 1);
+      tile_col_stats<BLOCK_N>(out_stage + acc * kOutTileBytes, et, min(kBlockM, M - m0), sums);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&img_free[acc]);
+    }
+    store_col_stats<BLOCK_N>(sums, et, (blockIdx.x % tiles_n) * BLOCK_N, N, blockIdx.x / tiles_n, epi.col_stats);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

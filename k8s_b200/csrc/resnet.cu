@@ -51,6 +51,7 @@ struct RnSlot {
   bf16* dcol = nullptr;              // shared staging of data gradients
   uint8_t* pool_arg = nullptr;
   float *bn_partial = nullptr, *splitk = nullptr;
+  float* tile_stats = nullptr;             // per GEMM tile column sums of z (fused batch-norm statistics)
   std::vector<uint8_t*> relu_bits;         // per relu unit: one bit per element of y, set where the relu passed
   unsigned int* bn_done = nullptr;         // per 64-channel group: row chunks finished (self-resetting)
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
@@ -68,7 +69,7 @@ struct ResnetModel {
   std::vector<RnUnit> units;
   int t_image = -1, t_pool_in = -1, t_pool_out = -1, t_last = -1;
   int v_fcw = -1, v_fcb = -1;
-  size_t col_elems = 0, splitk_floats = 0;
+  size_t col_elems = 0, splitk_floats = 0, tile_stats_floats = 0;
   int cmax = 0;
   std::vector<RnSlot> slots;
 };
@@ -118,6 +119,23 @@ static int add_tensor(ResnetModel* m, const std::string& name, long long n, long
 static int reg(tfg_job* j, const std::string& name, std::vector<int64_t> shape, bool trainable, int* var) {
   return tfg_var_register(j, name.c_str(), "VariableV2", TFG_DT_F32, shape.data(), (int)shape.size(), trainable ? 1 : 0,
                           var, nullptr);
+}
+
+// number of [2][kout] column-sum records the forward GEMM of a unit leaves for the batch-norm fold:
+// one per CTA row of the persistent grid and row slice (tc::store_col_stats)
+static int stat_tiles(const RnUnit& u) {
+  const int bn = u.kout >= 128 ? 128 : 64;
+  const int parts = bn == 128 ? tc::col_stats_parts<128>() : tc::col_stats_parts<64>();
+  const int tiles_n = (u.kout + bn - 1) / bn;
+  long long m_tiles;
+  if (u.implicit) {
+    int tn, th;
+    pick_conv_tile(u.g.N, u.g.OH, u.g.OW, false, &tn, &th);
+    m_tiles = (long long)((u.g.N + tn - 1) / tn) * ((u.g.OH + th - 1) / th);
+  } else {
+    m_tiles = ((long long)u.g.N * u.g.OH * u.g.OW + 127) / 128;
+  }
+  return parts * (tc::persistent_grid(m_tiles * tiles_n, tiles_n, true, kNumSMs) / tiles_n);
 }
 
 // conv(R, stride, kout) + BN on tensor `in`; returns the unit index
@@ -199,6 +217,7 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
     const long long splits = std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
     m->splitk_floats = std::max<size_t>(m->splitk_floats, (size_t)(splits * rsc * u.kout));
+    m->tile_stats_floats = std::max<size_t>(m->tile_stats_floats, (size_t)stat_tiles(u) * 2 * u.kout);
   }
   m->splitk_floats = std::max<size_t>(m->splitk_floats, (size_t)8 * 2048 * classes);
 
@@ -239,6 +258,7 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     alloc((void**)&s.dcol, sizeof(bf16) * m->col_elems);
     alloc((void**)&s.pool_arg, (size_t)m->tensors[m->t_pool_out].elems());
     alloc((void**)&s.bn_partial, sizeof(float) * 2 * kBnPartialFloats);
+    alloc((void**)&s.tile_stats, sizeof(float) * m->tile_stats_floats);
     alloc((void**)&s.bn_done, sizeof(unsigned int) * 64);
     if (e == cudaSuccess) e = cudaMemset(s.bn_done, 0, sizeof(unsigned int) * 64);
     alloc((void**)&s.splitk, sizeof(float) * m->splitk_floats);
@@ -271,7 +291,7 @@ void resnet_destroy(tfg_job* j) {
     for (auto p : s.invstd) cudaFree(p);
     for (auto p : s.col) cudaFree(p);
     for (auto p : s.relu_bits) cudaFree(p);
-    cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.bn_done); cudaFree(s.splitk);
+    cudaFree(s.dcol); cudaFree(s.pool_arg); cudaFree(s.bn_partial); cudaFree(s.tile_stats); cudaFree(s.bn_done); cudaFree(s.splitk);
     cudaFree(s.logits); cudaFree(s.loss_vec); cudaFree(s.pooled); cudaFree(s.dpooled); cudaFree(s.dlogits);
   }
   delete m;
@@ -435,6 +455,37 @@ static void bn_chunks(long long M, int C, int* chunks, int* rows) {
   *rows = r;
 }
 
+// TFGRAFT_BN_FUSED=0: batch-norm statistics from a pass over z instead of the GEMM epilogue's column sums
+static bool bn_fused_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    on = 1;
+    if (const char* e = getenv("TFGRAFT_BN_FUSED")) on = atoi(e) != 0;
+  }
+  return on == 1;
+}
+
+// batch statistics of unit i's convolution output: folded from the GEMM epilogue's per-tile column
+// sums when the output went through the TMA path, else reduced from z
+static int bn_forward_stats(tfg_job* j, RnSlot& s, const RnUnit& u, int i, bool fused, bool update_moving) {
+  const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
+  float* mm = update_moving ? u.mov_mean : nullptr;
+  float* mv = update_moving ? u.mov_var : nullptr;
+  const int groups = u.kout / 64;
+  if (fused) {
+    rn::bn_fold_kernel<<<groups, 1024, 0, j->stream>>>(s.tile_stats, stat_tiles(u), M, u.kout, 1e-5f, 0.997f, s.mean[i],
+                                                       s.invstd[i], mm, mv);
+    RN_OK(j, "rn bn fold");
+    return TFG_OK;
+  }
+  int chunks, rows;
+  bn_chunks(M, u.kout, &chunks, &rows);
+  rn::bn_stats_kernel<<<dim3(groups, chunks), 256, 0, j->stream>>>(s.data[u.z], s.bn_partial, s.bn_done, M, u.kout, rows,
+                                                                  1e-5f, 0.997f, s.mean[i], s.invstd[i], mm, mv);
+  RN_OK(j, "rn bn stats");
+  return TFG_OK;
+}
+
 int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int32_t* labels) {
   ResnetModel* m = j->resnet;
   RnSlot& s = m->slots[slot];
@@ -458,17 +509,19 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
     if (u.implicit) {
-      if ((rc = launch_conv_gemm(j, s.ifwd[i], st))) return rc;
+      ConvGemm f = s.ifwd[i];
+      const bool fused = f.tma_out != 0 && bn_fused_enabled();
+      if (fused) f.epi.col_stats = s.tile_stats;
+      if ((rc = launch_conv_gemm(j, f, st))) return rc;
+      if ((rc = bn_forward_stats(j, s, u, (int)i, fused, update_moving))) return rc;
     } else {
       if (!u.direct && (rc = run_im2col(j, u, s.data[u.in], s.col[i]))) return rc;
-      if ((rc = launch_tc(j, s.fwd[i], TFG_MATH_BF16, st))) return rc;
+      TcGemm f = s.fwd[i];
+      const bool fused = f.tma_out != 0 && bn_fused_enabled();
+      if (fused) f.epi.col_stats = s.tile_stats;
+      if ((rc = launch_tc(j, f, TFG_MATH_BF16, st))) return rc;
+      if ((rc = bn_forward_stats(j, s, u, (int)i, fused, update_moving))) return rc;
     }
-    int chunks, rows;
-    bn_chunks(M, u.kout, &chunks, &rows);
-    rn::bn_stats_kernel<<<dim3(u.kout / 64, chunks), 256, 0, st>>>(
-        s.data[u.z], s.bn_partial, s.bn_done, M, u.kout, rows, 1e-5f, 0.997f, s.mean[i], s.invstd[i],
-        update_moving ? u.mov_mean : nullptr, update_moving ? u.mov_var : nullptr);
-    RN_OK(j, "rn bn stats");
     rn::bn_apply_kernel<<<grid_resident(M * u.kout / 8), 256, 0, st>>>(
         s.data[u.z], s.mean[i], s.invstd[i], par(u.v_gamma), par(u.v_beta), u.res >= 0 ? s.data[u.res] : nullptr,
         s.data[u.y], u.relu ? s.relu_bits[i] : nullptr, M * u.kout, u.kout);

@@ -265,7 +265,24 @@ __device__ __forceinline__ bool bn_block_reduce(float (&s)[8], float (&q)[8], fl
   return true;
 }
 
-// forward statistics: mean, invstd (biased variance, eps) and the moving statistics update
+// mean, invstd (biased variance, eps) and the moving statistics update from the folded sums
+// (threads 0..63 of the block that folded channel group blockIdx.x)
+__device__ __forceinline__ void bn_write_stats(float fs, float fq, long long M, float eps, float decay,
+                                               float* __restrict__ mean, float* __restrict__ invstd,
+                                               float* __restrict__ mov_mean, float* __restrict__ mov_var) {
+  if (threadIdx.x >= 64) return;
+  const int c = blockIdx.x * 64 + threadIdx.x;
+  const float mu = fs / (float)M;
+  const float var = fmaxf(fq / (float)M - mu * mu, 0.f);
+  mean[c] = mu;
+  invstd[c] = rsqrtf(var + eps);
+  if (mov_mean) {
+    mov_mean[c] = decay * mov_mean[c] + (1.f - decay) * mu;
+    mov_var[c] = decay * mov_var[c] + (1.f - decay) * var * ((float)M / (float)max(M - 1, 1ll));
+  }
+}
+
+// forward statistics from z itself
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const bf16* __restrict__ z, float* partial, unsigned int* done, long long M, int C, int rows_per_chunk,
                 float eps, float decay, float* __restrict__ mean, float* __restrict__ invstd,
@@ -295,16 +312,36 @@ bn_stats_kernel(const bf16* __restrict__ z, float* partial, unsigned int* done, 
   }
   float fs = 0.f, fq = 0.f;
   if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
-  if (threadIdx.x < 64) {
-    const int c = blockIdx.x * 64 + threadIdx.x;
-    const float mu = fs / (float)M;
-    const float var = fmaxf(fq / (float)M - mu * mu, 0.f);
-    mean[c] = mu;
-    invstd[c] = rsqrtf(var + eps);
-    if (mov_mean) {
-      mov_mean[c] = decay * mov_mean[c] + (1.f - decay) * mu;
-      mov_var[c] = decay * mov_var[c] + (1.f - decay) * var * ((float)M / (float)max(M - 1, 1ll));
-    }
+  bn_write_stats(fs, fq, M, eps, decay, mean, invstd, mov_mean, mov_var);
+}
+
+// The same statistics from the column sums that the convolution's GEMM epilogue left in
+// stats[record][2][C] (sum, sum of squares over the rows one CTA slice saw): z is not read again.
+// At most a few hundred records, so one block of 1024 threads per 64 channels folds them in a
+// single pass: 16 channel quads x 64 strands of interleaved records, then the strands in order.
+__global__ void __launch_bounds__(1024)
+bn_fold_kernel(const float* __restrict__ stats, int records, long long M, int C, float eps, float decay,
+               float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ mov_mean,
+               float* __restrict__ mov_var) {
+  __shared__ float f1[64][65], f2[64][65];
+  const int t = threadIdx.x, quad = t & 15, strand = t >> 4;
+  const float* base = stats + blockIdx.x * 64 + quad * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 4
+  for (int r = strand; r < records; r += 64) {
+    const float4 x = __ldg(reinterpret_cast<const float4*>(base + (size_t)r * 2 * C));
+    const float4 y = __ldg(reinterpret_cast<const float4*>(base + (size_t)r * 2 * C + C));
+    a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+    b.x += y.x; b.y += y.y; b.z += y.z; b.w += y.w;
+  }
+  f1[strand][quad * 4 + 0] = a.x; f1[strand][quad * 4 + 1] = a.y; f1[strand][quad * 4 + 2] = a.z; f1[strand][quad * 4 + 3] = a.w;
+  f2[strand][quad * 4 + 0] = b.x; f2[strand][quad * 4 + 1] = b.y; f2[strand][quad * 4 + 2] = b.z; f2[strand][quad * 4 + 3] = b.w;
+  __syncthreads();
+  if (t < 64) {
+    float fs = 0.f, fq = 0.f;
+#pragma unroll 8
+    for (int l = 0; l < 64; ++l) { fs += f1[l][t]; fq += f2[l][t]; }
+    bn_write_stats(fs, fq, M, eps, decay, mean, invstd, mov_mean, mov_var);
   }
 }
 
