@@ -217,7 +217,7 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
     const long long splits = std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
     m->splitk_floats = std::max<size_t>(m->splitk_floats, (size_t)(splits * rsc * u.kout));
-    m->tile_stats_floats = std::max<size_t>(m->tile_stats_floats, (size_t)stat_tiles(u) * 2 * u.kout);
+    m->tile_stats_floats = std::max<size_t>(m->tile_stats_floats, (size_t)std::max(stat_tiles(u), kNumSMs * 3) * 2 * u.kout);
   }
   m->splitk_floats = std::max<size_t>(m->splitk_floats, (size_t)8 * 2048 * classes);
 
@@ -573,25 +573,25 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     bf16* g_out = nullptr;
     int g_acc = 0;
     if (u.res >= 0) { g_out = s.grad[u.res]; g_acc = written[u.res]; written[u.res] = 1; }
-    const dim3 sgrid(u.kout / 64, chunks);
     const int agrid = grid_resident(M * u.kout / 8);
-    if (u.relu) {
-      rn::bn_bwd_stats_kernel<true><<<sgrid, 256, 0, st>>>(s.grad[u.y], s.relu_bits[i], s.data[u.z], s.mean[i], s.invstd[i],
-                                                            s.bn_partial, s.bn_done, M, u.kout, rows, grd(u.v_beta),
-                                                            grd(u.v_gamma));
-      RN_OK(j, "rn bn bwd stats");
+    if (u.relu)
+      rn::bn_bwd_stats_kernel<true><<<agrid, 256, 0, st>>>(s.grad[u.y], s.relu_bits[i], s.data[u.z], s.mean[i], s.tile_stats,
+                                                           M * u.kout, u.kout);
+    else
+      rn::bn_bwd_stats_kernel<false><<<agrid, 256, 0, st>>>(s.grad[u.y], nullptr, s.data[u.z], s.mean[i], s.tile_stats,
+                                                            M * u.kout, u.kout);
+    RN_OK(j, "rn bn bwd stats");
+    rn::bn_bwd_fold_kernel<<<u.kout / 64, 1024, 0, st>>>(s.tile_stats, agrid, u.kout, s.invstd[i], grd(u.v_beta),
+                                                         grd(u.v_gamma));
+    RN_OK(j, "rn bn bwd fold");
+    if (u.relu)
       rn::bn_bwd_apply_kernel<true><<<agrid, 256, 0, st>>>(s.grad[u.y], s.relu_bits[i], s.data[u.z], s.mean[i], s.invstd[i],
                                                            par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma), s.grad[u.z], g_out,
                                                            g_acc, M * u.kout, u.kout, M);
-    } else {
-      rn::bn_bwd_stats_kernel<false><<<sgrid, 256, 0, st>>>(s.grad[u.y], nullptr, s.data[u.z], s.mean[i], s.invstd[i],
-                                                             s.bn_partial, s.bn_done, M, u.kout, rows, grd(u.v_beta),
-                                                             grd(u.v_gamma));
-      RN_OK(j, "rn bn bwd stats");
+    else
       rn::bn_bwd_apply_kernel<false><<<agrid, 256, 0, st>>>(s.grad[u.y], nullptr, s.data[u.z], s.mean[i], s.invstd[i],
                                                             par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma), s.grad[u.z], g_out,
                                                             g_acc, M * u.kout, u.kout, M);
-    }
     RN_OK(j, "rn bn bwd apply");
     // weight gradient: the im2col operand is the one the forward pass built
     if (u.implicit) {

@@ -393,55 +393,90 @@ bn_apply_kernel(const bf16* __restrict__ z, const float* __restrict__ mean, cons
 }
 
 // backward statistics: dbeta = sum g, dgamma = sum g * xhat, g = dy under the relu mask.
-// Three blocks per SM (<= 85 registers) hide the load latency.
+// Same linear walk as bn_bwd_apply_kernel (a thread keeps its 8 channels, consecutive threads
+// consecutive 16-byte pieces: whole rows, not 128-byte strips), two pieces in flight; the block
+// then adds the threads that share channels (fixed order) and leaves one record
+// stats[blockIdx.x][2][C] = (sum g, sum g * (z - mean)) for bn_bwd_fold_kernel.
 template <bool RELU>
 __global__ void __launch_bounds__(256, 3)
 bn_bwd_stats_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ relu_bits, const bf16* __restrict__ z,
-                    const float* __restrict__ mean, const float* __restrict__ invstd, float* partial,
-                    unsigned int* done, long long M, int C, int rows_per_chunk, float* __restrict__ dbeta,
-                    float* __restrict__ dgamma) {
-  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
-  const int c0 = blockIdx.x * 64 + cg * 8;
-  const long long r0 = (long long)blockIdx.y * rows_per_chunk, rend = min(M, r0 + rows_per_chunk);
-  float s[8], q[8], mu[8], is[8];
+                    const float* __restrict__ mean, float* __restrict__ stats, long long total, int C) {
+  __shared__ float red[2][8][257];
+  const long long total8 = total >> 3;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int c = (int)((i << 3) % C);
+  float s[8], q[8], mu[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
-  ldf8(mean + c0, mu);
-  ldf8(invstd + c0, is);
-  constexpr int kFlight = 2;
-  for (long long r = r0 + rl; r < rend; r += 32 * kFlight) {
-    uint4 rg[kFlight], rz[kFlight];
-    unsigned int bits[kFlight];
+  ldf8(mean + c, mu);
+  for (; i < total8; i += 2 * stride) {
+    const long long i2 = i + stride;
+    const bool two = i2 < total8;
+    const long long j2 = two ? i2 : i;
+    const uint4 g0 = ldraw(dy + (i << 3)), g1 = ldraw(dy + (j2 << 3));
+    const uint4 z0 = ldraw(z + (i << 3)), z1 = ldraw(z + (j2 << 3));
+    unsigned int b0 = 0xffu, b1 = 0xffu;
+    if (RELU) { b0 = __ldg(relu_bits + i); b1 = __ldg(relu_bits + j2); }
+    if (!two) b1 = 0u;                       // the tail piece counts once
 #pragma unroll
-    for (int u = 0; u < kFlight; ++u) {
-      const long long rr = r + 32 * u;
-      const long long e = (rr < rend ? rr : r) * C + c0;
-      rg[u] = ldraw(dy + e);
-      rz[u] = ldraw(z + e);
-      bits[u] = RELU ? (unsigned int)__ldg(relu_bits + (e >> 3)) : 0xffu;
-    }
+    for (int u = 0; u < 2; ++u) {
+      float g[8], zz[8];
+      unpack8(u ? g1 : g0, g);
+      unpack8(u ? z1 : z0, zz);
+      const unsigned int bits = u ? b1 : b0;
 #pragma unroll
-    for (int u = 0; u < kFlight; ++u) {
-      if (r + 32 * u < rend) {
-        float g[8], zz[8];
-        unpack8(rg[u], g);
-        unpack8(rz[u], zz);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float gg = (!RELU || ((bits[u] >> k) & 1u)) ? g[k] : 0.f;
-          s[k] += gg;
-          q[k] = fmaf(gg, zz[k] - mu[k], q[k]);      // invstd is applied once, after the sum
-        }
+      for (int k = 0; k < 8; ++k) {
+        const float gg = ((bits >> k) & 1u) ? g[k] : 0.f;
+        s[k] += gg;
+        q[k] = fmaf(gg, zz[k] - mu[k], q[k]);
       }
     }
   }
+  // threads t and t' hold the same channels iff t = t' (mod C / 8)
+  const int t = threadIdx.x;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) q[k] *= is[k];
-  float fs = 0.f, fq = 0.f;
-  if (!bn_block_reduce(s, q, partial, done, gridDim.y, C, cg, rl, &fs, &fq)) return;
-  if (threadIdx.x < 64) {
-    dbeta[blockIdx.x * 64 + threadIdx.x] = fs;
-    dgamma[blockIdx.x * 64 + threadIdx.x] = fq;
+  for (int k = 0; k < 8; ++k) { red[0][k][t] = s[k]; red[1][k][t] = q[k]; }
+  __syncthreads();
+  const int groups = min(C >> 3, 256);        // distinct channel groups in the block
+  for (int o = t; o < groups * 8; o += 256) {
+    const int grp = o >> 3, k = o & 7;
+    float a = 0.f, b = 0.f;
+    for (int tt = grp; tt < 256; tt += groups) { a += red[0][k][tt]; b += red[1][k][tt]; }
+    // channel of (thread grp of this block, element k): the block's first piece starts at channel
+    // (blockIdx.x * 2048) % C = 0, since C divides 2048
+    const int ch = grp * 8 + k;
+    stats[((size_t)blockIdx.x * 2 + 0) * C + ch] = a;
+    stats[((size_t)blockIdx.x * 2 + 1) * C + ch] = b;
+  }
+}
+
+// dbeta = sum of the records' first halves, dgamma = invstd * sum of the second halves; one
+// block of 1024 threads per 64 channels (see bn_fold_kernel)
+__global__ void __launch_bounds__(1024)
+bn_bwd_fold_kernel(const float* __restrict__ stats, int records, int C, const float* __restrict__ invstd,
+                   float* __restrict__ dbeta, float* __restrict__ dgamma) {
+  __shared__ float f1[64][65], f2[64][65];
+  const int t = threadIdx.x, quad = t & 15, strand = t >> 4;
+  const float* base = stats + blockIdx.x * 64 + quad * 4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll 4
+  for (int r = strand; r < records; r += 64) {
+    const float4 x = __ldg(reinterpret_cast<const float4*>(base + (size_t)r * 2 * C));
+    const float4 y = __ldg(reinterpret_cast<const float4*>(base + (size_t)r * 2 * C + C));
+    a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+    b.x += y.x; b.y += y.y; b.z += y.z; b.w += y.w;
+  }
+  f1[strand][quad * 4 + 0] = a.x; f1[strand][quad * 4 + 1] = a.y; f1[strand][quad * 4 + 2] = a.z; f1[strand][quad * 4 + 3] = a.w;
+  f2[strand][quad * 4 + 0] = b.x; f2[strand][quad * 4 + 1] = b.y; f2[strand][quad * 4 + 2] = b.z; f2[strand][quad * 4 + 3] = b.w;
+  __syncthreads();
+  if (t < 64) {
+    float fs = 0.f, fq = 0.f;
+#pragma unroll 8
+    for (int l = 0; l < 64; ++l) { fs += f1[l][t]; fq += f2[l][t]; }
+    const int ch = blockIdx.x * 64 + t;
+    dbeta[ch] = fs;
+    dgamma[ch] = fq * invstd[ch];
   }
 }
 
