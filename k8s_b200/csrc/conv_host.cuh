@@ -17,6 +17,15 @@ struct ConvGemm {              // forward (b_mn) or stride-1 data gradient (!b_m
   const char* name = "conv";
 };
 
+struct HaloConv {              // 3x3 stride-1 forward (b_mn) or data gradient (!b_mn), input tile resident in smem
+  CUtensorMap a, b, c;         // a: box {64, OW + 2, TH + 2, 1} of the gathered tensor; c: box {64, OW + 2, TH, 1} of the output
+  tc::HaloShape hs;
+  int N = 0, block_n = 128, b_rows_per_tap = 0, tma_out = 1;
+  bool b_mn = true;
+  tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 1, 1, nullptr};
+  const char* name = "conv halo";
+};
+
 struct ConvWgrad {
   CUtensorMap x, dz;
   tc::ConvShape cs;
@@ -32,5 +41,11 @@ void fill_conv_shape(tc::ConvShape* cs, int Nimg, int OH, int OW, int TN, int TH
                      int C, int flip);
 int launch_conv_gemm(tfg_job* j, const ConvGemm& g, cudaStream_t s);
 int launch_conv_wgrad(tfg_job* j, const ConvWgrad& g, cudaStream_t s);
+// 4-D map with an explicit box {64, bw, bh, 1} (element strides 1); bw may exceed W (clipped / zero-filled)
+int make_map_4d_box(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh);
+bool halo_fits(int OH, int OW, int C, int R, int stride);   // can conv3x3_halo_kernel take this layer?
+void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip);
+int halo_grid_rows(const tc::HaloShape& hs, int tiles_n);    // CTA rows of the launch (column-sum records / parts)
+int launch_conv_halo(tfg_job* j, const HaloConv& g, cudaStream_t s);
 
 }  // namespace tfg

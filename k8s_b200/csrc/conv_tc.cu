@@ -39,6 +39,85 @@ int make_map_4d(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, i
   return TFG_OK;
 }
 
+int make_map_4d_box(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh) {
+  PFN_cuTensorMapEncodeTiled enc = encode_fn();
+  if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (C * 2) % 16 != 0)
+    return fail(nullptr, TFG_EINVAL, "activation tensor must be 16-byte aligned with C a multiple of 8");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  if (bw > 256 || bh > 256) return fail(nullptr, TFG_ELIMIT, "TMA box dimension above 256");
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled(4d box) failed with CUresult " + std::to_string((int)r));
+  return TFG_OK;
+}
+
+// conv3x3_halo_kernel: 3x3, stride 1, 64-channel blocks, at least two image rows per 128-position tile
+// and a slab that fits its 32 KB stage
+bool halo_fits(int OH, int OW, int C, int R, int stride) {
+  static int on = -1;
+  if (on < 0) {
+    on = 1;
+    if (const char* e = getenv("TFGRAFT_HALO")) on = atoi(e) != 0;
+  }
+  const int PW = OW + 2;
+  return on == 1 && R == 3 && stride == 1 && C % 64 == 0 && OW >= 12 && PW <= 62 && OH >= 2;
+}
+
+void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip) {
+  hs->Nimg = Nimg; hs->OH = OH; hs->OW = OW; hs->PW = OW + 2;
+  hs->TH = std::max(1, std::min(OH, 128 / hs->PW));
+  hs->h_tiles = (OH + hs->TH - 1) / hs->TH;
+  hs->m_tiles = Nimg * hs->h_tiles;
+  hs->C = C; hs->flip = flip;
+}
+
+int halo_grid_rows(const tc::HaloShape& hs, int tiles_n) {
+  return tc::persistent_grid((long long)hs.m_tiles * tiles_n, tiles_n, true, kNumSMs) / tiles_n;
+}
+
+template <int BN, bool B_MN>
+static cudaError_t launch_halo(const HaloConv& g, cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_halo<BN>();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::conv3x3_halo_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  // Descriptor base-offset field for the shifted slab views: measured on B200, the MMA unit applies
+  // the 128-byte swizzle to absolute shared-memory address bits, so a start address that is a multiple
+  // of 128 B inside a 1024-B-aligned slab needs NO base offset (mode 1 = set it, gives wrong results).
+  static int base_mode = -1;
+  if (base_mode < 0) {
+    base_mode = 0;
+    if (const char* e = getenv("TFGRAFT_HALO_BASE")) base_mode = atoi(e);
+  }
+  const int tiles_n = (g.N + BN - 1) / BN;
+  const long long total = (long long)g.hs.m_tiles * tiles_n;
+  tc::Epilogue epi = g.epi;
+  epi.tma_out = g.tma_out;
+  const int grid = tc::persistent_grid(total, tiles_n, epi.col_stats != nullptr, kNumSMs);
+  tc::conv3x3_halo_kernel<BN, B_MN><<<grid, tc::kThreadsPersistent, smem, s>>>(g.a, g.b, g.c, g.hs, g.N, tiles_n,
+                                                                              g.b_rows_per_tap, base_mode, epi);
+  return cudaGetLastError();
+}
+
+int launch_conv_halo(tfg_job* j, const HaloConv& g, cudaStream_t s) {
+  cudaError_t e;
+  if (g.b_mn) e = g.block_n == 64 ? launch_halo<64, true>(g, s) : launch_halo<128, true>(g, s);
+  else e = g.block_n == 64 ? launch_halo<64, false>(g, s) : launch_halo<128, false>(g, s);
+  if (j) prof_mark(j, g.name);
+  if (e != cudaSuccess) return fail_cuda(j, e, g.name);
+  return TFG_OK;
+}
+
 // Tile of the pixel space: TN images x TH rows x OW columns, at most 128 pixels.  rows_mult16: the
 // pixel count must be a multiple of 16 (wgrad: pixels are the K dimension); rows past the image are
 // then allowed (the TMA unit zero-fills them).

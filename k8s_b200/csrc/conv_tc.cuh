@@ -223,6 +223,205 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   }
 }
 
+// ---- 3x3 stride-1 convolutions with the input tile resident in shared memory -----------------------
+// The kernel above fetches the A operand of every tap through L2 again: nine times the same pixels,
+// and L2 -> SM bandwidth is what bounds it.  Here a tile is TH full image rows; the producer loads,
+// per 64-channel block, ONE slab {64 ch, PW = OW + 2 columns from -1, TH + 2 rows from h0 - 1}
+// (borders zero-filled by the TMA unit): (TH + 2) * PW positions of 128 B, contiguous, position
+// q = hh * PW + ww.  Output row m of the MMA stands for (oh, ow') = (m / PW, m % PW); its input at
+// tap (r, s) is slab position m + r * PW + s, so the A operand of a tap is the SAME slab read from a
+// start address (r * PW + s) * 128 B further on -- a shifted K-major 128B-swizzled matrix (the swizzle
+// phase of the new start goes into the descriptor's base-offset field).  Rows with ow' >= OW or
+// beyond the tile's rows are not outputs: the epilogue stages zeros for them and the TMA store's box
+// {64, PW, TH} clips them at the tensor edge.  dgrad (flip): the taps are mirrored.
+struct HaloShape {
+  int Nimg, OH, OW, PW, TH, h_tiles, m_tiles, C, flip;
+};
+
+constexpr int kSlabBytes = 32 * 1024;       // >= (128 + 2 * PW + 2) * 128 for PW <= 62
+constexpr int kSlabStages = 2;
+template <int BLOCK_N> constexpr int halo_b_stages() { return BLOCK_N == 64 ? 8 : 6; }
+
+template <int BLOCK_N>
+constexpr size_t smem_bytes_halo() {
+  return 1024 + kSlabStages * kSlabBytes + static_cast<size_t>(halo_b_stages<BLOCK_N>()) * BLOCK_N * kBlockKBytes +
+         2 * (BLOCK_N / 64) * kOutHalfBytes + (2 * kSlabStages + 2 * halo_b_stages<BLOCK_N>() + 8) * sizeof(uint64_t) + 16;
+}
+static_assert(smem_bytes_halo<128>() <= 232448 && smem_bytes_halo<64>() <= 232448, "shared memory budget");
+
+// map_a: 4-D map over the gathered activation [Nimg, OH, OW, C], box {64, PW, TH + 2, 1}.
+// map_b: as conv_gemm_kernel.  map_c: 4-D map over the output [Nimg, OH, OW, N], box {64, PW, TH, 1}.
+template <int BLOCK_N, bool B_MN>
+__global__ void __launch_bounds__(kThreadsPersistent, 1)
+conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const __grid_constant__ CUtensorMap map_c, const __grid_constant__ HaloShape hs, int N, int tiles_n,
+                    int b_rows_per_tap, int base_offset_mode, Epilogue epi) {
+  constexpr int kBStages = halo_b_stages<BLOCK_N>();
+  constexpr int kBBytes = BLOCK_N * kBlockKBytes;
+  constexpr int kChunkBytes = 64 * 128;
+  constexpr uint32_t kStepB = B_MN ? (16 * 128) >> 4 : 32 >> 4;
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* slab = smem;
+  uint8_t* smem_b = slab + kSlabStages * kSlabBytes;
+  uint8_t* out_stage = smem_b + kBStages * kBBytes;
+  uint64_t* slab_full = reinterpret_cast<uint64_t*>(out_stage + 2 * kOutTileBytes);
+  uint64_t* slab_empty = slab_full + kSlabStages;
+  uint64_t* b_full = slab_empty + kSlabStages;
+  uint64_t* b_empty = b_full + kBStages;
+  uint64_t* tmem_full = b_empty + kBStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* img_full = tmem_empty + 2;
+  uint64_t* img_free = img_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(img_free + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = hs.m_tiles * tiles_n;
+  const int cblocks = hs.C / 64;
+  const uint32_t slab_tx = static_cast<uint32_t>((hs.TH + 2) * hs.PW * 128);
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_c)) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kSlabStages; ++s) { mbar_init(&slab_full[s], 1); mbar_init(&slab_empty[s], 1); }
+      for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 4);
+        mbar_init(&img_full[a], 1); mbar_init(&img_free[a], kStatsThreads / 32);
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(smem_u32(tmem_slot)), "n"(2 * BLOCK_N) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: per channel block one slab, then the nine taps' weight tiles =====
+    if (lane == 0) {
+      uint32_t sit = 0, bit = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;
+        const int img0 = mt / hs.h_tiles, h0 = (mt % hs.h_tiles) * hs.TH;
+        for (int cb = 0; cb < cblocks; ++cb, ++sit) {
+          const int ss = sit % kSlabStages;
+          mbar_wait(&slab_empty[ss], ((sit / kSlabStages) & 1) ^ 1);
+          mbar_expect_tx(&slab_full[ss], slab_tx);
+          tma_load_4d(slab + ss * kSlabBytes, &map_a, &slab_full[ss], cb * 64, -1, h0 - 1, img0);
+          for (int tap = 0; tap < 9; ++tap, ++bit) {
+            const int s = bit % kBStages;
+            mbar_wait(&b_empty[s], ((bit / kBStages) & 1) ^ 1);
+            mbar_expect_tx(&b_full[s], kBBytes);
+            const int krow = tap * b_rows_per_tap;
+            if (B_MN) {
+#pragma unroll
+              for (int c = 0; c < BLOCK_N / 64; ++c)
+                tma_load_2d(smem_b + s * kBBytes + c * kChunkBytes, &map_b, &b_full[s], n0 + c * 64, krow + cb * 64);
+            } else {
+              tma_load_2d(smem_b + s * kBBytes, &map_b, &b_full[s], cb * 64, krow + n0);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
+      uint32_t sit = 0, bit = 0, tcnt = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int cb = 0; cb < cblocks; ++cb, ++sit) {
+          const int ss = sit % kSlabStages;
+          mbar_wait(&slab_full[ss], (sit / kSlabStages) & 1);
+          const uint32_t slab_addr = smem_u32(slab + ss * kSlabBytes);
+          for (int tap = 0; tap < 9; ++tap, ++bit) {
+            const int s = bit % kBStages;
+            mbar_wait(&b_full[s], (bit / kBStages) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int r = tap / 3, sx = tap - r * 3;
+            const int shift = hs.flip ? (2 - r) * hs.PW + (2 - sx) : r * hs.PW + sx;   // slab positions
+            const uint32_t a_addr = slab_addr + static_cast<uint32_t>(shift) * 128u;
+            uint64_t da = make_smem_desc(a_addr, 16);
+            if (base_offset_mode) da |= static_cast<uint64_t>((a_addr >> 7) & 7u) << 49;
+            const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma<0>(d_tmem, da + 2 * k, db + kStepB * k, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&b_empty[s]);
+          }
+          umma_commit(&slab_empty[ss]);
+        }
+        umma_commit(&tmem_full[acc]);
+      }
+    }
+  } else if (warp < 6) {
+    // ===== epilogue warps =====
+    uint32_t tcnt = 0;
+    const int m = (warp & 3) * 32 + lane;                 // this thread's row of every tile
+    const int oh = m / hs.PW, owp = m - oh * hs.PW;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+      const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;
+      const int img0 = mt / hs.h_tiles, h0 = (mt % hs.h_tiles) * hs.TH;
+      const bool keep = owp < hs.OW && oh < hs.TH && h0 + oh < hs.OH;
+      const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
+      uint8_t* img = out_stage + acc * kOutTileBytes;
+      if (warp == 2 && lane == 0) bulk_wait_read<1>();
+      if (epi.col_stats && tcnt >= 2) mbar_wait(&img_free[acc], ((tcnt >> 1) - 1) & 1);
+      epi_barrier();
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      drain_tile_staged<BLOCK_N>(tmem_base + acc * BLOCK_N, img, warp, lane, n0, epi, keep);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      epi_barrier();
+      if (warp == 2 && lane == 0) {
+#pragma unroll
+        for (int h = 0; h < BLOCK_N / 64; ++h)
+          if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
+        bulk_commit();
+        if (epi.col_stats) mbar_arrive(&img_full[acc]);
+      }
+    }
+    if (warp == 2 && lane == 0) bulk_wait_all();
+  } else if (epi.col_stats) {
+    // ===== column-sum warps (rows that are not outputs were staged as zeros) =====
+    uint32_t tcnt = 0;
+    ColStats sums;
+    const int et = threadIdx.x - kThreads;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
+      const uint32_t acc = tcnt & 1;
+      mbar_wait(&img_full[acc], (tcnt >> 1) & 1);
+      tile_col_stats<BLOCK_N>(out_stage + acc * kOutTileBytes, et, kBlockM, sums);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&img_free[acc]);
+    }
+    store_col_stats<BLOCK_N>(sums, et, (blockIdx.x % tiles_n) * BLOCK_N, N, blockIdx.x / tiles_n, epi.col_stats);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * BLOCK_N) : "memory");
+  }
+}
+
 // ---- weight gradient ---------------------------------------------------------------------------------
 // dW[(r,s,c), k] = sum over pixels.  The pixel tiles are the K dimension: both operands are MN-major
 // boxes of P = TN*TH*OW pixel rows (P a multiple of 16, rows past the image zero-filled):

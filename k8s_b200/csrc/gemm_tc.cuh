@@ -427,9 +427,10 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void*
 
 // TMEM accumulator -> bf16 tile image in `out_stage` (BLOCK_N / 64 halves of kOutHalfBytes);
 // bias and relu applied on the way.  Called by the four epilogue warps.
+// keep = false: this thread's row is not part of the output (halo convolution) and is staged as zeros.
 template <int BLOCK_N>
 __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* out_stage, int warp, int lane, int n0,
-                                                  const Epilogue& epi) {
+                                                  const Epilogue& epi, bool keep = true) {
   const int q = warp & 3;
   const int row = q * 32 + lane;
 #pragma unroll 1
@@ -452,7 +453,7 @@ __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* ou
     for (int u = 0; u < 4; ++u) {
       float v[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(r[u * 8 + k]);
+      for (int k = 0; k < 8; ++k) v[k] = keep ? __uint_as_float(r[u * 8 + k]) : 0.f;
       if (epi.bias) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) v[k] += epi.bias[n0 + c0 + u * 8 + k];

@@ -37,6 +37,7 @@ struct RnUnit {                      // conv + batch norm (+ residual add) (+ re
   int kout = 0;
   int in = -1, res = -1, z = -1, y = -1;   // tensor ids
   bool relu = true, direct = false;        // direct: 1x1 stride 1, the activation itself is the GEMM operand
+  bool halo = false;                       // 3x3 stride 1 with the input tile resident in shared memory (conv3x3_halo_kernel)
   bool implicit = false;                   // implicit GEMM through 4-D TMA boxes (C % 64 == 0): no im2col either
   int v_w = -1, v_gamma = -1, v_beta = -1;
   float *mov_mean = nullptr, *mov_var = nullptr;   // per job
@@ -57,6 +58,7 @@ struct RnSlot {
   float *logits = nullptr, *loss_vec = nullptr, *dbn = nullptr;   // dbn: [2][Cmax] dbeta, dgamma staging unused
   bf16 *pooled = nullptr, *dpooled = nullptr, *dlogits = nullptr;
   std::vector<TcGemm> fwd, wgrad, dgrad;   // per unit (explicit-operand GEMMs)
+  std::vector<HaloConv> hfwd, hdgrad;      // per unit (halo kernel)
   std::vector<ConvGemm> ifwd, idgrad;      // per unit (implicit GEMM)
   std::vector<ConvWgrad> iwgrad;
   TcGemm fc_fwd, fc_wgrad, fc_dgrad;
@@ -121,6 +123,13 @@ static int reg(tfg_job* j, const std::string& name, std::vector<int64_t> shape, 
                           var, nullptr);
 }
 
+// split-K factor of a weight-gradient GEMM with `tiles` output tiles: as many splits as keep
+// tiles * splits within ONE wave of CTAs (rounding up instead leaves a second wave of a few CTAs
+// that doubles the kernel's time)
+static long long wgrad_splits(long long tiles) {
+  return std::max<long long>(1, std::min<long long>(64, kNumSMs / tiles));
+}
+
 // number of [2][kout] column-sum records the forward GEMM of a unit leaves for the batch-norm fold:
 // one per CTA row of the persistent grid and row slice (tc::store_col_stats)
 static int stat_tiles(const RnUnit& u) {
@@ -128,6 +137,11 @@ static int stat_tiles(const RnUnit& u) {
   const int parts = bn == 128 ? tc::col_stats_parts<128>() : tc::col_stats_parts<64>();
   const int tiles_n = (u.kout + bn - 1) / bn;
   long long m_tiles;
+  if (u.halo) {
+    tc::HaloShape hs;
+    fill_halo_shape(&hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0);
+    return parts * halo_grid_rows(hs, tiles_n);
+  }
   if (u.implicit) {
     int tn, th;
     pick_conv_tile(u.g.N, u.g.OH, u.g.OW, false, &tn, &th);
@@ -156,6 +170,7 @@ static int add_unit(tfg_job* j, ResnetModel* m, const std::string& name, int in,
   u.kout = kout; u.in = in; u.res = res; u.relu = relu;
   u.direct = (R == 1 && stride == 1);
   u.implicit = !u.direct && (x.c % 64 == 0) && getenv("TFGRAFT_NO_IMPLICIT") == nullptr;
+  u.halo = u.implicit && tma_out_enabled() && halo_fits(u.g.OH, u.g.OW, u.g.C, R, stride);
   u.z = add_tensor(m, name + "/z", x.n, u.g.OH, u.g.OW, kout);
   u.y = add_tensor(m, name + "/y", x.n, u.g.OH, u.g.OW, kout);
   int dummy;
@@ -215,7 +230,7 @@ int resnet_build(tfg_job* j, int batch, int image_hw, int classes) {
     const long long rsc = (long long)u.g.R * u.g.S * u.g.C;
     const int bn = u.kout >= 128 ? 128 : 64;
     const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
-    const long long splits = std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
+    const long long splits = wgrad_splits(tiles);
     m->splitk_floats = std::max<size_t>(m->splitk_floats, (size_t)(splits * rsc * u.kout));
     m->tile_stats_floats = std::max<size_t>(m->tile_stats_floats, (size_t)std::max(stat_tiles(u), kNumSMs * 3) * 2 * u.kout);
   }
@@ -316,6 +331,8 @@ static int prepare_maps(tfg_job* j, int slot) {
   s.fwd.assign(nu, TcGemm());
   s.wgrad.assign(nu, TcGemm());
   s.dgrad.assign(nu, TcGemm());
+  s.hfwd.assign(nu, HaloConv());
+  s.hdgrad.assign(nu, HaloConv());
   s.ifwd.assign(nu, ConvGemm());
   s.idgrad.assign(nu, ConvGemm());
   s.iwgrad.assign(nu, ConvWgrad());
@@ -324,6 +341,23 @@ static int prepare_maps(tfg_job* j, int slot) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
     const int rsc = u.g.R * u.g.S * u.g.C;
+    if (u.halo) {
+      const int bn = u.kout >= 128 ? 128 : 64, bnd = u.g.C >= 128 ? 128 : 64;
+      HaloConv& f = s.hfwd[i];
+      fill_halo_shape(&f.hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0);
+      f.name = "rn conv fwd (halo)"; f.N = u.kout; f.block_n = bn; f.b_mn = true; f.b_rows_per_tap = u.g.C; f.tma_out = 1;
+      f.epi.out_bf16 = s.data[u.z];
+      if ((rc = make_map_4d_box(&f.a, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, f.hs.PW, f.hs.TH + 2))) return rc;
+      if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
+      if ((rc = make_map_4d_box(&f.c, s.data[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, f.hs.PW, f.hs.TH))) return rc;
+      HaloConv& d = s.hdgrad[i];
+      fill_halo_shape(&d.hs, u.g.N, u.g.H, u.g.W, u.kout, 1);
+      d.name = "rn conv dgrad (halo)"; d.N = u.g.C; d.block_n = bnd; d.b_mn = false; d.b_rows_per_tap = u.g.C;
+      d.epi.out_bf16 = s.grad[u.in];
+      if ((rc = make_map_4d_box(&d.a, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, d.hs.PW, d.hs.TH + 2))) return rc;
+      if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
+      if ((rc = make_map_4d_box(&d.c, s.grad[u.in], u.g.N, u.g.H, u.g.W, u.g.C, d.hs.PW, d.hs.TH))) return rc;
+    }
     if (u.implicit) {
       const int bn = u.kout >= 128 ? 128 : 64;
       int tn, th;
@@ -346,7 +380,7 @@ static int prepare_maps(tfg_job* j, int slot) {
       fill_conv_shape(&w.cs, u.g.N, u.g.OH, u.g.OW, tn, th, u.g.R, u.g.S, u.g.stride, u.g.pad, u.g.C, 0);
       const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
       w.name = "rn conv wgrad (implicit)"; w.M = rsc; w.N = u.kout; w.block_n = bn; w.C = grd(u.v_w); w.partial = s.splitk;
-      w.splits = (int)std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
+      w.splits = (int)wgrad_splits(tiles);
       if ((rc = make_map_4d(&w.x, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.OW, th, tn, u.g.stride))) return rc;
       if ((rc = make_map_4d(&w.dz, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.OW, th, tn, 1))) return rc;
       // data gradient, stride 1: tiles of input pixels, A = boxes of dz at the mirrored tap offsets
@@ -386,7 +420,7 @@ static int prepare_maps(tfg_job* j, int slot) {
     TcGemm& w = s.wgrad[i];
     const long long tiles = ((rsc + 127) / 128) * ((u.kout + bn - 1) / bn);
     w.name = "rn conv wgrad"; w.M = rsc; w.N = u.kout; w.K = (int)M; w.C = grd(u.v_w); w.ldc = u.kout; w.block_n = bn;
-    w.splits = (int)std::max<long long>(1, std::min<long long>(64, (kNumSMs + tiles - 1) / tiles));
+    w.splits = (int)wgrad_splits(tiles);
     w.partial = s.splitk; w.a_mn = true; w.b_mn = true;
     if ((rc = make_map(&w.a, kind, a_ptr, rsc, M, a_ld, tc::kBlockM, true))) return rc;
     if ((rc = make_map(&w.b, kind, s.grad[u.z], u.kout, M, u.kout, bn, true))) return rc;
@@ -508,7 +542,13 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
   for (size_t i = 0; i < m->units.size(); ++i) {
     const RnUnit& u = m->units[i];
     const long long M = (long long)u.g.N * u.g.OH * u.g.OW;
-    if (u.implicit) {
+    if (u.halo) {
+      HaloConv f = s.hfwd[i];
+      const bool fused = bn_fused_enabled();
+      if (fused) f.epi.col_stats = s.tile_stats;
+      if ((rc = launch_conv_halo(j, f, st))) return rc;
+      if ((rc = bn_forward_stats(j, s, u, (int)i, fused, update_moving))) return rc;
+    } else if (u.implicit) {
       ConvGemm f = s.ifwd[i];
       const bool fused = f.tma_out != 0 && bn_fused_enabled();
       if (fused) f.epi.col_stats = s.tile_stats;
@@ -603,7 +643,11 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     // data gradient
     TcGemm d = s.dgrad[i];
     const long long in_elems = m->tensors[u.in].elems();
-    if (u.implicit && u.g.stride == 1) {
+    if (u.halo) {
+      HaloConv dg = s.hdgrad[i];
+      dg.tma_out = written[u.in] ? 2 : 1;
+      if ((rc = launch_conv_halo(j, dg, st))) return rc;
+    } else if (u.implicit && u.g.stride == 1) {
       ConvGemm dg = s.idgrad[i];
       if (dg.tma_out) {
         dg.epi.out_bf16 = s.grad[u.in];
