@@ -132,27 +132,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
-      uint32_t it = 0, tcnt = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
-        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+    // converged warp, one elected lane issues (gemm_tc.cuh, "lean issue path")
+    constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
+    constexpr uint32_t hi = desc_hi();
+    const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    const uint32_t tmem_full0 = smem_u32(tmem_full), tmem_empty0 = smem_u32(tmem_empty);
+    uint32_t st = 0, ph = 0, acc = 0, acc_ph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      mbar_wait_addr(tmem_empty0 + acc * 8, acc_ph ^ 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        mbar_wait_addr(full0 + st * 8, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < k_blocks; ++kb, ++it) {
-          const int s = it % kStages;
-          const uint32_t phase = (it / kStages) & 1;
-          mbar_wait(&full[s], phase);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), 16);
-          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16);
+        const uint32_t a_lo = desc_lo(a0 + st * kABytes, 16), b_lo = desc_lo(b0 + st * kBBytes, B_MN ? kChunkBytes : 16);
+        if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma<0>(d_tmem, da + 2 * k, db + kStepB * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-          umma_commit(&empty[s]);
+          for (int k = 0; k < 4; ++k) umma2<0>(d_tmem, a_lo + 2 * k, hi, b_lo + kStepB * k, hi, idesc, kb > 0 || k > 0);
+          umma_commit_addr(empty0 + st * 8);
         }
-        umma_commit(&tmem_full[acc]);
+        __syncwarp();
+        if (++st == kStages) { st = 0; ph ^= 1; }
       }
+      if (elect_one()) umma_commit_addr(tmem_full0 + acc * 8);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_ph ^= 1;
     }
   } else if (warp < 6) {
     uint32_t tcnt = 0;
@@ -336,38 +342,50 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
-      uint32_t sit = 0, bit = 0, tcnt = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
-        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int cb = 0; cb < cblocks; ++cb, ++sit) {
-          const int ss = sit % kSlabStages;
-          mbar_wait(&slab_full[ss], (sit / kSlabStages) & 1);
-          const uint32_t slab_addr = smem_u32(slab + ss * kSlabBytes);
-          for (int tap = 0; tap < 9; ++tap, ++bit) {
-            const int s = bit % kBStages;
-            mbar_wait(&b_full[s], (bit / kBStages) & 1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int r = tap / 3, sx = tap - r * 3;
-            const int shift = hs.flip ? (2 - r) * hs.PW + (2 - sx) : r * hs.PW + sx;   // slab positions
-            const uint32_t a_addr = slab_addr + static_cast<uint32_t>(shift) * 128u;
-            uint64_t da = make_smem_desc(a_addr, 16);
-            if (base_offset_mode) da |= static_cast<uint64_t>((a_addr >> 7) & 7u) << 49;
-            const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16);
+    // ===== MMA issuer: the warp stays converged, one elected lane issues (see gemm_tc.cuh) =====
+    constexpr uint32_t idesc = make_idesc(1, BLOCK_N, false, B_MN);
+    constexpr uint32_t hi = desc_hi();
+    const uint32_t slab0 = smem_u32(slab), b0 = smem_u32(smem_b);
+    const uint32_t slab_full0 = smem_u32(slab_full), slab_empty0 = smem_u32(slab_empty);
+    const uint32_t b_full0 = smem_u32(b_full), b_empty0 = smem_u32(b_empty);
+    const uint32_t tmem_full0 = smem_u32(tmem_full), tmem_empty0 = smem_u32(tmem_empty);
+    uint32_t shift8[9];                                   // tap offset in 16-byte units of the descriptor address
+#pragma unroll
+    for (int tap = 0; tap < 9; ++tap) {
+      const int r = tap / 3, sx = tap % 3;
+      shift8[tap] = static_cast<uint32_t>(hs.flip ? (2 - r) * hs.PW + (2 - sx) : r * hs.PW + sx) * 8u;
+    }
+    uint32_t ss = 0, sph = 0, bs = 0, bph = 0, acc = 0, acc_ph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      mbar_wait_addr(tmem_empty0 + acc * 8, acc_ph ^ 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int cb = 0; cb < cblocks; ++cb) {
+        mbar_wait_addr(slab_full0 + ss * 8, sph);
+        const uint32_t a_base = desc_lo(slab0 + ss * kSlabBytes, 16);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          mbar_wait_addr(b_full0 + bs * 8, bph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_lo = a_base + shift8[tap];
+          const uint32_t b_lo = desc_lo(b0 + bs * kBBytes, B_MN ? kChunkBytes : 16);
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              umma<0>(d_tmem, da + 2 * k, db + kStepB * k, idesc, (cb > 0 || tap > 0 || k > 0) ? 1u : 0u);
-            umma_commit(&b_empty[s]);
+              umma2<0>(d_tmem, a_lo + 2 * k, hi, b_lo + kStepB * k, hi, idesc, cb > 0 || tap > 0 || k > 0);
+            umma_commit_addr(b_empty0 + bs * 8);
           }
-          umma_commit(&slab_empty[ss]);
+          __syncwarp();
+          if (++bs == kBStages) { bs = 0; bph ^= 1; }
         }
-        umma_commit(&tmem_full[acc]);
+        if (elect_one()) umma_commit_addr(slab_empty0 + ss * 8);
+        __syncwarp();
+        if (++ss == kSlabStages) { ss = 0; sph ^= 1; }
       }
+      if (elect_one()) umma_commit_addr(tmem_full0 + acc * 8);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_ph ^= 1;
     }
   } else if (warp < 6) {
     // ===== epilogue warps =====
@@ -509,30 +527,36 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(1, BLOCK_N, true, true);
-      uint32_t it = 0, tcnt = 0;
-      const int k_steps = P / 16;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
-        const int z = t / (tiles_m * tiles_n);
-        const int kt_begin = z * k_tiles_per_split, kt_end = min(k_tiles, kt_begin + k_tiles_per_split);
-        const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+    // converged warp, one elected lane issues (gemm_tc.cuh, "lean issue path")
+    constexpr uint32_t idesc = make_idesc(1, BLOCK_N, true, true);
+    constexpr uint32_t hi = desc_hi();
+    const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    const uint32_t tmem_full0 = smem_u32(tmem_full), tmem_empty0 = smem_u32(tmem_empty);
+    const int k_steps = P / 16;
+    uint32_t st = 0, ph = 0, acc = 0, acc_ph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int z = t / (tiles_m * tiles_n);
+      const int kt_begin = z * k_tiles_per_split, kt_end = min(k_tiles, kt_begin + k_tiles_per_split);
+      mbar_wait_addr(tmem_empty0 + acc * 8, acc_ph ^ 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kt = kt_begin; kt < kt_end; ++kt) {
+        mbar_wait_addr(full0 + st * 8, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kt = kt_begin; kt < kt_end; ++kt, ++it) {
-          const int s = it % kStages;
-          const uint32_t phase = (it / kStages) & 1;
-          mbar_wait(&full[s], phase);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kAStage), chunk_bytes);
-          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBStage), chunk_bytes);
+        const uint32_t a_lo = desc_lo(a0 + st * kAStage, chunk_bytes), b_lo = desc_lo(b0 + st * kBStage, chunk_bytes);
+        if (elect_one()) {
           for (int k = 0; k < k_steps; ++k)                   // 16 pixel rows = 2048 B per instruction
-            umma<0>(d_tmem, da + 128u * k, db + 128u * k, idesc, (kt > kt_begin || k > 0) ? 1u : 0u);
-          umma_commit(&empty[s]);
+            umma2<0>(d_tmem, a_lo + 128u * k, hi, b_lo + 128u * k, hi, idesc, kt > kt_begin || k > 0);
+          umma_commit_addr(empty0 + st * 8);
         }
-        umma_commit(&tmem_full[acc]);
+        __syncwarp();
+        if (++st == kStages) { st = 0; ph ^= 1; }
       }
+      if (elect_one()) umma_commit_addr(tmem_full0 + acc * 8);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_ph ^= 1;
     }
   } else {
     uint32_t tcnt = 0;

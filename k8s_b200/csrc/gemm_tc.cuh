@@ -56,21 +56,23 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
                :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 
+// Wait with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the
+// hint expires) instead of spinning.  A CTA here holds up to 14 warps of which ONE thread issues
+// all the MMAs; twelve warps polling without the hint took three quarters of that thread's issue
+// slots (tensor pipe 40 % active with every operand already in shared memory).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
   long long t0 = 0;
-  for (uint32_t spin = 0;; ++spin) {
+  for (;;) {
     uint32_t done;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        : "=r"(done) : "r"(addr), "r"(parity), "r"(1000000u) : "memory");
     if (done) return;
-    if ((spin & 1023u) == 1023u) {
-      if (t0 == 0) t0 = clock64();
-      else if (clock64() - t0 > kWaitLimitCycles) __trap();
-    }
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > kWaitLimitCycles) __trap();
   }
 }
 
@@ -122,6 +124,60 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t desc_a, uint64_t 
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+
+// ---- lean issue path -----------------------------------------------------------------------------
+// ONE thread issues every MMA of a CTA, so the instructions between two tcgen05.mma set the pace of
+// the tensor pipe (measured: ~100 instructions per K block held it at 40 %).  The MMA warp therefore
+// runs converged (values stay warp-uniform), waits as a warp, and elects a lane only for the issue;
+// descriptors are kept as a constant high word and a 32-bit low word that is bumped by constants.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// low word: start address >> 4 in [0,14), leading byte offset >> 4 in [16,30)
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+// high word: stride byte offset >> 4 in [0,14), version 1 at bit 14, layout type at bit 29
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes = 1024, uint32_t layout_type = 2) {
+  return (sbo_bytes >> 4) | (1u << 14) | (layout_type << 29);
+}
+template <int KIND>
+__device__ __forceinline__ void umma2(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                      uint32_t idesc, bool accumulate) {
+  if (KIND == 0) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+        :: "r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate ? 1u : 0u) : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n\t}"
+        :: "r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate ? 1u : 0u) : "memory");
+  }
+}
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar_addr) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar_addr) : "memory");
+}
+// mbar_wait on a shared-memory address (no generic-to-shared conversion in the loop)
+__device__ __forceinline__ void mbar_wait_addr(uint32_t addr, uint32_t parity) {
+  long long t0 = 0;
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity), "r"(1000000u) : "memory");
+    if (done) return;
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > kWaitLimitCycles) __trap();
   }
 }
 
@@ -352,26 +408,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
-      for (int i = 0; i < n_kb; ++i) {
-        const int s = i % kStages;
-        const uint32_t phase = (i / kStages) & 1;
-        mbar_wait(&full[s], phase);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        constexpr bool kBase32 = KIND == 1;   // MN-major tf32: 32-byte-base swizzle, 4-line atoms
-        const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), A_MN ? kChunkBytes : 16,
-                                           (A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
-        const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16,
-                                           (B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
+    // ===== MMA issuer: converged warp, one elected lane issues ("lean issue path") =====
+    constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
+    constexpr bool kBase32 = KIND == 1;   // MN-major tf32: 32-byte-base swizzle, 4-line atoms
+    constexpr uint32_t hi_a = desc_hi((A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
+    constexpr uint32_t hi_b = desc_hi((B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
+    const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    uint32_t st = 0, ph = 0;
+    for (int i = 0; i < n_kb; ++i) {
+      mbar_wait_addr(full0 + st * 8, ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a_lo = desc_lo(a0 + st * kABytes, A_MN ? kChunkBytes : 16);
+      const uint32_t b_lo = desc_lo(b0 + st * kBBytes, B_MN ? kChunkBytes : 16);
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < kBlockK / kUmmaK; ++k)    // 32 bytes of K per instruction
-          umma<KIND>(tmem_base, da + kStepA * k, db + kStepB * k, idesc, (i | k) != 0);
-        umma_commit(&empty[s]);                        // frees the stage when these MMAs retire
+          umma2<KIND>(tmem_base, a_lo + kStepA * k, hi_a, b_lo + kStepB * k, hi_b, idesc, (i | k) != 0);
+        umma_commit_addr(empty0 + st * 8);             // frees the stage when these MMAs retire
       }
-      umma_commit(tmem_full);                          // accumulator complete
+      __syncwarp();
+      if (++st == kStages) { st = 0; ph ^= 1; }
     }
+    if (elect_one()) umma_commit_addr(smem_u32(tmem_full));   // accumulator complete
+    __syncwarp();
   } else {
     // ===== epilogue =====
     if (n_kb > 0) {
@@ -639,34 +699,40 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: accumulator `acc` alternates between the two TMEM halves =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
-      constexpr bool kBase32 = KIND == 1;
-      uint32_t it = 0, tc = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tc) {
-        const int z = t / (tiles_m * tiles_n);
-        const int kb_begin = z * k_blocks_per_split, kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
-        const uint32_t acc = tc & 1, acc_phase = (tc >> 1) & 1;
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);      // the epilogue has drained this half
+    // ===== MMA issuer: accumulator `acc` alternates between the two TMEM halves; converged warp,
+    // one elected lane issues ("lean issue path") =====
+    constexpr uint32_t idesc = make_idesc(KIND == 0 ? 1 : 2, BLOCK_N, A_MN, B_MN);
+    constexpr bool kBase32 = KIND == 1;
+    constexpr uint32_t hi_a = desc_hi((A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
+    constexpr uint32_t hi_b = desc_hi((B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
+    const uint32_t a0 = smem_u32(smem_a), b0 = smem_u32(smem_b);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    const uint32_t tmem_full0 = smem_u32(tmem_full), tmem_empty0 = smem_u32(tmem_empty);
+    uint32_t st = 0, ph = 0, acc = 0, acc_ph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int z = t / (tiles_m * tiles_n);
+      const int kb_begin = z * k_blocks_per_split, kb_end = min(k_blocks, kb_begin + k_blocks_per_split);
+      mbar_wait_addr(tmem_empty0 + acc * 8, acc_ph ^ 1);      // the epilogue has drained this half
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait_addr(full0 + st * 8, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
-          const int s = it % kStages;
-          const uint32_t phase = (it / kStages) & 1;
-          mbar_wait(&full[s], phase);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint64_t da = make_smem_desc(smem_u32(smem_a + s * kABytes), A_MN ? kChunkBytes : 16,
-                                             (A_MN && kBase32) ? 512 : 1024, (A_MN && kBase32) ? 1 : 2);
-          const uint64_t db = make_smem_desc(smem_u32(smem_b + s * kBBytes), B_MN ? kChunkBytes : 16,
-                                             (B_MN && kBase32) ? 512 : 1024, (B_MN && kBase32) ? 1 : 2);
+        const uint32_t a_lo = desc_lo(a0 + st * kABytes, A_MN ? kChunkBytes : 16);
+        const uint32_t b_lo = desc_lo(b0 + st * kBBytes, B_MN ? kChunkBytes : 16);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k)
-            umma<KIND>(d_tmem, da + kStepA * k, db + kStepB * k, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
-          umma_commit(&empty[s]);
+            umma2<KIND>(d_tmem, a_lo + kStepA * k, hi_a, b_lo + kStepB * k, hi_b, idesc, kb > kb_begin || k > 0);
+          umma_commit_addr(empty0 + st * 8);
         }
-        umma_commit(&tmem_full[acc]);
+        __syncwarp();
+        if (++st == kStages) { st = 0; ph ^= 1; }
       }
+      if (elect_one()) umma_commit_addr(tmem_full0 + acc * 8);
+      __syncwarp();
+      acc ^= 1;
+      if (acc == 0) acc_ph ^= 1;
     }
   } else if (warp < 6) {
     // ===== epilogue warps =====
