@@ -275,9 +275,12 @@ def config_dict(a, n: int, math: str) -> dict:
 
 
 # ---- algorithmic work per launch of every kernel in the step (DESIGN.md "Kernels") ----------
-def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int):
-    """-> (bound, amount per launch): FLOPs for the contractions ("tensor"), bytes for the
-    rest ("hbm").  B = examples per replica."""
+def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int, math: str = "bf16",
+                     peaks: dict | None = None):
+    """-> (bound, amount per launch): FLOPs ("tensor") or bytes ("hbm").  B = examples per replica.
+    A contraction is charged to whichever of its two rooflines takes longer at the measured peaks
+    (operands read once + output written once against HBM, 2 M N K against the tensor pipe): the
+    thin-K GEMMs of this model (conv2 dgrad: K = 64, an 800-wide output) are HBM-bound."""
     M2 = B * 196
     gemm = {"gemm conv2 fwd": (M2, 64, 800), "gemm conv2 dgrad": (M2, 800, 64), "gemm conv2 wgrad": (800, 64, M2),
             "gemm fc1 fwd": (B, 1024, 3136), "gemm fc1 dgrad": (B, 3136, 1024), "gemm fc1 wgrad": (3136, 1024, B),
@@ -285,7 +288,13 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
     name = name[3:] if name.startswith("tc ") else name     # the tensor-path GEMMs carry a "tc " prefix
     if name in gemm:
         m, n, k = gemm[name]
-        return "tensor", 2.0 * m * n * k
+        flops = 2.0 * m * n * k
+        esz = 2 if math == "bf16" else 4
+        out = 2 if (math == "bf16" and name == "gemm conv2 dgrad") else 4   # dcol is kept in bf16, the rest fp32
+        nbytes = float((m * k + n * k) * esz + m * n * out)
+        if peaks and nbytes / (peaks["hbm_gbs"] * 1e9) > flops / (peaks["bf16_tflops_sustained"] * 1e12):
+            return "hbm", nbytes
+        return "tensor", flops
     f = 4
     hbm = {
         "conv1_pool_relu_kernel": B * 784 * f + B * 6272 * (f + 1),
@@ -297,6 +306,9 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
         "col2im_mask_kernel": M2 * 800 * f + B * 6272 * 2 * f,
         "softmax_xent_kernel": B * (10 * 2 * f + 2 * f),
         "push_apply_pull_kernel": n_params * f * (n_replicas + 2 + (2 if opt != "sgd" else 0)),
+        # three launches per step (conv2 wgrad 21 splits of 800x64, fc1 fwd 7 of Bx1024, fc1 dgrad 3 of Bx3136):
+        # partials read once, result written once; the average launch
+        "split-K reduce": f * ((21 + 1) * 800 * 64 + (7 + 1) * B * 1024 + (3 + 1) * B * 3136) / 3.0,
     }
     if name in hbm:
         return "hbm", float(hbm[name])
@@ -516,7 +528,7 @@ def run_graft(a) -> dict:
     if rank == 0:
         total = sum(v["ms"] for v in prof.values()) or 1.0
         top = max(prof, key=lambda k_: prof[k_]["ms"])
-        bound, amount = algorithmic_work(top, B, 3274634, a.opt, n)
+        bound, amount = algorithmic_work(top, B, 3274634, a.opt, n, math, peaks)
         per_launch_ms = prof[top]["ms"] / prof[top]["count"]
         if resnet:   # per-layer launches share a name: work = the sum over the 53 convolutions, per step
             bound, amount = resnet_work(top, B, a.image, a.classes)

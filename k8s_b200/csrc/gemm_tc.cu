@@ -199,23 +199,30 @@ template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-// row-major im2col of a1[B,14,14,32] in operand precision: col[m, (kh*5+kw)*32 + c]
+// row-major im2col of a1[B,14,14,32] in operand precision: col[m, (kh*5+kw)*32 + c]; a thread moves
+// 16 bytes of col (4 fp32 / 8 bf16 channels)
 template <typename T>
 __global__ void __launch_bounds__(256)
 im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
-  const long long total = (long long)B * 196 * 25 * 8;
+  constexpr int kPer = 16 / sizeof(T);          // channels per thread
+  constexpr int kGroups = 32 / kPer;            // threads per tap
+  const long long total = (long long)B * 196 * 25 * kGroups;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int c4 = (int)(i & 7);
-    const int kk = (int)((i >> 3) % 25);
-    const long long m = (i >> 3) / 25;
+    const int cg = (int)(i % kGroups);
+    const int kk = (int)((i / kGroups) % 25);
+    const long long m = (i / kGroups) / 25;
     const int ow = (int)(m % 14), oh = (int)((m / 14) % 14);
     const long long b = m / 196;
     const int ih = oh + kk / 5 - 2, iw = ow + kk % 5 - 2;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (ih >= 0 && ih < 14 && iw >= 0 && iw < 14)
-      v = *reinterpret_cast<const float4*>(a1 + ((b * 14 + ih) * 14 + iw) * 32 + c4 * 4);
-    store4(col + m * 800 + kk * 32 + c4 * 4, v);
+    const bool ok = ih >= 0 && ih < 14 && iw >= 0 && iw < 14;
+    const float* src = a1 + ((b * 14 + ih) * 14 + iw) * 32 + cg * kPer;
+    T* dst = col + m * 800 + kk * 32 + cg * kPer;
+#pragma unroll
+    for (int q = 0; q < kPer / 4; ++q) {
+      const float4 v = ok ? *reinterpret_cast<const float4*>(src + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      store4(dst + 4 * q, v);
+    }
   }
 }
 
@@ -371,6 +378,11 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
                64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
   if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
                128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+  if (bf) {   // dcol is the step's largest tensor: keep it in bf16, written through the TMA store epilogue
+    t->conv2_dgrad.epi.out_bf16 = s.dcol;
+    t->conv2_dgrad.tma_out = 1;
+    if ((rc = make_map(&t->conv2_dgrad.c, kind, s.dcol, M2, 800, 800, tc::kBlockM, false))) return rc;
+  }
   return TFG_OK;
 }
 
@@ -384,7 +396,7 @@ static int tc_forward_t(tfg_job* j, int slot) {
   int rc = mnist_tc_prepare(j, slot);
   if (rc) return rc;
   // conv2 as im2col GEMM
-  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 200), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
+  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 25 * (32 / (16 / (int)sizeof(T)))), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
   TC_LAUNCH_OK(j, "im2col_lp_kernel");
   if ((rc = launch_tc(j, t->conv2_fwd, m->math, st))) return rc;
   if ((rc = mnist_pool2(j, slot, t->a2_lp))) return rc;     // also drops the bf16 copy of a2

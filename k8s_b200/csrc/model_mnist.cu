@@ -203,8 +203,19 @@ relu_mask_kernel(const float* __restrict__ g, const float* __restrict__ a, float
 }
 
 // ===== col2im: dcol[B*196, 800] -> g1m[B,14,14,32], masked by a1 > 0 ======================
+// T = float, or bf16 when the tensor path's data-gradient GEMM stored dcol in bf16 (half the bytes
+// of the step's largest tensor)
+__device__ __forceinline__ float4 load4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 load4(const __nv_bfloat16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+
+template <typename T>
 __global__ void __launch_bounds__(256)
-col2im_mask_kernel(const float* __restrict__ dcol, const float* __restrict__ a1,
+col2im_mask_kernel(const T* __restrict__ dcol, const float* __restrict__ a1,
                    float* __restrict__ g1m, int B) {
   const long long total = (long long)B * 196 * 8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -222,8 +233,7 @@ col2im_mask_kernel(const float* __restrict__ dcol, const float* __restrict__ a1,
       for (int kw = 0; kw < 5; ++kw) {
         const int ow = w - kw + 2;
         if (ow < 0 || ow >= 14) continue;
-        const float4 v = *reinterpret_cast<const float4*>(
-            dcol + ((b * 14 + oh) * 14 + ow) * 800 + (kh * 5 + kw) * 32 + c4 * 4);
+        const float4 v = load4(dcol + ((b * 14 + oh) * 14 + ow) * 800 + (kh * 5 + kw) * 32 + c4 * 4);
         s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
     }
@@ -741,7 +751,11 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   }
   // db2 = sum over pooled positions of the masked pooled gradient
   if ((rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
-  col2im_mask_kernel<<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
+  if (m->math == TFG_MATH_BF16)   // the tensor path's dgrad GEMM stored dcol as bf16 (mnist_tc_prepare)
+    col2im_mask_kernel<__nv_bfloat16><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(
+        reinterpret_cast<const __nv_bfloat16*>(s.dcol), s.a1, s.g1m, B);
+  else
+    col2im_mask_kernel<float><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
   LAUNCH_OK(j, "col2im_mask_kernel");
   conv1_bwd_kernel<<<2 * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
