@@ -315,6 +315,16 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
     return "hbm", None
 
 
+def measured_traffic(model: str, kernel: str):
+    """DRAM bytes per launch of `kernel` from this round's ncu capture (profiles/r1_traffic.json), at the
+    default batch sizes; None when that kernel was not captured."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            return json.load(f).get("%s:%s" % (model, kernel))
+    except (OSError, ValueError):
+        return None
+
+
 def resnet_work(name: str, B: int, image: int, classes: int):
     """Algorithmic work per STEP of all ResNet-50 launches that share a profile name: FLOPs of the
     convolutions (explicit-operand and implicit-GEMM launches counted apart, as the profile names
@@ -534,7 +544,9 @@ def run_graft(a) -> dict:
             bound, amount = resnet_work(top, B, a.image, a.classes)
             per_launch_ms = prof[top]["ms"] / a.steps
         roof = {"kernel": top, "bound": bound, "share_of_step": prof[top]["ms"] / total,
-                "ms_per_launch": per_launch_ms, "traffic": None, "peak_source": peaks["source"]}
+                "ms_per_launch": per_launch_ms, "traffic": (measured_traffic("resnet50" if resnet else "mnist", top)
+                            if n == 1 and B == (256 if resnet else 128) else None),   # captured at these sizes only
+                "peak_source": peaks["source"]}
         if amount is not None and bound == "tensor":
             ach = amount / (per_launch_ms * 1e-3) / 1e12
             roof.update(achieved=ach, peak=peaks["bf16_tflops_sustained"], unit="TFLOP/s",
