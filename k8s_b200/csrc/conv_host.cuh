@@ -39,6 +39,7 @@ int make_map_4d(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, i
 void pick_conv_tile(int Nimg, int OH, int OW, bool rows_mult16, int* TN, int* TH);
 void fill_conv_shape(tc::ConvShape* cs, int Nimg, int OH, int OW, int TN, int TH, int R, int S, int stride, int pad,
                      int C, int flip);
+int fill_dgrad_s2_class(tc::ConvShape* cs, int R, int ph, int pw);
 int launch_conv_gemm(tfg_job* j, const ConvGemm& g, cudaStream_t s);
 int launch_conv_wgrad(tfg_job* j, const ConvWgrad& g, cudaStream_t s);
 // 4-D map with an explicit box {64, bw, bh, 1} (element strides 1); bw may exceed W (clipped / zero-filled)

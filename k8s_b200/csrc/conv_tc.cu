@@ -148,6 +148,29 @@ void fill_conv_shape(tc::ConvShape* cs, int Nimg, int OH, int OW, int TN, int TH
   cs->h_tiles = (OH + TH - 1) / TH;
   cs->m_tiles = ((Nimg + TN - 1) / TN) * cs->h_tiles;
   cs->R = R; cs->S = S; cs->stride = stride; cs->pad = pad; cs->C = C; cs->flip = flip;
+  cs->ntaps = 0; cs->out_stride = 1; cs->out_h0 = 0; cs->out_w0 = 0;
+  for (int t = 0; t < 9; ++t) cs->tap_dh[t] = cs->tap_dw[t] = cs->tap_w[t] = 0;
+}
+
+// Parity class (ph, pw) of the data gradient of an R x R (R = 1 or 3), stride-2, pad R/2 convolution:
+// dx[2i + ph, 2j + pw] = sum over the taps (r, s) with (ph + pad - r), (pw + pad - s) even of
+// dz[i + (ph + pad - r) / 2, j + (pw + pad - s) / 2] * W[r, s].  Returns the number of taps (0: the
+// class receives no gradient from this convolution).
+int fill_dgrad_s2_class(tc::ConvShape* cs, int R, int ph, int pw) {
+  const int pad = R / 2;
+  int n = 0;
+  for (int r = 0; r < R; ++r)
+    for (int s = 0; s < R; ++s) {
+      const int a = ph + pad - r, b = pw + pad - s;
+      if ((a & 1) || (b & 1)) continue;
+      cs->tap_dh[n] = (signed char)(a / 2);     // a in {-1..2}: exact for even a
+      cs->tap_dw[n] = (signed char)(b / 2);
+      cs->tap_w[n] = (signed char)(r * R + s);
+      ++n;
+    }
+  cs->ntaps = n;
+  cs->out_stride = 2; cs->out_h0 = ph; cs->out_w0 = pw;
+  return n;
 }
 
 __global__ void __launch_bounds__(256)

@@ -24,6 +24,14 @@ struct ConvShape {
   int R, S, stride, pad;
   int C;                     // channels of the gathered tensor (K dimension per tap), multiple of 64
   int flip;                  // 0: tap offset (+r - pad, +s - pad) scaled by stride (forward / wgrad); 1: (pad - r, pad - s) (dgrad)
+  // conv_gemm_kernel only.  ntaps > 0: an explicit tap list replaces the R x S walk -- tap t gathers
+  // at offset (tap_dh[t], tap_dw[t]) and multiplies by filter tap tap_w[t] (row block tap_w[t] of the
+  // weight matrix).  The tile at pixel rows h0.. is stored at rows h0 * out_stride + out_h0 (columns
+  // from out_w0) of the output map, whose element strides are out_stride: one parity class of a
+  // stride-2 data gradient, dx[2i + ph, 2j + pw] = sum_t dz[i + dh_t, j + dw_t] W[tap_t].
+  int ntaps;
+  signed char tap_dh[9], tap_dw[9], tap_w[9];
+  int out_stride, out_h0, out_w0;
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
@@ -78,7 +86,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = cs.m_tiles * tiles_n;
   const int cblocks = cs.C / 64;
-  const int k_blocks = cs.R * cs.S * cblocks;
+  const int k_blocks = (cs.ntaps > 0 ? cs.ntaps : cs.R * cs.S) * cblocks;
   const int box_rows = cs.TN * cs.TH * cs.OW;                   // rows one A box writes (<= 128)
 
   if (warp == 0 && lane == 0) {
@@ -118,9 +126,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const int r = tap / cs.S, sx = tap - r * cs.S;
           mbar_wait(&empty[s], phase ^ 1);
           mbar_expect_tx(&full[s], box_rows * 128 + kBBytes);
-          const int ch = cs.flip ? cs.pad - r : r - cs.pad, cw = cs.flip ? cs.pad - sx : sx - cs.pad;
+          int ch = cs.flip ? cs.pad - r : r - cs.pad, cw = cs.flip ? cs.pad - sx : sx - cs.pad, wtap = tap;
+          if (cs.ntaps > 0) { ch = cs.tap_dh[tap]; cw = cs.tap_dw[tap]; wtap = cs.tap_w[tap]; }
           tma_load_4d(smem_a + s * kABytes, &map_a, &full[s], cb * 64, cw, h0 * cs.stride + ch, img0);
-          const int krow = tap * b_rows_per_tap;                // first row of this tap in W viewed [R*S*C_w, Kout]
+          const int krow = wtap * b_rows_per_tap;               // first row of this tap in W viewed [R*S*C_w, Kout]
           if (B_MN) {                                           // rows = K (channel block of the tap), columns = n
 #pragma unroll
             for (int c = 0; c < BLOCK_N / 64; ++c)
@@ -185,7 +194,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (warp == 2 && lane == 0) {
 #pragma unroll
           for (int h = 0; h < BLOCK_N / 64; ++h)
-            if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
+            if (n0 + h * 64 < N)
+              tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, cs.out_w0, h0 * cs.out_stride + cs.out_h0, img0,
+                           epi.tma_out == 2);
           bulk_commit();
           if (epi.col_stats) mbar_arrive(&img_full[acc]);
         }

@@ -12,6 +12,7 @@
 // Batch norm uses batch statistics (two-stage fixed-order reductions), eps 1e-5, and keeps
 // moving statistics with decay 0.997.
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -59,6 +60,7 @@ struct RnSlot {
   bf16 *pooled = nullptr, *dpooled = nullptr, *dlogits = nullptr;
   std::vector<TcGemm> fwd, wgrad, dgrad;   // per unit (explicit-operand GEMMs)
   std::vector<HaloConv> hfwd, hdgrad;      // per unit (halo kernel)
+  std::vector<std::array<ConvGemm, 4>> s2dgrad;   // per stride-2 implicit unit: one data-gradient GEMM per output parity class (ntaps == 0: none)
   std::vector<ConvGemm> ifwd, idgrad;      // per unit (implicit GEMM)
   std::vector<ConvWgrad> iwgrad;
   TcGemm fc_fwd, fc_wgrad, fc_dgrad;
@@ -101,6 +103,17 @@ static bool tma_out_enabled() {
 // element-wise kernels with a grid-stride loop and three resident blocks per SM: one full wave
 static inline int grid_resident(long long n, int per = 256) {
   return (int)std::max<long long>(1, std::min<long long>((n + per - 1) / per, kNumSMs * 3));
+}
+
+// TFGRAFT_S2_DGRAD=0: stride-2 data gradients through dz x W^T and a col2im gather instead of the
+// parity-class GEMMs
+static bool s2_dgrad_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    on = 1;
+    if (const char* e = getenv("TFGRAFT_S2_DGRAD")) on = atoi(e) != 0;
+  }
+  return on == 1;
 }
 
 #define RN_OK(j, what)                                           \
@@ -333,6 +346,7 @@ static int prepare_maps(tfg_job* j, int slot) {
   s.dgrad.assign(nu, TcGemm());
   s.hfwd.assign(nu, HaloConv());
   s.hdgrad.assign(nu, HaloConv());
+  s.s2dgrad.assign(nu, std::array<ConvGemm, 4>());
   s.ifwd.assign(nu, ConvGemm());
   s.idgrad.assign(nu, ConvGemm());
   s.iwgrad.assign(nu, ConvWgrad());
@@ -397,6 +411,25 @@ static int prepare_maps(tfg_job* j, int slot) {
         if (tma_out_enabled()) {   // store or reduce-add (chosen per call) straight into the input's gradient
           d.tma_out = 1;
           if ((rc = make_map_4d(&d.c, s.grad[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.W, th, tn, 1))) return rc;
+        }
+      }
+      // data gradient, stride 2: one GEMM per parity class of the input position, tiles over the
+      // OUTPUT pixel space (A = boxes of dz at the class's tap offsets), stored through a map of the
+      // input gradient with element strides 2 -- no dcol, no col2im
+      if (u.g.stride == 2 && u.in != m->t_image && tma_out_enabled() && s2_dgrad_enabled() && u.g.H == 2 * u.g.OH &&
+          u.g.W == 2 * u.g.OW && 2 * u.g.OW <= 256) {
+        const int bnd = u.g.C >= 128 ? 128 : 64;
+        pick_conv_tile(u.g.N, u.g.OH, u.g.OW, false, &tn, &th);
+        for (int cls = 0; cls < 4; ++cls) {
+          ConvGemm& d = s.s2dgrad[i][cls];
+          fill_conv_shape(&d.cs, u.g.N, u.g.OH, u.g.OW, tn, th, 1, 1, 1, 0, u.kout, 0);
+          if (fill_dgrad_s2_class(&d.cs, u.g.R, cls >> 1, cls & 1) == 0) continue;
+          d.name = "rn conv dgrad (stride 2)"; d.N = u.g.C; d.ldc = u.g.C; d.block_n = bnd; d.b_mn = false;
+          d.b_rows_per_tap = u.g.C; d.C = nullptr; d.tma_out = 1;
+          d.epi = tc::Epilogue{nullptr, nullptr, 0, s.grad[u.in], 1};
+          if ((rc = make_map_4d(&d.a, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, u.g.OW, th, tn, 1))) return rc;
+          if ((rc = make_map(&d.b, kind, wlp(u.v_w), rsc, u.kout, u.kout, bnd, false))) return rc;
+          if ((rc = make_map_4d(&d.c, s.grad[u.in], u.g.N, u.g.H, u.g.W, u.g.C, u.g.OW, th, tn, 2))) return rc;
         }
       }
     }
@@ -674,6 +707,20 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
         if ((rc = launch_tc(j, d, TFG_MATH_BF16, st))) return rc;
         rn::add_bf16_kernel<<<grid_for(in_elems / 8), 256, 0, st>>>(s.dcol, s.grad[u.in], in_elems, 1);
         RN_OK(j, "rn grad add");
+      }
+    } else if (u.implicit && (s.s2dgrad[i][0].cs.ntaps > 0)) {
+      // stride 2: the parity classes write disjoint positions; a 1x1 convolution reaches the
+      // (even, even) class only, so a gradient buffer nobody wrote yet is cleared first
+      const bool partial_cover = s.s2dgrad[i][3].cs.ntaps == 0;
+      if (!written[u.in] && partial_cover) {
+        cudaError_t e = cudaMemsetAsync(s.grad[u.in], 0, sizeof(bf16) * (size_t)in_elems, st);
+        if (e != cudaSuccess) return fail_cuda(j, e, "cudaMemsetAsync(input gradient)");
+      }
+      for (int cls = 0; cls < 4; ++cls) {
+        ConvGemm dg = s.s2dgrad[i][cls];
+        if (dg.cs.ntaps == 0) continue;
+        dg.tma_out = (written[u.in] || partial_cover) ? 2 : 1;
+        if ((rc = launch_conv_gemm(j, dg, st))) return rc;
       }
     } else {
       d.epi.out_bf16 = s.dcol;
