@@ -61,7 +61,7 @@ struct tfg_job {
   float* accum = nullptr;
   void* params_lp = nullptr;           // bf16 shadow of `params`, kept current by the apply kernel (bf16 math only)
   std::vector<float*> grads;           // one flat buffer per local replica slot
-  float* loss = nullptr;               // [TFG_MAX_REPLICAS + 1]; [r] = replica r, last = mean
+  float* loss = nullptr;               // [TFG_MAX_REPLICAS + 2]; [r] = replica r, then the mean, then the error word (dev_err)
   uint32_t* flags = nullptr;           // [TFG_MAX_GPUS] barrier epochs written by peers
   int* dev_err = nullptr;              // device-side error word (barrier timeout)
   tfg::Segment* d_segs = nullptr;

@@ -177,13 +177,11 @@ int tfg_job_destroy(tfg_job* j) {
     for (float* g : j->grads) cudaFree(g);
     cudaFree(j->loss);
     cudaFree(j->flags);
-    cudaFree(j->dev_err);
     cudaFree(j->dev_epoch);
     for (auto& g : j->step_graphs)
       if (g.exec) cudaGraphExecDestroy(g.exec);
     cudaFree(j->d_segs);
     if (j->h_loss) cudaFreeHost(j->h_loss);
-    if (j->h_err) cudaFreeHost(j->h_err);
     if (j->own_stream && j->stream) cudaStreamDestroy(j->stream);
     cudaGetLastError();
   }
@@ -202,17 +200,17 @@ int tfg_job_bind(tfg_job* j, int cuda_device, void* stream) {
     TFG_CUDA(j, cudaStreamCreateWithFlags(&j->stream, cudaStreamNonBlocking));
     j->own_stream = true;
   }
-  TFG_CUDA(j, cudaMalloc(&j->loss, sizeof(float) * (TFG_MAX_REPLICAS + 1)));
-  TFG_CUDA(j, cudaMemset(j->loss, 0, sizeof(float) * (TFG_MAX_REPLICAS + 1)));
+  // [replica losses | mean loss | error word]: the last two words are read back by ONE 8-byte copy per step
+  TFG_CUDA(j, cudaMalloc(&j->loss, sizeof(float) * (TFG_MAX_REPLICAS + 2)));
+  TFG_CUDA(j, cudaMemset(j->loss, 0, sizeof(float) * (TFG_MAX_REPLICAS + 2)));
+  j->dev_err = reinterpret_cast<int*>(j->loss + TFG_MAX_REPLICAS + 1);
   TFG_CUDA(j, cudaMalloc(&j->flags, sizeof(uint32_t) * TFG_MAX_GPUS));
   TFG_CUDA(j, cudaMemset(j->flags, 0, sizeof(uint32_t) * TFG_MAX_GPUS));
-  TFG_CUDA(j, cudaMalloc(&j->dev_err, sizeof(int)));
-  TFG_CUDA(j, cudaMemset(j->dev_err, 0, sizeof(int)));
   TFG_CUDA(j, cudaMalloc(&j->dev_epoch, sizeof(uint32_t)));
   TFG_CUDA(j, cudaMemset(j->dev_epoch, 0, sizeof(uint32_t)));
   if (const char* g = getenv("TFGRAFT_GRAPH")) j->use_graphs = atoi(g) != 0;
-  TFG_CUDA(j, cudaMallocHost(&j->h_loss, sizeof(float) * (TFG_MAX_REPLICAS + 1)));
-  TFG_CUDA(j, cudaMallocHost(&j->h_err, sizeof(int)));
+  TFG_CUDA(j, cudaMallocHost(&j->h_loss, sizeof(float) * (TFG_MAX_REPLICAS + 2)));   // same layout, pinned
+  j->h_err = reinterpret_cast<int*>(j->h_loss + TFG_MAX_REPLICAS + 1);
   *j->h_err = 0;
   j->peer_loss[j->gpu_rank] = j->loss;
   j->peer_flags[j->gpu_rank] = j->flags;
@@ -750,12 +748,11 @@ static int step_run(tfg_job* j, const float* const* images, const int32_t* const
 
 static int step_finish(tfg_job* j, float* loss_out) {
   if (loss_out) {
-    TFG_CUDA(j, cudaMemcpyAsync(j->h_loss, j->loss + TFG_MAX_REPLICAS, sizeof(float),
-                                cudaMemcpyDeviceToHost, j->stream));
-    TFG_CUDA(j, cudaMemcpyAsync(j->h_err, j->dev_err, sizeof(int), cudaMemcpyDeviceToHost, j->stream));
+    TFG_CUDA(j, cudaMemcpyAsync(j->h_loss + TFG_MAX_REPLICAS, j->loss + TFG_MAX_REPLICAS, 2 * sizeof(float),
+                                cudaMemcpyDeviceToHost, j->stream));   // mean loss + error word
     TFG_CUDA(j, cudaStreamSynchronize(j->stream));
     if (*j->h_err) return fail(j, TFG_EPEER, "cross-rank barrier timed out (a peer rank is gone?)");
-    *loss_out = j->h_loss[0];
+    *loss_out = j->h_loss[TFG_MAX_REPLICAS];
   }
   return TFG_OK;
 }
