@@ -56,8 +56,12 @@ CHECK_UNITS = ["conv1", "stage1/block1/shortcut", "stage1/block1/a", "stage1/blo
                "stage3/block6/b", "stage4/block1/b", "stage4/block3/c"]
 
 
-def test_resnet50_layerwise_parity():
-    B, HW, NC = 4, 64, 16
+@pytest.mark.parametrize("B,HW", [(4, 64), (2, 96), (3, 128)])
+def test_resnet50_layerwise_parity(B, HW):
+    """64x64: stage widths 16 / 8 / 4 / 2 (halo kernel at 16, several images per tile below);
+    96x96: 24 / 12 / 6 / 3 (halo tiles that do not divide the image height, odd widths);
+    128x128 with an odd batch: 32 / 16 / 8 / 4 (image groups that do not divide the batch)."""
+    NC = 16
     j = SyncPSJob(cfg(), 0, 1, cuda_device=0)
     j.build_resnet50(B, HW, NC)
     info = {v: j.var_info(v) for v in range(j.n_vars)}
