@@ -225,3 +225,34 @@ def test_resnet50_step_applies_its_gradients_exactly_and_is_deterministic():
     assert outs[0][0] == outs[1][0]
     np.testing.assert_array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
     assert outs[0][0][-1] < 0.6 * outs[0][0][0], outs[0][0]
+
+
+def test_resnet50_full_size_properties():
+    """The BASELINE shape (224x224 images, 1000 classes; batch 16 to keep the test short) has no CPU
+    reference run, so it is held to size-independent properties: the loss of the freshly initialised
+    net is ln(1000) within its spread; a batch-norm output without relu has per-channel mean beta = 0
+    and variance gamma^2 = 1 over the batch (the statistics come from the GEMM epilogue's column sums
+    here: 3 136 tiles of the halo / implicit / persistent kernels at their full-size tile shapes); the
+    gradient of the logits sums to zero per example; two runs from the same state give the same bits."""
+    B, HW, NC = 16, 224, 1000
+    outs = []
+    for _ in range(2):
+        j = SyncPSJob(cfg(), 0, 1, cuda_device=0)
+        j.build_resnet50(B, HW, NC)
+        j.optimizer("sgd", 0.001, 0.0)
+        x, y = synthetic_images(0, B, HW, NC)
+        loss = j.step([x], [y])
+        assert np.isfinite(loss) and abs(loss - np.log(NC)) < 0.6, loss
+        for name, c in (("stage1/block1/shortcut/y", 256), ("stage3/block1/shortcut/y", 1024)):
+            t = j.tensor(name).reshape(-1, c).astype(np.float64)
+            assert np.abs(t.mean(axis=0)).max() < 2e-2, (name, np.abs(t.mean(axis=0)).max())
+            assert np.abs(t.var(axis=0) - 1.0).max() < 3e-2, (name, np.abs(t.var(axis=0) - 1.0).max())
+        v_fcb = [v for v in range(j.n_vars) if j.var_info(v)[0] == "fc/biases"][0]
+        # d loss / d fc bias = column sums of dlogits = (softmax - onehot) / B summed over the batch: sums to 0
+        # up to the bf16 rounding of dlogits (B entries of size 1/B, each off by at most 2^-9 relative)
+        assert abs(float(j.get_grad(0, v_fcb).astype(np.float64).sum())) < 2.0 ** -9 * 1.5
+        outs.append((loss, j.get_var(0).copy(), j.get_var(v_fcb).copy()))
+        j.close()
+    assert outs[0][0] == outs[1][0]
+    np.testing.assert_array_equal(outs[0][1].view(np.uint32), outs[1][1].view(np.uint32))
+    np.testing.assert_array_equal(outs[0][2].view(np.uint32), outs[1][2].view(np.uint32))
