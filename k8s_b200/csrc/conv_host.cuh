@@ -45,7 +45,8 @@ int launch_conv_wgrad(tfg_job* j, const ConvWgrad& g, cudaStream_t s);
 // 4-D map with an explicit box {64, bw, bh, 1} (element strides 1); bw may exceed W (clipped / zero-filled)
 int make_map_4d_box(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh);
 bool halo_fits(int OH, int OW, int C, int R, int stride);   // can conv3x3_halo_kernel take this layer?
-void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip);
+int halo_mt(int Nimg, int OH, int OW, int tiles_n);           // M tiles per CTA (1 or 2) for this layer
+void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip, int tiles_n);
 int halo_grid_rows(const tc::HaloShape& hs, int tiles_n);    // CTA rows of the launch (column-sum records / parts)
 int launch_conv_halo(tfg_job* j, const HaloConv& g, cudaStream_t s);
 

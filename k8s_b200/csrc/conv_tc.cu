@@ -58,7 +58,7 @@ int make_map_4d_box(CUtensorMap* map, const void* ptr, int N, int H, int W, int 
 }
 
 // conv3x3_halo_kernel: 3x3, stride 1, 64-channel blocks, at least two image rows per 128-position tile
-// and a slab that fits its 32 KB stage
+// and a slab that fits its stage
 bool halo_fits(int OH, int OW, int C, int R, int stride) {
   static int on = -1;
   if (on < 0) {
@@ -66,12 +66,33 @@ bool halo_fits(int OH, int OW, int C, int R, int stride) {
     if (const char* e = getenv("TFGRAFT_HALO")) on = atoi(e) != 0;
   }
   const int PW = OW + 2;
-  return on == 1 && R == 3 && stride == 1 && C % 64 == 0 && OW >= 12 && PW <= 62 && OH >= 2;
+  return on == 1 && R == 3 && stride == 1 && C % 64 == 0 && OW >= 12 && PW <= tc::halo_max_pw<1>() && OH >= 2;
 }
 
-void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip) {
+// M tiles per CTA: two (256 positions, the accumulators share every weight tile) when the wider slab
+// fits its stage and the coarser tiles do not cost more in wave quantisation than the sharing returns
+// (ResNet stage 3: 512 double tiles are 4 waves of 2 units against 7 waves of 1: stay with one);
+// TFGRAFT_HALO_MT=1 keeps one everywhere
+int halo_mt(int Nimg, int OH, int OW, int tiles_n) {
+  static int want = -1;
+  if (want < 0) {
+    want = 2;
+    if (const char* e = getenv("TFGRAFT_HALO_MT")) want = atoi(e) == 1 ? 1 : 2;
+  }
+  const int PW = OW + 2;
+  if (want == 1 || PW > tc::halo_max_pw<2>()) return 1;
+  auto waves = [&](int mt) {
+    const int th = std::max(1, std::min(OH, 128 * mt / PW));
+    const long long tiles = (long long)Nimg * ((OH + th - 1) / th) * tiles_n;
+    return (tiles + kNumSMs - 1) / kNumSMs;
+  };
+  return 2.0 * (double)waves(2) <= 1.1 * (double)waves(1) ? 2 : 1;
+}
+
+void fill_halo_shape(tc::HaloShape* hs, int Nimg, int OH, int OW, int C, int flip, int tiles_n) {
   hs->Nimg = Nimg; hs->OH = OH; hs->OW = OW; hs->PW = OW + 2;
-  hs->TH = std::max(1, std::min(OH, 128 / hs->PW));
+  hs->MT = halo_mt(Nimg, OH, OW, tiles_n);
+  hs->TH = std::max(1, std::min(OH, 128 * hs->MT / hs->PW));
   hs->h_tiles = (OH + hs->TH - 1) / hs->TH;
   hs->m_tiles = Nimg * hs->h_tiles;
   hs->C = C; hs->flip = flip;
@@ -81,12 +102,12 @@ int halo_grid_rows(const tc::HaloShape& hs, int tiles_n) {
   return tc::persistent_grid((long long)hs.m_tiles * tiles_n, tiles_n, true, kNumSMs) / tiles_n;
 }
 
-template <int BN, bool B_MN>
+template <int BN, bool B_MN, int MT>
 static cudaError_t launch_halo(const HaloConv& g, cudaStream_t s) {
   static bool attr_set = false;
-  constexpr size_t smem = tc::smem_bytes_halo<BN>();
+  constexpr size_t smem = tc::smem_bytes_halo<BN, MT>();
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tc::conv3x3_halo_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(tc::conv3x3_halo_kernel<BN, B_MN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
@@ -104,15 +125,19 @@ static cudaError_t launch_halo(const HaloConv& g, cudaStream_t s) {
   tc::Epilogue epi = g.epi;
   epi.tma_out = g.tma_out;
   const int grid = tc::persistent_grid(total, tiles_n, epi.col_stats != nullptr, kNumSMs);
-  tc::conv3x3_halo_kernel<BN, B_MN><<<grid, tc::kThreadsPersistent, smem, s>>>(g.a, g.b, g.c, g.hs, g.N, tiles_n,
-                                                                              g.b_rows_per_tap, base_mode, epi);
+  tc::conv3x3_halo_kernel<BN, B_MN, MT><<<grid, tc::kThreadsPersistent, smem, s>>>(g.a, g.b, g.c, g.hs, g.N, tiles_n,
+                                                                                  g.b_rows_per_tap, base_mode, epi);
   return cudaGetLastError();
 }
 
+template <int MT>
+static cudaError_t launch_halo_mt(const HaloConv& g, cudaStream_t s) {
+  if (g.b_mn) return g.block_n == 64 ? launch_halo<64, true, MT>(g, s) : launch_halo<128, true, MT>(g, s);
+  return g.block_n == 64 ? launch_halo<64, false, MT>(g, s) : launch_halo<128, false, MT>(g, s);
+}
+
 int launch_conv_halo(tfg_job* j, const HaloConv& g, cudaStream_t s) {
-  cudaError_t e;
-  if (g.b_mn) e = g.block_n == 64 ? launch_halo<64, true>(g, s) : launch_halo<128, true>(g, s);
-  else e = g.block_n == 64 ? launch_halo<64, false>(g, s) : launch_halo<128, false>(g, s);
+  const cudaError_t e = g.hs.MT == 2 ? launch_halo_mt<2>(g, s) : launch_halo_mt<1>(g, s);
   if (j) prof_mark(j, g.name);
   if (e != cudaSuccess) return fail_cuda(j, e, g.name);
   return TFG_OK;

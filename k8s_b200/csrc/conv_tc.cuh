@@ -253,38 +253,52 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 // {64, PW, TH} clips them at the tensor edge.  dgrad (flip): the taps are mirrored.
 struct HaloShape {
   int Nimg, OH, OW, PW, TH, h_tiles, m_tiles, C, flip;
+  int MT;                    // M tiles of 128 positions per CTA (host-side choice, selects the kernel instance)
 };
 
-constexpr int kSlabBytes = 32 * 1024;       // >= (128 + 2 * PW + 2) * 128 for PW <= 62
+// MT = M tiles (of 128 positions) per CTA.  MT = 2: a tile is 256 consecutive positions, the two
+// accumulators share every weight tile (the weight tiles dominate L2 -> SM traffic once the input is
+// resident: 72 -> 42 B/clk/SM at full MMA rate, against an L2 limit of ~42), one 256-row output image.
 constexpr int kSlabStages = 2;
-template <int BLOCK_N> constexpr int halo_b_stages() { return BLOCK_N == 64 ? 8 : 6; }
-
-template <int BLOCK_N>
-constexpr size_t smem_bytes_halo() {
-  return 1024 + kSlabStages * kSlabBytes + static_cast<size_t>(halo_b_stages<BLOCK_N>()) * BLOCK_N * kBlockKBytes +
-         2 * (BLOCK_N / 64) * kOutHalfBytes + (2 * kSlabStages + 2 * halo_b_stages<BLOCK_N>() + 8) * sizeof(uint64_t) + 16;
+template <int MT> constexpr int halo_slab_bytes() {          // >= (128 MT + 2 PW + 2) * 128
+  return MT == 1 ? 32 * 1024 : 47 * 1024;                    // PW <= 62 / PW <= 58
 }
-static_assert(smem_bytes_halo<128>() <= 232448 && smem_bytes_halo<64>() <= 232448, "shared memory budget");
+template <int MT> constexpr int halo_max_pw() { return MT == 1 ? 62 : 58; }
+template <int BLOCK_N, int MT> constexpr int halo_b_stages() { return MT == 1 ? (BLOCK_N == 64 ? 8 : 6) : (BLOCK_N == 64 ? 8 : 4); }
+
+template <int BLOCK_N, int MT>
+constexpr size_t smem_bytes_halo() {
+  return 1024 + kSlabStages * halo_slab_bytes<MT>() +
+         static_cast<size_t>(halo_b_stages<BLOCK_N, MT>()) * BLOCK_N * kBlockKBytes + 2 * (BLOCK_N / 64) * kOutHalfBytes +
+         (2 * kSlabStages + 2 * halo_b_stages<BLOCK_N, MT>() + 8) * sizeof(uint64_t) + 16;
+}
+static_assert(smem_bytes_halo<128, 1>() <= 232448 && smem_bytes_halo<64, 1>() <= 232448 &&
+              smem_bytes_halo<128, 2>() <= 232448 && smem_bytes_halo<64, 2>() <= 232448, "shared memory budget");
 
 // map_a: 4-D map over the gathered activation [Nimg, OH, OW, C], box {64, PW, TH + 2, 1}.
 // map_b: as conv_gemm_kernel.  map_c: 4-D map over the output [Nimg, OH, OW, N], box {64, PW, TH, 1}.
-template <int BLOCK_N, bool B_MN>
+template <int BLOCK_N, bool B_MN, int MT>
 __global__ void __launch_bounds__(kThreadsPersistent, 1)
 conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const __grid_constant__ CUtensorMap map_c, const __grid_constant__ HaloShape hs, int N, int tiles_n,
                     int b_rows_per_tap, int base_offset_mode, Epilogue epi) {
-  constexpr int kBStages = halo_b_stages<BLOCK_N>();
+  constexpr int kBStages = halo_b_stages<BLOCK_N, MT>();
+  constexpr int kSlabBytes = halo_slab_bytes<MT>();
+  constexpr int kRows = kBlockM * MT;                     // positions per tile
+  constexpr int kHalfBytes = kRows * 128;                 // one 64-column half of the output image
+  constexpr int kImages = MT == 1 ? 2 : 1;                // output images in the staging area
+  constexpr int kAccCols = MT * BLOCK_N;                  // TMEM columns of one accumulator set
   constexpr int kBBytes = BLOCK_N * kBlockKBytes;
   constexpr int kChunkBytes = 64 * 128;
   constexpr uint32_t kStepB = B_MN ? (16 * 128) >> 4 : 32 >> 4;
-  constexpr int kOutTileBytes = (BLOCK_N / 64) * kOutHalfBytes;
+  constexpr int kOutTileBytes = (BLOCK_N / 64) * kHalfBytes;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* slab = smem;
   uint8_t* smem_b = slab + kSlabStages * kSlabBytes;
   uint8_t* out_stage = smem_b + kBStages * kBBytes;
-  uint64_t* slab_full = reinterpret_cast<uint64_t*>(out_stage + 2 * kOutTileBytes);
+  uint64_t* slab_full = reinterpret_cast<uint64_t*>(out_stage + kImages * kOutTileBytes);
   uint64_t* slab_empty = slab_full + kSlabStages;
   uint64_t* b_full = slab_empty + kSlabStages;
   uint64_t* b_empty = b_full + kBStages;
@@ -316,7 +330,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     }
     __syncwarp();
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                 :: "r"(smem_u32(tmem_slot)), "n"(2 * BLOCK_N) : "memory");
+                 :: "r"(smem_u32(tmem_slot)), "n"(2 * kAccCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -370,7 +384,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       mbar_wait_addr(tmem_empty0 + acc * 8, acc_ph ^ 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      const uint32_t d_tmem = tmem_base + acc * kAccCols;
       for (int cb = 0; cb < cblocks; ++cb) {
         mbar_wait_addr(slab_full0 + ss * 8, sph);
         const uint32_t a_base = desc_lo(slab0 + ss * kSlabBytes, 16);
@@ -382,8 +396,11 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           const uint32_t b_lo = desc_lo(b0 + bs * kBBytes, B_MN ? kChunkBytes : 16);
           if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma2<0>(d_tmem, a_lo + 2 * k, hi, b_lo + kStepB * k, hi, idesc, cb > 0 || tap > 0 || k > 0);
+            for (int h = 0; h < MT; ++h)                  // M tile h: 128 positions (16 KB) further on in the slab
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma2<0>(d_tmem + h * BLOCK_N, a_lo + h * 1024 + 2 * k, hi, b_lo + kStepB * k, hi, idesc,
+                         cb > 0 || tap > 0 || k > 0);
             umma_commit_addr(b_empty0 + bs * 8);
           }
           __syncwarp();
@@ -401,20 +418,30 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   } else if (warp < 6) {
     // ===== epilogue warps =====
     uint32_t tcnt = 0;
-    const int m = (warp & 3) * 32 + lane;                 // this thread's row of every tile
-    const int oh = m / hs.PW, owp = m - oh * hs.PW;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
       const int n0 = (t % tiles_n) * BLOCK_N, mt = t / tiles_n;
       const int img0 = mt / hs.h_tiles, h0 = (mt % hs.h_tiles) * hs.TH;
-      const bool keep = owp < hs.OW && oh < hs.TH && h0 + oh < hs.OH;
       const uint32_t acc = tcnt & 1, acc_phase = (tcnt >> 1) & 1;
-      uint8_t* img = out_stage + acc * kOutTileBytes;
-      if (warp == 2 && lane == 0) bulk_wait_read<1>();
-      if (epi.col_stats && tcnt >= 2) mbar_wait(&img_free[acc], ((tcnt >> 1) - 1) & 1);
+      const uint32_t ib = MT == 1 ? acc : 0;              // output image buffer
+      uint8_t* img = out_stage + ib * kOutTileBytes;
+      if (warp == 2 && lane == 0) {                       // the previous user of this image has been read by its store
+        if (MT == 1) bulk_wait_read<1>(); else bulk_wait_read<0>();
+      }
+      if (epi.col_stats) {                                // ... and by the column-sum warps
+        if (MT == 1) { if (tcnt >= 2) mbar_wait(&img_free[ib], ((tcnt >> 1) - 1) & 1); }
+        else if (tcnt >= 1) mbar_wait(&img_free[ib], (tcnt - 1) & 1);
+      }
       epi_barrier();
       mbar_wait(&tmem_full[acc], acc_phase);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      drain_tile_staged<BLOCK_N>(tmem_base + acc * BLOCK_N, img, warp, lane, n0, epi, keep);
+#pragma unroll
+      for (int h = 0; h < MT; ++h) {
+        const int m = h * kBlockM + (warp & 3) * 32 + lane;   // this thread's position in the tile
+        const int oh = m / hs.PW, owp = m - oh * hs.PW;
+        const bool keep = owp < hs.OW && oh < hs.TH && h0 + oh < hs.OH;
+        drain_tile_staged<BLOCK_N>(tmem_base + acc * kAccCols + h * BLOCK_N, img, warp, lane, n0, epi, keep, h * kBlockM,
+                                   kHalfBytes);
+      }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -423,9 +450,9 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       if (warp == 2 && lane == 0) {
 #pragma unroll
         for (int h = 0; h < BLOCK_N / 64; ++h)
-          if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kOutHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
+          if (n0 + h * 64 < N) tma_store_4d(&map_c, img + h * kHalfBytes, n0 + h * 64, 0, h0, img0, epi.tma_out == 2);
         bulk_commit();
-        if (epi.col_stats) mbar_arrive(&img_full[acc]);
+        if (epi.col_stats) mbar_arrive(&img_full[ib]);
       }
     }
     if (warp == 2 && lane == 0) bulk_wait_all();
@@ -435,11 +462,11 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     ColStats sums;
     const int et = threadIdx.x - kThreads;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tcnt) {
-      const uint32_t acc = tcnt & 1;
-      mbar_wait(&img_full[acc], (tcnt >> 1) & 1);
-      tile_col_stats<BLOCK_N>(out_stage + acc * kOutTileBytes, et, kBlockM, sums);
+      const uint32_t ib = MT == 1 ? (tcnt & 1) : 0;
+      mbar_wait(&img_full[ib], MT == 1 ? (tcnt >> 1) & 1 : tcnt & 1);
+      tile_col_stats<BLOCK_N, kRows>(out_stage + ib * kOutTileBytes, et, kRows, sums);
       __syncwarp();
-      if (lane == 0) mbar_arrive(&img_free[acc]);
+      if (lane == 0) mbar_arrive(&img_free[ib]);
     }
     store_col_stats<BLOCK_N>(sums, et, (blockIdx.x % tiles_n) * BLOCK_N, N, blockIdx.x / tiles_n, epi.col_stats);
   }
@@ -447,7 +474,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * BLOCK_N) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(2 * kAccCols) : "memory");
   }
 }
 

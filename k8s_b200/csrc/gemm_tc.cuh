@@ -488,11 +488,14 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void*
 // TMEM accumulator -> bf16 tile image in `out_stage` (BLOCK_N / 64 halves of kOutHalfBytes);
 // bias and relu applied on the way.  Called by the four epilogue warps.
 // keep = false: this thread's row is not part of the output (halo convolution) and is staged as zeros.
+// row_base / half_bytes: the tile image may be taller than 128 rows (two M tiles of one CTA): this
+// accumulator's rows start at row_base and the 64-column halves are half_bytes apart.
 template <int BLOCK_N>
 __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* out_stage, int warp, int lane, int n0,
-                                                  const Epilogue& epi, bool keep = true) {
+                                                  const Epilogue& epi, bool keep = true, int row_base = 0,
+                                                  int half_bytes = kOutHalfBytes) {
   const int q = warp & 3;
-  const int row = q * 32 + lane;
+  const int row = row_base + q * 32 + lane;
 #pragma unroll 1
   for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
     uint32_t r[32];
@@ -507,7 +510,7 @@ __device__ __forceinline__ void drain_tile_staged(uint32_t tmem_acc, uint8_t* ou
           "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-    uint8_t* half = out_stage + (c0 >> 6) * kOutHalfBytes + row * 128;
+    uint8_t* half = out_stage + (c0 >> 6) * half_bytes + row * 128;
     const int j0 = (c0 & 63) >> 3;
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -544,12 +547,12 @@ struct ColStats {
   float s0[2] = {0.f, 0.f}, s1[2] = {0.f, 0.f}, q0[2] = {0.f, 0.f}, q1[2] = {0.f, 0.f};
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, int ROWS = kBlockM>
 __device__ __forceinline__ void tile_col_stats(const uint8_t* img, int et, int valid, ColStats& a) {
   constexpr int kPairs = BLOCK_N / 2;
-  constexpr int kRows = kBlockM / col_stats_parts<BLOCK_N>();
+  constexpr int kRows = ROWS / col_stats_parts<BLOCK_N>();
   const int c = (et % kPairs) * 2, part = et / kPairs;
-  const uint8_t* col = img + (c >> 6) * kOutHalfBytes + (c & 7) * 2;
+  const uint8_t* col = img + (c >> 6) * (ROWS * 128) + (c & 7) * 2;
   const int j = (c & 63) >> 3;
   const int r_end = min(valid, (part + 1) * kRows);
 #pragma unroll 1

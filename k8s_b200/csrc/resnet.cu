@@ -152,7 +152,7 @@ static int stat_tiles(const RnUnit& u) {
   long long m_tiles;
   if (u.halo) {
     tc::HaloShape hs;
-    fill_halo_shape(&hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0);
+    fill_halo_shape(&hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0, tiles_n);
     return parts * halo_grid_rows(hs, tiles_n);
   }
   if (u.implicit) {
@@ -358,14 +358,14 @@ static int prepare_maps(tfg_job* j, int slot) {
     if (u.halo) {
       const int bn = u.kout >= 128 ? 128 : 64, bnd = u.g.C >= 128 ? 128 : 64;
       HaloConv& f = s.hfwd[i];
-      fill_halo_shape(&f.hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0);
+      fill_halo_shape(&f.hs, u.g.N, u.g.OH, u.g.OW, u.g.C, 0, (u.kout + bn - 1) / bn);
       f.name = "rn conv fwd (halo)"; f.N = u.kout; f.block_n = bn; f.b_mn = true; f.b_rows_per_tap = u.g.C; f.tma_out = 1;
       f.epi.out_bf16 = s.data[u.z];
       if ((rc = make_map_4d_box(&f.a, s.data[u.in], u.g.N, u.g.H, u.g.W, u.g.C, f.hs.PW, f.hs.TH + 2))) return rc;
       if ((rc = make_map(&f.b, kind, wlp(u.v_w), u.kout, rsc, u.kout, bn, true))) return rc;
       if ((rc = make_map_4d_box(&f.c, s.data[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, f.hs.PW, f.hs.TH))) return rc;
       HaloConv& d = s.hdgrad[i];
-      fill_halo_shape(&d.hs, u.g.N, u.g.H, u.g.W, u.kout, 1);
+      fill_halo_shape(&d.hs, u.g.N, u.g.H, u.g.W, u.kout, 1, (u.g.C + bnd - 1) / bnd);
       d.name = "rn conv dgrad (halo)"; d.N = u.g.C; d.block_n = bnd; d.b_mn = false; d.b_rows_per_tap = u.g.C;
       d.epi.out_bf16 = s.grad[u.in];
       if ((rc = make_map_4d_box(&d.a, s.grad[u.z], u.g.N, u.g.OH, u.g.OW, u.kout, d.hs.PW, d.hs.TH + 2))) return rc;
