@@ -83,6 +83,12 @@ struct tfg_job {
   tfg::MnistModel* model = nullptr;
   tfg::ResnetModel* resnet = nullptr;
   int64_t launches = 0;
+  // Side branch of the step: kernels that are leaves of the dependency graph (the ResNet weight
+  // gradients) run on side_stream between side_fork() and side_join(); inside the captured step they
+  // become a parallel branch of the graph.  With per-kernel timing on, the side stream IS the main one.
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_side[2] = {nullptr, nullptr};
+  bool side_open = false;
   // optional per-kernel timing: one event after every launch (see prof_mark)
   bool prof_on = false;
   std::vector<std::pair<const char*, cudaEvent_t>> prof_ev;
@@ -114,6 +120,11 @@ int fail_cuda(tfg_job* j, cudaError_t e, const char* what);
 // serial, so the span between consecutive events is the kernel's duration plus any gap in
 // front of it.
 void prof_mark(tfg_job* j, const char* what);
+// side branch (see tfg_job::side_stream): side_fork makes the side stream wait for everything
+// enqueued on j->stream so far and returns the stream to launch on; side_join makes j->stream wait
+// for the side branch (no-op when none is open)
+cudaStream_t side_fork(tfg_job* j);
+void side_join(tfg_job* j);
 
 // apply.cu
 int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole = false);

@@ -39,6 +39,29 @@ void prof_mark(tfg_job* j, const char* what) {
   j->prof_used++;
 }
 
+cudaStream_t side_fork(tfg_job* j) {
+  static int on = -1;
+  if (on < 0) {
+    on = 1;
+    if (const char* e = getenv("TFGRAFT_SIDE")) on = atoi(e) != 0;
+  }
+  if (!on || j->prof_on || !j->side_stream) return j->stream;   // per-kernel timing attributes time on one stream
+  if (cudaEventRecord(j->ev_side[0], j->stream) != cudaSuccess ||
+      cudaStreamWaitEvent(j->side_stream, j->ev_side[0], 0) != cudaSuccess) {
+    cudaGetLastError();
+    return j->stream;
+  }
+  j->side_open = true;
+  return j->side_stream;
+}
+
+void side_join(tfg_job* j) {
+  if (!j->side_open) return;
+  j->side_open = false;
+  cudaEventRecord(j->ev_side[1], j->side_stream);
+  cudaStreamWaitEvent(j->stream, j->ev_side[1], 0);
+}
+
 // [TF1.3] replica_device_setter default ps_ops (python/training/device_setter.py).
 static bool is_ps_op(const std::string& t) {
   return t == "Variable" || t == "VariableV2" || t == "VarHandleOp";
@@ -182,6 +205,9 @@ int tfg_job_destroy(tfg_job* j) {
       if (g.exec) cudaGraphExecDestroy(g.exec);
     cudaFree(j->d_segs);
     if (j->h_loss) cudaFreeHost(j->h_loss);
+    if (j->side_stream) cudaStreamDestroy(j->side_stream);
+    for (cudaEvent_t e : j->ev_side)
+      if (e) cudaEventDestroy(e);
     if (j->own_stream && j->stream) cudaStreamDestroy(j->stream);
     cudaGetLastError();
   }
@@ -200,6 +226,8 @@ int tfg_job_bind(tfg_job* j, int cuda_device, void* stream) {
     TFG_CUDA(j, cudaStreamCreateWithFlags(&j->stream, cudaStreamNonBlocking));
     j->own_stream = true;
   }
+  TFG_CUDA(j, cudaStreamCreateWithFlags(&j->side_stream, cudaStreamNonBlocking));
+  for (cudaEvent_t& e : j->ev_side) TFG_CUDA(j, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   // [replica losses | mean loss | error word]: the last two words are read back by ONE 8-byte copy per step
   TFG_CUDA(j, cudaMalloc(&j->loss, sizeof(float) * (TFG_MAX_REPLICAS + 2)));
   TFG_CUDA(j, cudaMemset(j->loss, 0, sizeof(float) * (TFG_MAX_REPLICAS + 2)));

@@ -666,11 +666,17 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
                                                             par(u.v_gamma), grd(u.v_beta), grd(u.v_gamma), s.grad[u.z], g_out,
                                                             g_acc, M * u.kout, u.kout, M);
     RN_OK(j, "rn bn bwd apply");
-    // weight gradient: the im2col operand is the one the forward pass built
-    if (u.implicit) {
-      if ((rc = launch_conv_wgrad(j, s.iwgrad[i], st))) return rc;
-    } else if ((rc = launch_tc(j, s.wgrad[i], TFG_MATH_BF16, st))) {
-      return rc;
+    // weight gradient: a leaf of the dependency graph (nothing downstream in this step reads it before
+    // the apply), so it goes to the side stream and overlaps the data-gradient / batch-norm chain; the
+    // side stream runs the weight gradients one after another, which keeps their shared split-K
+    // partial buffer safe.  (the im2col operand of the stem is the one the forward pass built)
+    {
+      cudaStream_t ws = side_fork(j);
+      if (u.implicit) {
+        if ((rc = launch_conv_wgrad(j, s.iwgrad[i], ws))) return rc;
+      } else if ((rc = launch_tc(j, s.wgrad[i], TFG_MATH_BF16, ws))) {
+        return rc;
+      }
     }
     if (u.in == m->t_image) continue;
     // data gradient
@@ -733,6 +739,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
     }
     written[u.in] = 1;
   }
+  side_join(j);
   return TFG_OK;
 }
 
