@@ -53,6 +53,9 @@ extern "C" {
 #define TFG_MATH_FP32      0   /* CUDA-core FFMA, fp32 everywhere                      */
 #define TFG_MATH_BF16      1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate    */
 #define TFG_MATH_TF32      2   /* tcgen05 kind::tf32, fp32 storage                     */
+#define TFG_MATH_TF32X3    3   /* tcgen05 kind::tf32, three MMAs per product (hi*hi +  */
+                               /* hi*lo + lo*hi, fp32 accumulate): fp32-equivalent,    */
+                               /* held to the fp32 parity bounds                       */
 /* [TF1.3] embedding_lookup partition_strategy                                         */
 #define TFG_PART_MOD       0
 #define TFG_PART_DIV       1
@@ -298,6 +301,20 @@ int64_t tfg_launch_count(const tfg_job* job);
 int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const void* b_dev, int b_mn_major,
                 float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb, int block_n, int splits,
                 float* partial_dev, const float* bias_dev, int relu, void* stream);
+
+/* The same GEMM as a 3xTF32 split product (math mode TFG_MATH_TF32X3): fp32 operands plus their
+ * low-order planes (same shape and pitch; lo = rn_tf32(x - trunc_tf32(x)), produced by
+ * tfg_tf32_split_lo or by the kernel that wrote x), three kind::tf32 MMAs per K step
+ * (a_lo*b + a*b_lo + a*b).  The tensor core adds into its accumulator with truncation, so K is cut
+ * into chunks of chunk_kb K blocks (32 fp32 each; 0 = the default 2) that accumulate in TMEM from
+ * zero and are summed in registers with round-to-nearest: the result carries fp32 summation-level
+ * error at tensor-core speed.  This is how the fp32 sample model of BASELINE configs 1-3
+ * (SURVEY.md par. 8d "which roofline") runs its contractions. */
+int tfg_gemm_tc_x3(const float* a_dev, const float* a_lo_dev, int a_mn_major, const float* b_dev,
+                   const float* b_lo_dev, int b_mn_major, float* c_dev, int M, int N, int K, int64_t lda,
+                   int64_t ldb, int block_n, int splits, int chunk_kb, float* partial_dev,
+                   const float* bias_dev, int relu, void* stream);
+int tfg_tf32_split_lo(const float* src_dev, float* lo_dev, int64_t n, void* stream);
 
 /* per-kernel device time of this job's launches, measured with CUDA events on the job's
  * stream (bench.py's roofline leg).  enable(1) starts a fresh record; report() writes

@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 
 #include "common.cuh"
+#include "gemm_tc.cuh"
 
 namespace tfg {
 
@@ -18,7 +19,8 @@ constexpr int kChunk = 4096;            // elements per work chunk = 4 float4 pe
 struct ApplyArgs {
   const float* grads[TFG_MAX_REPLICAS];
   float* pull[TFG_MAX_GPUS];
-  __nv_bfloat16* lp[TFG_MAX_GPUS];   // bf16 shadows of the parameter buffers (own + peers), n_lp of them
+  void* lp[TFG_MAX_GPUS];            // operand-precision shadows of the parameter buffers (own + peers), n_lp of them
+  int lp_mode;                       // 1: bf16 copy, 2: fp32 low-order plane of the 3xTF32 split (gemm_tc.cuh:tf32_lo)
   const float* loss_src[TFG_MAX_REPLICAS];
   float* var;
   float* accum;
@@ -26,6 +28,7 @@ struct ApplyArgs {
   const Segment* segs;   // NULL: the single inline segment `seg0`
   Segment seg0;
   int n_segs;
+  const int* err;        // the job's error word: set by a barrier that timed out; the update is then skipped
   int n_grads, n_pull, n_lp, n_loss, kind;
   long long n_chunks;
   float divisor, lr, mu;
@@ -56,6 +59,9 @@ __device__ __forceinline__ void update1(float g, float& v, float& a, float lr, f
 template <int KIND>
 __global__ void __launch_bounds__(kApplyThreads)
 push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
+  // a peer rank is gone (the barrier in front of this launch gave up): its gradients are stale, so
+  // no parameter may change; the host reports TFG_EPEER when it reads the error word
+  if (a.err && *reinterpret_cast<const volatile int*>(a.err) != 0) return;
   // mean loss over replicas, replica order (the step's scalar result)
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.n_loss > 0) {
     float s = a.loss_src[0][0];
@@ -115,12 +121,15 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
         if (KIND != TFG_OPT_SGD) *reinterpret_cast<float4*>(a.accum + idx[u]) = m[u];
         if (a.var) *reinterpret_cast<float4*>(a.var + idx[u]) = v[u];
         for (int p = 0; p < a.n_pull; ++p) *reinterpret_cast<float4*>(a.pull[p] + idx[u]) = v[u];
-        if (a.n_lp > 0) {   // the tensor path reads its weights from this bf16 copy: no cast kernels per step
+        if (a.n_lp > 0 && a.lp_mode == 1) {   // the tensor path reads its weights from this bf16 copy: no cast kernels per step
           const __nv_bfloat162 lo = __floats2bfloat162_rn(v[u].x, v[u].y), hi = __floats2bfloat162_rn(v[u].z, v[u].w);
           uint2 pk;
           pk.x = *reinterpret_cast<const uint32_t*>(&lo);
           pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<uint2*>(a.lp[p] + idx[u]) = pk;
+          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(a.lp[p]) + idx[u]) = pk;
+        } else if (a.n_lp > 0) {              // 3xTF32: the low-order plane of the new value
+          const float4 lo = make_float4(tc::tf32_lo(v[u].x), tc::tf32_lo(v[u].y), tc::tf32_lo(v[u].z), tc::tf32_lo(v[u].w));
+          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<float4*>(static_cast<float*>(a.lp[p]) + idx[u]) = lo;
         }
       }
   }
@@ -167,7 +176,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole) {
     a.var = j->params;
     a.n_pull = 0;
     a.n_loss = 0;
-    if (j->params_lp) a.lp[a.n_lp++] = static_cast<__nv_bfloat16*>(j->params_lp);   // owned ranges only
+    if (j->params_lp) a.lp[a.n_lp++] = j->params_lp;   // owned ranges only
   } else {
     for (int r = 0; r < j->n_replicas; ++r) a.grads[r] = j->peer_grads[r];
     a.n_grads = j->n_replicas;
@@ -177,10 +186,12 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole) {
     for (int g = 0; g < j->n_gpus; ++g)
       if (g != j->gpu_rank) a.pull[a.n_pull++] = j->peer_params[g];
     if (j->params_lp)
-      for (int g = 0; g < j->n_gpus; ++g) a.lp[a.n_lp++] = static_cast<__nv_bfloat16*>(j->peer_params_lp[g]);
+      for (int g = 0; g < j->n_gpus; ++g) a.lp[a.n_lp++] = j->peer_params_lp[g];
     a.n_loss = (j->model || j->resnet) ? j->n_replicas : 0;
     for (int r = 0; r < a.n_loss; ++r) a.loss_src[r] = j->peer_loss[r % j->n_gpus] + r;
   }
+  a.lp_mode = j->lp_mode;
+  a.err = j->n_gpus > 1 ? j->dev_err : nullptr;
   a.loss_dst = j->loss + TFG_MAX_REPLICAS;
   a.accum = j->accum;
   a.segs = j->d_segs;
@@ -261,16 +272,18 @@ int launch_dense_apply(int kind, float* var, float* accum, const float* const* g
 }
 
 __global__ void __launch_bounds__(256)
-cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    dst[i] = __float2bfloat16_rn(src[i]);
+cast_lp_kernel(const float* __restrict__ src, void* __restrict__ dst, long long n, int lp_mode) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    if (lp_mode == 1) static_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16_rn(src[i]);
+    else static_cast<float*>(dst)[i] = tc::tf32_lo(src[i]);
+  }
 }
 
-int launch_cast_bf16(const float* src, void* dst, long long n, cudaStream_t s) {
+int launch_cast_lp(const float* src, void* dst, long long n, int lp_mode, cudaStream_t s) {
   if (n <= 0) return TFG_OK;
   long long blocks = (n + 255) / 256;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  cast_bf16_kernel<<<(int)blocks, 256, 0, s>>>(src, static_cast<__nv_bfloat16*>(dst), n);
+  cast_lp_kernel<<<(int)blocks, 256, 0, s>>>(src, dst, n, lp_mode);
   return cudaGetLastError() == cudaSuccess ? TFG_OK : TFG_ECUDA;
 }
 

@@ -59,7 +59,8 @@ struct tfg_job {
   cudaStream_t stream = nullptr;
   float* params = nullptr;
   float* accum = nullptr;
-  void* params_lp = nullptr;           // bf16 shadow of `params`, kept current by the apply kernel (bf16 math only)
+  void* params_lp = nullptr;           // operand-precision shadow of `params`, kept current by the apply kernel
+  int lp_mode = 0;                     // 0 none, 1 = bf16 copy [flat], 2 = fp32 low-order plane of the 3xTF32 split [flat]
   std::vector<float*> grads;           // one flat buffer per local replica slot
   float* loss = nullptr;               // [TFG_MAX_REPLICAS + 2]; [r] = replica r, then the mean, then the error word (dev_err)
   uint32_t* flags = nullptr;           // [TFG_MAX_GPUS] barrier epochs written by peers
@@ -151,7 +152,7 @@ int32_t* resnet_stage_labels(tfg_job* j, int slot);
 int resnet_tensor_get(tfg_job* j, int slot, const char* name, float* host, size_t cap_floats, size_t* n_out);
 int mnist_batch(const tfg_job* j);
 int mnist_math(const tfg_job* j);
-int launch_cast_bf16(const float* src, void* dst, long long n, cudaStream_t s);   // apply.cu
+int launch_cast_lp(const float* src, void* dst, long long n, int lp_mode, cudaStream_t s);   // apply.cu
 float* mnist_stage_images(tfg_job* j, int slot);
 int32_t* mnist_stage_labels(tfg_job* j, int slot);
 

@@ -8,6 +8,7 @@
 
 #include "common.cuh"
 #include "gemm_tc.cuh"
+#include "gemm_x3.cuh"
 #include "model_mnist.cuh"
 #include "tc_host.cuh"
 
@@ -83,6 +84,43 @@ static cudaError_t launch_stage(const TcGemm& g, float* dst, int ldc, int k_bloc
   return cudaGetLastError();
 }
 
+// 3xTF32 split product (gemm_x3.cuh): stages of 48 KB (BLOCK_N = 64) / 64 KB (128), one tile per CTA
+template <int BN, bool A_MN, bool B_MN, int STAGES>
+static cudaError_t launch_x3_stage(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                                   tc::Epilogue epi, cudaStream_t s) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_x3<BN, STAGES>();
+  static_assert(smem <= 232448, "shared memory budget");
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::gemm_x3_kernel<BN, A_MN, B_MN, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  dim3 grid((g.N + BN - 1) / BN, (g.M + tc::kBlockM - 1) / tc::kBlockM, splits);
+  tc::gemm_x3_kernel<BN, A_MN, B_MN, STAGES><<<grid, tc::kThreads, smem, s>>>(
+      g.a, g.b, g.a_lo, g.b_lo, dst, g.M, g.N, ldc, k_blocks, kps, g.chunk_kb > 0 ? g.chunk_kb : 2, epi);
+  return cudaGetLastError();
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static cudaError_t launch_x3(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                             tc::Epilogue epi, cudaStream_t s) {
+  const long long ctas = (long long)((g.N + BN - 1) / BN) * ((g.M + tc::kBlockM - 1) / tc::kBlockM) * splits;
+  if (kps <= 1) return launch_x3_stage<BN, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (kps <= 3 || ctas >= 2ll * kNumSMs) return launch_x3_stage<BN, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  return launch_x3_stage<BN, A_MN, B_MN, 3>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+}
+
+template <int BN>
+static cudaError_t launch_x3_major(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
+                                   tc::Epilogue epi, cudaStream_t s) {
+  if (!g.a_mn && !g.b_mn) return launch_x3<BN, false, false>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (!g.a_mn && g.b_mn) return launch_x3<BN, false, true>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  if (g.a_mn && g.b_mn) return launch_x3<BN, true, true>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  return launch_x3<BN, true, false>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+}
+
 template <int BN, int KIND, bool A_MN, bool B_MN>
 static cudaError_t launch_persistent(const TcGemm& g, float* dst, int ldc, int k_blocks, int kps, int splits,
                                      tc::Epilogue epi, cudaStream_t s) {
@@ -151,6 +189,7 @@ static cudaError_t launch_major(const TcGemm& g, float* dst, int ldc, int k_bloc
 
 // j may be NULL (stateless test entry point)
 int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
+  if (g.x3 && (kind != TFG_MATH_TF32 || g.tma_out)) return fail(j, TFG_EINVAL, "the split product takes fp32 operands and a plain store");
   const int block_k = tc::kBlockKBytes / (kind == TFG_MATH_BF16 ? 2 : 4);
   const int k_blocks = (g.K + block_k - 1) / block_k;
   int splits = std::max(1, std::min(g.splits, k_blocks));
@@ -175,7 +214,10 @@ int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
   if (splits > 1 && (!g.partial || g.ldc != g.N))
     return fail(j, TFG_EINVAL, "split-K needs a partial buffer and a dense output");
   cudaError_t e;
-  if (kind == TFG_MATH_BF16)
+  if (g.x3)
+    e = g.block_n == 64 ? launch_x3_major<64>(g, dst, ldc, k_blocks, kps, splits, epi, s)
+                        : launch_x3_major<128>(g, dst, ldc, k_blocks, kps, splits, epi, s);
+  else if (kind == TFG_MATH_BF16)
     e = g.block_n == 64 ? launch_major<64, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s)
                         : launch_major<128, 0>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   else
@@ -203,7 +245,7 @@ template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16
 // 16 bytes of col (4 fp32 / 8 bf16 channels)
 template <typename T>
 __global__ void __launch_bounds__(256)
-im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
+im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, float* __restrict__ col_lo, int B) {
   constexpr int kPer = 16 / sizeof(T);          // channels per thread
   constexpr int kGroups = 32 / kPer;            // threads per tap
   const long long total = (long long)B * 196 * 25 * kGroups;
@@ -222,6 +264,9 @@ im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
     for (int q = 0; q < kPer / 4; ++q) {
       const float4 v = ok ? *reinterpret_cast<const float4*>(src + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
       store4(dst + 4 * q, v);
+      if (col_lo)   // T = float: the low-order plane of the 3xTF32 split
+        store4(col_lo + m * 800 + kk * 32 + cg * kPer + 4 * q,
+               make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w)));
     }
   }
 }
@@ -230,7 +275,7 @@ im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
 template <typename T>
 __global__ void __launch_bounds__(256)
 unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, const uint8_t* __restrict__ idx,
-                 T* __restrict__ gy, int B, int HO, int C) {
+                 T* __restrict__ gy, float* __restrict__ gy_lo, int B, int HO, int C) {
   const long long total = (long long)B * HO * HO * C;
   const int HI = HO * 2;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -246,6 +291,7 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
       for (int dx = 0; dx < 2; ++dx) {
         const long long m = (b * HI + 2 * ph + dy) * HI + 2 * pw + dx;
         gy[m * C + c] = cvt<T>((dy * 2 + dx == arg) ? g : 0.f);
+        if (gy_lo) gy_lo[m * C + c] = (dy * 2 + dx == arg) ? tc::tf32_lo(g) : 0.f;
       }
   }
 }
@@ -267,6 +313,7 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
 
 struct TcSlot {            // per replica slot: operand copies of activations + GEMM descriptors
   void *col_lp = nullptr, *a2_lp = nullptr, *dh1_lp = nullptr, *dy2_lp = nullptr;   // a2/dh1: bf16 math only
+  float *col_lo = nullptr, *a2_lo = nullptr, *dh1_lo = nullptr, *dy2_lo = nullptr;   // 3xTF32: low-order planes
   float* partial = nullptr;
   TcGemm conv2_fwd, fc1_fwd, fc1_wgrad, fc1_dgrad, conv2_wgrad, conv2_dgrad;
 };
@@ -294,7 +341,7 @@ void mnist_tc_destroy(tfg_job* j) {
   for (auto& sl : m->slots) {
     if (!sl.tc) continue;
     TcSlot* t = static_cast<TcSlot*>(sl.tc);
-    void* ps[] = {t->col_lp, t->a2_lp, t->dh1_lp, t->dy2_lp, t->partial};
+    void* ps[] = {t->col_lp, t->a2_lp, t->dh1_lp, t->dy2_lp, t->partial, t->col_lo, t->a2_lo, t->dh1_lo, t->dy2_lo};
     for (void* p : ps) cudaFree(p);
     delete t;
     sl.tc = nullptr;
@@ -305,6 +352,11 @@ void* mnist_tc_dh1_bf16(tfg_job* j, int slot) {
   MnistModel* m = j->model;
   if (!m || m->math != TFG_MATH_BF16 || !m->slots[slot].tc) return nullptr;
   return static_cast<TcSlot*>(m->slots[slot].tc)->dh1_lp;
+}
+float* mnist_tc_dh1_lo(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  if (!m || m->math != TFG_MATH_TF32X3 || !m->slots[slot].tc) return nullptr;
+  return static_cast<TcSlot*>(m->slots[slot].tc)->dh1_lo;
 }
 
 // Allocations only; tensor maps need the flat parameter/gradient buffers, which exist after
@@ -325,6 +377,12 @@ int mnist_tc_build(tfg_job* j) {
       alloc(&t->a2_lp, (size_t)B * 3136 * es);
       alloc(&t->dh1_lp, (size_t)B * 1024 * es);
     }
+    if (m->math == TFG_MATH_TF32X3) {
+      alloc((void**)&t->col_lo, (size_t)M2 * 800 * 4);
+      alloc((void**)&t->dy2_lo, (size_t)M2 * 64 * 4);
+      alloc((void**)&t->a2_lo, (size_t)B * 3136 * 4);
+      alloc((void**)&t->dh1_lo, (size_t)B * 1024 * 4);
+    }
     alloc((void**)&t->partial, sizeof(float) * std::max<size_t>({(size_t)kSplitW2Tc * 800 * 64,
                                                                   (size_t)kSplitFc1Fwd * B * 1024,
                                                                   (size_t)kSplitFc1Dgrad * B * 3136}));
@@ -338,9 +396,11 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   MnistSlot& s = m->slots[slot];
   TcSlot* t = static_cast<TcSlot*>(s.tc);
   if (t->conv2_fwd.C) return TFG_OK;
-  const int kind = m->math;
+  const bool x3 = m->math == TFG_MATH_TF32X3;
+  const int kind = x3 ? TFG_MATH_TF32 : m->math;      // element kind of the operands
   const bool bf = kind == TFG_MATH_BF16;
-  if (bf && !j->params_lp) return fail(j, TFG_ESTATE, "bf16 math needs the bf16 parameter shadow");
+  if ((bf || x3) && !j->params_lp) return fail(j, TFG_ESTATE, "this math mode needs the parameter shadow");
+  auto wgt_lo = [&](int v) -> const void* { return static_cast<const float*>(j->params_lp) + j->vars[m->var[v]].offset; };
   auto wgt = [&](int v) -> const void* {   // weight operand of variable v
     const int64_t off = j->vars[m->var[v]].offset;
     return bf ? static_cast<const void*>(static_cast<const char*>(j->params_lp) + 2 * off)
@@ -359,25 +419,31 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   // operand = (pointer, row-major pitch, mn_major); rows/K follow from the GEMM shape
   auto mk = [&](TcGemm& g, const char* name, int M, int N, int K, const void* A, long long lda, bool a_mn,
                 const void* Bp, long long ldb, bool b_mn, float* C, int block_n, int splits,
-                tc::Epilogue epi) -> int {
+                tc::Epilogue epi, const void* A_lo = nullptr, const void* B_lo = nullptr) -> int {
     g.name = name; g.M = M; g.N = N; g.K = K; g.C = C; g.ldc = N;
     g.block_n = block_n; g.splits = splits; g.epi = epi; g.partial = t->partial;
     g.a_mn = a_mn; g.b_mn = b_mn;
+    g.x3 = x3;
+    if (x3) {
+      if ((rc = make_map(&g.a_lo, kind, A_lo, M, K, lda, tc::kBlockM, a_mn))) return rc;
+      if ((rc = make_map(&g.b_lo, kind, B_lo, N, K, ldb, block_n, b_mn))) return rc;
+    }
     if ((rc = make_map(&g.a, kind, A, M, K, lda, tc::kBlockM, a_mn))) return rc;
     return make_map(&g.b, kind, Bp, N, K, ldb, block_n, b_mn);
   };
+  const void *w2l = x3 ? wgt_lo(2) : nullptr, *w3l = x3 ? wgt_lo(4) : nullptr;
   if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, w2, 64, true, s.y2, 64, 1,
-               tc::Epilogue{par(3), nullptr, 0, nullptr, 0}))) return rc;
+               tc::Epilogue{par(3), nullptr, 0, nullptr, 0}, t->col_lo, w2l))) return rc;
   if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, a2, 3136, false, w3, 1024, true, s.h1, 64,
-               kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1, nullptr, 0}))) return rc;
+               kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1, nullptr, 0}, t->a2_lo, w3l))) return rc;
   if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, a2, 3136, true, dh1, 1024, true, grd(4),
-               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->a2_lo, t->dh1_lo))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
-               64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+               64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dh1_lo, w3l))) return rc;
   if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
-               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->col_lo, t->dy2_lo))) return rc;
   if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
-               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dy2_lo, w2l))) return rc;
   if (bf) {   // dcol is the step's largest tensor: keep it in bf16, written through the TMA store epilogue
     t->conv2_dgrad.epi.out_bf16 = s.dcol;
     t->conv2_dgrad.tma_out = 1;
@@ -396,11 +462,13 @@ static int tc_forward_t(tfg_job* j, int slot) {
   int rc = mnist_tc_prepare(j, slot);
   if (rc) return rc;
   // conv2 as im2col GEMM
-  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 25 * (32 / (16 / (int)sizeof(T)))), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
+  const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
+  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 25 * (32 / (16 / (int)sizeof(T)))), 256, 0, st>>>(s.a1, (T*)t->col_lp,
+                                                                                                    t->col_lo, B);
   TC_LAUNCH_OK(j, "im2col_lp_kernel");
-  if ((rc = launch_tc(j, t->conv2_fwd, m->math, st))) return rc;
-  if ((rc = mnist_pool2(j, slot, t->a2_lp))) return rc;     // also drops the bf16 copy of a2
-  return launch_tc(j, t->fc1_fwd, m->math, st);
+  if ((rc = launch_tc(j, t->conv2_fwd, kind, st))) return rc;
+  if ((rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) return rc;     // also drops the operand copy / low-order plane of a2
+  return launch_tc(j, t->fc1_fwd, kind, st);
 }
 
 template <typename T>
@@ -411,12 +479,13 @@ static int tc_backward_t(tfg_job* j, int slot) {
   cudaStream_t st = j->stream;
   const int B = m->B;
   int rc;
-  if ((rc = launch_tc(j, t->fc1_wgrad, m->math, st))) return rc;   // dh1 (bf16) came from fc2_bwd_kernel
-  if ((rc = launch_tc(j, t->fc1_dgrad, m->math, st))) return rc;
-  unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, B, 7, 64);
+  const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
+  if ((rc = launch_tc(j, t->fc1_wgrad, kind, st))) return rc;   // dh1 (bf16 / low-order plane) came from fc2_bwd_kernel
+  if ((rc = launch_tc(j, t->fc1_dgrad, kind, st))) return rc;
+  unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
   TC_LAUNCH_OK(j, "unpool_lp_kernel");
-  if ((rc = launch_tc(j, t->conv2_wgrad, m->math, st))) return rc;
-  return launch_tc(j, t->conv2_dgrad, m->math, st);
+  if ((rc = launch_tc(j, t->conv2_wgrad, kind, st))) return rc;
+  return launch_tc(j, t->conv2_dgrad, kind, st);
 }
 
 int mnist_tc_forward(tfg_job* j, int slot) {
@@ -428,12 +497,12 @@ int mnist_tc_backward(tfg_job* j, int slot) {
 
 }  // namespace tfg
 
-// ---- stateless GEMM entry point (parity tests of the tensor kernel alone) --------------------
-extern "C" int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const void* b_dev, int b_mn_major,
-                           float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb, int block_n, int splits,
-                           float* partial_dev, const float* bias_dev, int relu, void* stream) {
+// ---- stateless GEMM entry points (parity tests of the tensor kernel alone) -------------------
+static int gemm_tc_entry(int math, const void* a_dev, const void* a_lo, int a_mn_major, const void* b_dev,
+                         const void* b_lo, int b_mn_major, float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb,
+                         int block_n, int splits, float* partial_dev, const float* bias_dev, int relu, void* stream,
+                         int chunk_kb = 0) {
   using namespace tfg;
-  if (math != TFG_MATH_BF16 && math != TFG_MATH_TF32) return fail(nullptr, TFG_EINVAL, "math must be bf16 or tf32");
   if (!a_dev || !b_dev || !c_dev || M < 1 || N < 1 || K < 1) return fail(nullptr, TFG_EINVAL, "bad argument");
   if (block_n != 64 && block_n != 128) return fail(nullptr, TFG_EINVAL, "block_n must be 64 or 128");
   TcGemm g;
@@ -445,5 +514,37 @@ extern "C" int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const vo
   int rc = make_map(&g.a, math, a_dev, M, K, lda, tc::kBlockM, g.a_mn);
   if (rc) return rc;
   if ((rc = make_map(&g.b, math, b_dev, N, K, ldb, block_n, g.b_mn))) return rc;
+  if (a_lo) {
+    g.x3 = true;
+    g.chunk_kb = chunk_kb;
+    if ((rc = make_map(&g.a_lo, math, a_lo, M, K, lda, tc::kBlockM, g.a_mn))) return rc;
+    if ((rc = make_map(&g.b_lo, math, b_lo, N, K, ldb, block_n, g.b_mn))) return rc;
+  }
   return launch_tc(nullptr, g, math, (cudaStream_t)stream);
+}
+
+extern "C" int tfg_gemm_tc(int math, const void* a_dev, int a_mn_major, const void* b_dev, int b_mn_major,
+                           float* c_dev, int M, int N, int K, int64_t lda, int64_t ldb, int block_n, int splits,
+                           float* partial_dev, const float* bias_dev, int relu, void* stream) {
+  using namespace tfg;
+  if (math != TFG_MATH_BF16 && math != TFG_MATH_TF32) return fail(nullptr, TFG_EINVAL, "math must be bf16 or tf32");
+  return gemm_tc_entry(math, a_dev, nullptr, a_mn_major, b_dev, nullptr, b_mn_major, c_dev, M, N, K, lda, ldb, block_n,
+                       splits, partial_dev, bias_dev, relu, stream);
+}
+
+extern "C" int tfg_gemm_tc_x3(const float* a_dev, const float* a_lo_dev, int a_mn_major, const float* b_dev,
+                              const float* b_lo_dev, int b_mn_major, float* c_dev, int M, int N, int K, int64_t lda,
+                              int64_t ldb, int block_n, int splits, int chunk_kb, float* partial_dev, const float* bias_dev,
+                              int relu, void* stream) {
+  using namespace tfg;
+  if (!a_lo_dev || !b_lo_dev) return fail(nullptr, TFG_EINVAL, "the split product needs both low-order planes");
+  if (chunk_kb < 0) return fail(nullptr, TFG_EINVAL, "chunk_kb must be >= 0");
+  return gemm_tc_entry(TFG_MATH_TF32, a_dev, a_lo_dev, a_mn_major, b_dev, b_lo_dev, b_mn_major, c_dev, M, N, K, lda, ldb,
+                       block_n, splits, partial_dev, bias_dev, relu, stream, chunk_kb);
+}
+
+extern "C" int tfg_tf32_split_lo(const float* src_dev, float* lo_dev, int64_t n, void* stream) {
+  using namespace tfg;
+  if (!src_dev || !lo_dev || n < 0) return fail(nullptr, TFG_EINVAL, "bad argument");
+  return launch_cast_lp(src_dev, lo_dev, n, 2, (cudaStream_t)stream) ? fail(nullptr, TFG_ECUDA, "split kernel launch failed") : TFG_OK;
 }

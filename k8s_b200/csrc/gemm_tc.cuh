@@ -47,6 +47,16 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Low-order plane of the 3xTF32 split (gemm_x3.cuh): kind::tf32 reads an fp32 word's top 19 bits
+// (truncation), so hi = x with the low 13 mantissa bits cleared, x - hi is exact, and lo is that
+// remainder rounded to tf32 (round-to-nearest) so that the hardware's truncation of lo loses nothing.
+__device__ __forceinline__ float tf32_lo(float x) {
+  const float hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+  uint32_t o;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(o) : "f"(x - hi));
+  return __uint_as_float(o);
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
 }

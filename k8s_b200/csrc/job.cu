@@ -391,9 +391,14 @@ int tfg_vars_finalize(tfg_job* j, int layout) {
     j->peer_grads[j->local_replicas[s]] = g;
   }
   j->peer_params[j->gpu_rank] = j->params;
-  if ((j->model && mnist_math(j) == TFG_MATH_BF16) || j->resnet) {
-    TFG_CUDA(j, cudaMalloc(&j->params_lp, bytes / 2));
-    TFG_CUDA(j, cudaMemsetAsync(j->params_lp, 0, bytes / 2, j->stream));
+  // operand-precision shadow of the parameters, kept current by the apply kernel: bf16 copy (bf16
+  // math, ResNet-50) or the fp32 low-order plane of the 3xTF32 split
+  if (j->model && mnist_math(j) == TFG_MATH_TF32X3) j->lp_mode = 2;
+  else if ((j->model && mnist_math(j) == TFG_MATH_BF16) || j->resnet) j->lp_mode = 1;
+  if (j->lp_mode) {
+    const size_t lp_bytes = j->lp_mode == 2 ? bytes : bytes / 2;
+    TFG_CUDA(j, cudaMalloc(&j->params_lp, lp_bytes));
+    TFG_CUDA(j, cudaMemsetAsync(j->params_lp, 0, lp_bytes, j->stream));
     j->peer_params_lp[j->gpu_rank] = j->params_lp;
   }
   build_segments(j);
@@ -439,10 +444,11 @@ static int var_copy(tfg_job* j, float* base, int var, void* host_out, const void
 
 int tfg_var_set(tfg_job* j, int var, const void* host, size_t bytes) {
   int rc = var_copy(j, j ? j->params : nullptr, var, nullptr, host, bytes);
-  if (rc == TFG_OK && j->params_lp) {   // keep the bf16 shadow current
+  if (rc == TFG_OK && j->params_lp) {   // keep the operand-precision shadow current
     const VarInfo& v = j->vars[var];
-    if (launch_cast_bf16(j->params + v.offset, static_cast<char*>(j->params_lp) + 2 * v.offset, v.count, j->stream))
-      return fail(j, TFG_ECUDA, "bf16 shadow cast failed");
+    const size_t es = j->lp_mode == 2 ? 4 : 2;
+    if (launch_cast_lp(j->params + v.offset, static_cast<char*>(j->params_lp) + es * v.offset, v.count, j->lp_mode, j->stream))
+      return fail(j, TFG_ECUDA, "parameter shadow cast failed");
     TFG_CUDA(j, cudaStreamSynchronize(j->stream));
   }
   return rc;
@@ -487,6 +493,17 @@ int tfg_opt_config(tfg_job* j, int kind, float lr, float momentum) {
   if (!j) return fail(nullptr, TFG_EINVAL, "job is NULL");
   if (kind != TFG_OPT_SGD && kind != TFG_OPT_MOMENTUM && kind != TFG_OPT_NESTEROV)
     return fail(j, TFG_EINVAL, "unknown optimizer kind");
+  if (kind != j->opt_kind || lr != j->lr || momentum != j->mu) {
+    // the captured step graphs carry the optimizer's constants as kernel arguments: drop them, the
+    // next step with each input set runs eagerly once and is captured again
+    if (j->bound && !j->step_graphs.empty()) {
+      TFG_CUDA(j, cudaSetDevice(j->device));
+      TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+      for (auto& g : j->step_graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+      j->step_graphs.clear();
+    }
+  }
   j->opt_kind = kind;
   j->lr = lr;
   j->mu = momentum;
@@ -694,7 +711,7 @@ int tfg_model_mnist_cnn(tfg_job* j, int batch, int math) {
   if (has_model(j)) return fail(j, TFG_ESTATE, "a model is already built");
   if (j->finalized) return fail(j, TFG_ESTATE, "variables are already finalized");
   if (batch < 1 || batch > 65536) return fail(j, TFG_EINVAL, "batch_per_replica out of range");
-  if (math != TFG_MATH_FP32 && math != TFG_MATH_BF16 && math != TFG_MATH_TF32)
+  if (math != TFG_MATH_FP32 && math != TFG_MATH_BF16 && math != TFG_MATH_TF32 && math != TFG_MATH_TF32X3)
     return fail(j, TFG_EINVAL, "unknown math mode");
   int rc = ensure_bound(j);
   if (rc) return rc;
@@ -742,7 +759,12 @@ static int step_run(tfg_job* j, const float* const* images, const int32_t* const
     for (size_t s = 0; s < ns; ++s) { key.push_back(images[s]); key.push_back(labels[s]); }
     for (auto& e : j->step_graphs)
       if (e.key == key) g = &e;
-    if (!g && j->step_graphs.size() < 32) {
+    if (!g) {
+      if (j->step_graphs.size() >= 32) {   // bounded cache: the oldest input set makes room
+        TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+        if (j->step_graphs.front().exec) cudaGraphExecDestroy(j->step_graphs.front().exec);
+        j->step_graphs.erase(j->step_graphs.begin());
+      }
       j->step_graphs.emplace_back();
       g = &j->step_graphs.back();
       g->key = key;

@@ -16,6 +16,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "gemm_tc.cuh"
 #include "model_mnist.cuh"
 
 namespace tfg {
@@ -142,7 +143,8 @@ im2col_kernel(const float* __restrict__ a1, T* __restrict__ col, T* __restrict__
 // ===== pool2 forward: y2[B,14,14,64] (bias included) -> a2[B,7,7,64] + argmax =============
 __global__ void __launch_bounds__(256)
 pool_relu_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t* __restrict__ idx,
-                 __nv_bfloat16* __restrict__ a_bf /* optional operand-precision copy */, int B, int HO, int C) {
+                 __nv_bfloat16* __restrict__ a_bf /* optional operand-precision copy */,
+                 float* __restrict__ a_lo /* optional low-order plane of the 3xTF32 split */, int B, int HO, int C) {
   const long long total = (long long)B * HO * HO * C;
   const int HI = HO * 2;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -161,6 +163,7 @@ pool_relu_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t* __
       }
     a[i] = fmaxf(best, 0.f);
     if (a_bf) a_bf[i] = __float2bfloat16_rn(fmaxf(best, 0.f));
+    if (a_lo) a_lo[i] = tc::tf32_lo(fmaxf(best, 0.f));
     idx[i] = (uint8_t)arg;
   }
 }
@@ -438,7 +441,8 @@ constexpr int kFc2PartialStride = 1024 * 11;
 
 __global__ void __launch_bounds__(128)
 fc2_bwd_kernel(const float* __restrict__ h1, const float* __restrict__ dlogits, const float* __restrict__ w4,
-               float* __restrict__ partial, float* __restrict__ dh1, __nv_bfloat16* __restrict__ dh1_bf, int B) {
+               float* __restrict__ partial, float* __restrict__ dh1, __nv_bfloat16* __restrict__ dh1_bf,
+               float* __restrict__ dh1_lo, int B) {
   __shared__ float dl[kFc2Chunk][10];
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int b0 = blockIdx.y * kFc2Chunk;
@@ -462,6 +466,7 @@ fc2_bwd_kernel(const float* __restrict__ h1, const float* __restrict__ dlogits, 
     v = hv > 0.f ? v : 0.f;
     dh1[(size_t)(b0 + b) * 1024 + k] = v;
     if (dh1_bf) dh1_bf[(size_t)(b0 + b) * 1024 + k] = __float2bfloat16_rn(v);
+    if (dh1_lo) dh1_lo[(size_t)(b0 + b) * 1024 + k] = tc::tf32_lo(v);
     bsum += v;
   }
   float* p = partial + (size_t)blockIdx.y * kFc2PartialStride;
@@ -675,11 +680,11 @@ int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes) {
   return TFG_OK;
 }
 
-int mnist_pool2(tfg_job* j, int slot, void* a2_bf16) {
+int mnist_pool2(tfg_job* j, int slot, void* a2_bf16, float* a2_lo) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
   pool_relu_kernel<<<blocks_for((long long)m->B * 3136), 256, 0, j->stream>>>(
-      s.y2, s.a2, s.idx2, static_cast<__nv_bfloat16*>(a2_bf16), m->B, 7, 64);
+      s.y2, s.a2, s.idx2, static_cast<__nv_bfloat16*>(a2_bf16), a2_lo, m->B, 7, 64);
   LAUNCH_OK(j, "pool_relu_kernel");
   return TFG_OK;
 }
@@ -708,7 +713,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     // y2[M2,64] = col[M2,800] * W2[800,64] + b2
     if ((rc = sgemm(j, "gemm conv2 fwd", s.col, true, 800, 1, par(2), true, 64, 1, s.y2, M2, 64, 800,
                     GemmEpi{par(3), nullptr, 0}, 1, nullptr))) return rc;
-    if ((rc = mnist_pool2(j, slot, nullptr))) return rc;
+    if ((rc = mnist_pool2(j, slot, nullptr, nullptr))) return rc;
     // h1[B,1024] = relu(a2[B,3136] * W3[3136,1024] + b3)
     if ((rc = sgemm(j, "gemm fc1 fwd", s.a2, true, 3136, 1, par(4), true, 1024, 1, s.h1, B, 1024, 3136,
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
@@ -724,7 +729,8 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   {
     const int chunks = (B + kFc2Chunk - 1) / kFc2Chunk;
     fc2_bwd_kernel<<<dim3(1024 / 128, chunks), 128, 0, st>>>(s.h1, s.dlogits, par(6), s.scratch, s.dh1,
-                                                             static_cast<__nv_bfloat16*>(mnist_tc_dh1_bf16(j, slot)), B);
+                                                             static_cast<__nv_bfloat16*>(mnist_tc_dh1_bf16(j, slot)),
+                                                             mnist_tc_dh1_lo(j, slot), B);
     LAUNCH_OK(j, "fc2_bwd_kernel");
     fc2_bwd_reduce_kernel<<<(kFc2PartialStride + 10 + 255) / 256, 256, 0, st>>>(s.scratch, s.dlogits, grd(6), grd(5),
                                                                                grd(7), chunks, B);

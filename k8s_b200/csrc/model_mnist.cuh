@@ -58,7 +58,7 @@ struct MnistModel {
 };
 
 // model_mnist.cu: y2 -> a2, idx2 (shared by both math paths)
-int mnist_pool2(tfg_job* j, int slot, void* a2_bf16);
+int mnist_pool2(tfg_job* j, int slot, void* a2_bf16, float* a2_lo);
 
 // gemm_tc.cu
 int mnist_tc_build(tfg_job* j);
@@ -66,5 +66,6 @@ void mnist_tc_destroy(tfg_job* j);
 int mnist_tc_forward(tfg_job* j, int slot);    // a1 -> y2/a2/idx2 -> h1
 int mnist_tc_backward(tfg_job* j, int slot);   // dh1 -> dW3, da2, dy2, dW2, dcol
 void* mnist_tc_dh1_bf16(tfg_job* j, int slot); // where fc2_bwd drops its bf16 copy of dh1 (NULL unless bf16 math)
+float* mnist_tc_dh1_lo(tfg_job* j, int slot);  // ... and the low-order plane of dh1 (NULL unless 3xTF32 math)
 
 }  // namespace tfg

@@ -7,6 +7,9 @@ namespace tfg {
 
 struct TcGemm {
   CUtensorMap a, b;
+  CUtensorMap a_lo, b_lo;      // x3: maps of the operands' low-order planes (same geometry as a / b)
+  bool x3 = false;             // 3xTF32 split product (gemm_x3.cuh; kind tf32 only): fp32-equivalent result
+  int chunk_kb = 0;            // x3: K blocks accumulated inside the tensor core per chunk (0 = default 2)
   CUtensorMap c;               // bf16 output [M, ldc], box {64, 128} (make_map(.., M, N, ldc, 128)); used when tma_out != 0
   int tma_out = 0;             // 1: TMA store, 2: TMA reduce-add into the output; forces the persistent kernel
   float* C = nullptr;          // [M, ldc]

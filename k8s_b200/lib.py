@@ -16,14 +16,14 @@ HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "tfgraft.h")
 # enums of include/tfgraft.h
 OPT_SGD, OPT_MOMENTUM, OPT_NESTEROV = 0, 1, 2
 LAYOUT_LOGICAL, LAYOUT_BALANCED = 0, 1
-MATH_FP32, MATH_BF16, MATH_TF32 = 0, 1, 2
+MATH_FP32, MATH_BF16, MATH_TF32, MATH_TF32X3 = 0, 1, 2, 3
 PART_MOD, PART_DIV = 0, 1
 DT_F32, DT_I64 = 0, 1
 BUF_PARAMS, BUF_GRADS, BUF_ACCUM, BUF_LOSS, BUF_FLAGS = 0, 1, 2, 3, 4
 MAX_REPLICAS, MAX_GPUS, IPC_HANDLE_BYTES = 64, 16, 64
 SPARSE_STATIC_MAX_IDS, SPARSE_STATIC_SCRATCH_BYTES = 65536, 1081600
 OPT_KINDS = {"sgd": OPT_SGD, "momentum": OPT_MOMENTUM, "nesterov": OPT_NESTEROV}
-MATH_MODES = {"fp32": MATH_FP32, "bf16": MATH_BF16, "tf32": MATH_TF32}
+MATH_MODES = {"fp32": MATH_FP32, "bf16": MATH_BF16, "tf32": MATH_TF32, "tf32x3": MATH_TF32X3}
 LAYOUTS = {"logical": LAYOUT_LOGICAL, "balanced": LAYOUT_BALANCED}
 
 
@@ -111,6 +111,9 @@ _SIGS = {
     "tfg_launch_count": (C.c_int64, [_p]),
     "tfg_gemm_tc": (C.c_int, [C.c_int, _p, C.c_int, _p, C.c_int, _p, C.c_int, C.c_int, C.c_int, C.c_int64,
                               C.c_int64, C.c_int, C.c_int, _p, _p, C.c_int, _p]),
+    "tfg_gemm_tc_x3": (C.c_int, [_p, _p, C.c_int, _p, _p, C.c_int, _p, C.c_int, C.c_int, C.c_int, C.c_int64,
+                                 C.c_int64, C.c_int, C.c_int, C.c_int, _p, _p, C.c_int, _p]),
+    "tfg_tf32_split_lo": (C.c_int, [_p, _p, C.c_int64, _p]),
     "tfg_profile_enable": (C.c_int, [_p, C.c_int]),
     "tfg_profile_report": (C.c_int, [_p, C.c_char_p, C.c_size_t]),
     "tfg_smoke": (C.c_int, [_p, C.c_int, _p, C.c_size_t, C.POINTER(C.c_int)]),

@@ -56,6 +56,67 @@ def test_gemm_tc_matches_float64(lib, math, majors, M, N, K, block_n, splits):
     assert bool((err <= tol).all()), "max err %.3e at bound %.3e" % (float(err.max()), float(bound.max()))
 
 
+def _x3_case(lib, majors, M, N, K, block_n, splits, chunk_kb, same_sign):
+    g = torch.Generator(device="cpu").manual_seed(M * 11 + N * 5 + K)
+    a = torch.randn(M, K, generator=g)
+    b = torch.randn(N, K, generator=g)
+    if same_sign:
+        a, b = a.abs(), b.abs()
+    a_mn, b_mn = majors[0] == "M", majors[1] == "M"
+    if (a_mn and (M * 4) % 16) or (b_mn and (N * 4) % 16):
+        pytest.skip("row pitch of the MN-major operand is not a multiple of 16 bytes")
+    da = (a.t() if a_mn else a).contiguous().cuda()
+    db = (b.t() if b_mn else b).contiguous().cuda()
+    da_lo, db_lo = torch.empty_like(da), torch.empty_like(db)
+    lib.check(lib.tf32_split_lo(da.data_ptr(), da_lo.data_ptr(), da.numel(), 0))
+    lib.check(lib.tf32_split_lo(db.data_ptr(), db_lo.data_ptr(), db.numel(), 0))
+    # the split itself: hi = the top 19 bits, lo = the remainder rounded to tf32, |x - hi - lo| <= 2^-21 |x|
+    hi = (da.view(torch.int32) & -8192).view(torch.float32)
+    assert bool(((da - hi - da_lo).abs() <= da.abs() * 2.0 ** -21).all())
+    assert bool(((da_lo.view(torch.int32) & 8191) == 0).all())
+    lda, ldb = (M if a_mn else K), (N if b_mn else K)
+    c = torch.full((M, N), float("nan"), device="cuda")
+    partial = torch.empty(max(splits, 1) * M * N, device="cuda")
+    bias = torch.randn(N, generator=g).cuda()
+    lib.check(lib.gemm_tc_x3(da.data_ptr(), da_lo.data_ptr(), int(a_mn), db.data_ptr(), db_lo.data_ptr(), int(b_mn),
+                             c.data_ptr(), M, N, K, lda, ldb, block_n, splits, chunk_kb, partial.data_ptr(),
+                             bias.data_ptr(), 0, 0))
+    torch.cuda.synchronize()
+    assert not torch.isnan(c).any()
+    ref = a.double() @ b.double().T + bias.cpu().double()
+    err = (c.cpu().double() - ref).abs()
+    err32 = ((a @ b.T + bias.cpu()).double() - ref).abs()          # what plain fp32 on the CPU makes of it
+    return err, err32, ref, a.double().abs() @ b.double().abs().T
+
+
+@pytest.mark.parametrize("same_sign", [False, True])
+@pytest.mark.parametrize("majors", ["KK", "KM", "MM", "MK"])
+@pytest.mark.parametrize("M,N,K,block_n,splits", SHAPES)
+def test_gemm_tc_x3_is_fp32_equivalent(lib, majors, M, N, K, block_n, splits, same_sign):
+    """The 3xTF32 split product with chunked accumulation (gemm_x3.cuh) against float64: the error
+    must be of the order of fp32 summation noise, not of the tf32 operand error (1e-3) nor of the
+    tensor core's truncating accumulator (6e-5 of the result at K = 3136).  Bound: 8e-7 of
+    sum|a||b| per element (the dropped lo*lo term is < 2^-20 and the truncation inside a chunk a few
+    ulp; same-sign inputs make both add up coherently and make sum|a||b| the result itself) -- what
+    a sequential fp32 sum of a few thousand terms achieves."""
+    err, err32, ref, bound = _x3_case(lib, majors, M, N, K, block_n, splits, 0, same_sign)
+    assert bool((err <= 8e-7 * bound + 1e-6).all()), "max err/bound %.3e" % float((err / (bound + 1e-30)).max())
+
+
+def test_gemm_tc_x3_chunking_is_what_removes_the_accumulator_bias(lib):
+    """K = 3136 with same-sign operands: one TMEM accumulator for the whole K loop (chunk_kb = 98)
+    shows the tensor core's truncating adds as a bias that shrinks the result; chunks of 2 K
+    blocks summed in registers do not."""
+    big = _x3_case(lib, "KK", 128, 64, 3136, 64, 1, 98, True)
+    small = _x3_case(lib, "KK", 128, 64, 3136, 64, 1, 2, True)
+    rel_big = float((big[0] / big[2].abs()).mean())
+    rel_small = float((small[0] / small[2].abs()).mean())
+    print("mean relative error: one accumulator %.3e, chunks of 2 K blocks %.3e, fp32 CPU matmul %.3e"
+          % (rel_big, rel_small, float((small[1] / small[2].abs()).mean())))
+    assert rel_small <= 5e-7
+    assert rel_big >= 20 * rel_small
+
+
 def test_gemm_tc_relu_and_argument_checks(lib):
     a = torch.randn(64, 64).bfloat16().cuda()
     b = torch.randn(32, 64).bfloat16().cuda()
