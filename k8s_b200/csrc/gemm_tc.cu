@@ -8,6 +8,7 @@
 
 #include "common.cuh"
 #include "gemm_tc.cuh"
+#include "conv_x3.cuh"
 #include "gemm_x3.cuh"
 #include "model_mnist.cuh"
 #include "tc_host.cuh"
@@ -52,6 +53,25 @@ int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t 
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+  return TFG_OK;
+}
+
+// fp32 NHWC tensor [N, H, W, C]: box {32 channels (one 128-byte line), bw columns, bh rows, 1 image}.
+// mn_major: the box feeds an MN-major tf32 operand (pixels = K): 128-byte swizzle with 32-byte atoms.
+int make_map_4d_f32(CUtensorMap* map, const void* ptr, int N, int H, int W, int C, int bw, int bh, bool mn_major) {
+  PFN_cuTensorMapEncodeTiled enc = get_encode();
+  if (!enc) return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || C % 32 != 0)
+    return fail(nullptr, TFG_EINVAL, "activation tensor must be 16-byte aligned with C a multiple of 32");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(nullptr, TFG_ECUDA, "cuTensorMapEncodeTiled(4d fp32) failed with CUresult " + std::to_string((int)r));
   return TFG_OK;
 }
 
@@ -245,7 +265,7 @@ template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16
 // 16 bytes of col (4 fp32 / 8 bf16 channels)
 template <typename T>
 __global__ void __launch_bounds__(256)
-im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, float* __restrict__ col_lo, int B) {
+im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, int B) {
   constexpr int kPer = 16 / sizeof(T);          // channels per thread
   constexpr int kGroups = 32 / kPer;            // threads per tap
   const long long total = (long long)B * 196 * 25 * kGroups;
@@ -264,9 +284,6 @@ im2col_lp_kernel(const float* __restrict__ a1, T* __restrict__ col, float* __res
     for (int q = 0; q < kPer / 4; ++q) {
       const float4 v = ok ? *reinterpret_cast<const float4*>(src + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
       store4(dst + 4 * q, v);
-      if (col_lo)   // T = float: the low-order plane of the 3xTF32 split
-        store4(col_lo + m * 800 + kk * 32 + cg * kPer + 4 * q,
-               make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w)));
     }
   }
 }
@@ -313,9 +330,16 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
 
 struct TcSlot {            // per replica slot: operand copies of activations + GEMM descriptors
   void *col_lp = nullptr, *a2_lp = nullptr, *dh1_lp = nullptr, *dy2_lp = nullptr;   // a2/dh1: bf16 math only
-  float *col_lo = nullptr, *a2_lo = nullptr, *dh1_lo = nullptr, *dy2_lo = nullptr;   // 3xTF32: low-order planes
+  float *a1_lo = nullptr, *a2_lo = nullptr, *dh1_lo = nullptr, *dy2_lo = nullptr;   // 3xTF32: low-order planes
   float* partial = nullptr;
   TcGemm conv2_fwd, fc1_fwd, fc1_wgrad, fc1_dgrad, conv2_wgrad, conv2_dgrad;
+  // 3xTF32: conv2 as implicit GEMMs (conv_x3.cuh): maps of the slabs (x = a1 / dy2 and their low-order
+  // planes) and of W2 viewed [800, 64], per kernel
+  CUtensorMap c2f_x, c2f_x_lo, c2f_w, c2f_w_lo;       // forward: a1 slabs, W2 MN-major boxes
+  CUtensorMap c2d_x, c2d_x_lo, c2d_w, c2d_w_lo;       // data gradient: dy2 slabs, W2 K-major boxes
+  CUtensorMap c2w_x, c2w_x_lo, c2w_dy, c2w_dy_lo;     // weight gradient: a1 slab and dy2 boxes, MN-major
+  tc::WgradPlan wplan;
+  float* wpartial = nullptr;                          // [nz][800][64]
 };
 
 constexpr int kSplitW2Tc = 21;   // 7 M-tiles x 21 K-splits = 147 CTAs on 148 SMs
@@ -341,7 +365,7 @@ void mnist_tc_destroy(tfg_job* j) {
   for (auto& sl : m->slots) {
     if (!sl.tc) continue;
     TcSlot* t = static_cast<TcSlot*>(sl.tc);
-    void* ps[] = {t->col_lp, t->a2_lp, t->dh1_lp, t->dy2_lp, t->partial, t->col_lo, t->a2_lo, t->dh1_lo, t->dy2_lo};
+    void* ps[] = {t->col_lp, t->a2_lp, t->dh1_lp, t->dy2_lp, t->partial, t->a1_lo, t->a2_lo, t->dh1_lo, t->dy2_lo, t->wpartial};
     for (void* p : ps) cudaFree(p);
     delete t;
     sl.tc = nullptr;
@@ -368,17 +392,24 @@ int mnist_tc_build(tfg_job* j) {
   const long long B = m->B, M2 = B * 196;
   cudaError_t e = cudaSuccess;
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16); };
+  const bool x3 = m->math == TFG_MATH_TF32X3;
   for (auto& sl : m->slots) {
     TcSlot* t = new TcSlot();
     sl.tc = t;
-    alloc(&t->col_lp, (size_t)M2 * 800 * es);
+    if (!x3) alloc(&t->col_lp, (size_t)M2 * 800 * es);      // 3xTF32 runs conv2 without an im2col matrix
     alloc(&t->dy2_lp, (size_t)M2 * 64 * es);
     if (bf) {
       alloc(&t->a2_lp, (size_t)B * 3136 * es);
       alloc(&t->dh1_lp, (size_t)B * 1024 * es);
     }
-    if (m->math == TFG_MATH_TF32X3) {
-      alloc((void**)&t->col_lo, (size_t)M2 * 800 * 4);
+    if (x3) {
+      // CTAs per M-tile group of the conv2 weight gradient: groups 0..2 hold two M tiles, group 3 one
+      const int tiles = (int)B * tc::kWTilesPerImage;
+      const int nz2 = std::min(42, tiles), nz1 = std::min(kNumSMs - 3 * 42, tiles);
+      t->wplan.cta0[0] = 0;
+      for (int g = 0; g < 4; ++g) t->wplan.cta0[g + 1] = t->wplan.cta0[g] + (g < 3 ? nz2 : nz1);
+      alloc((void**)&t->wpartial, (size_t)nz2 * 800 * 64 * 4);
+      alloc((void**)&t->a1_lo, (size_t)B * 6272 * 4);
       alloc((void**)&t->dy2_lo, (size_t)M2 * 64 * 4);
       alloc((void**)&t->a2_lo, (size_t)B * 3136 * 4);
       alloc((void**)&t->dh1_lo, (size_t)B * 1024 * 4);
@@ -395,7 +426,7 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
   TcSlot* t = static_cast<TcSlot*>(s.tc);
-  if (t->conv2_fwd.C) return TFG_OK;
+  if (t->fc1_fwd.C) return TFG_OK;
   const bool x3 = m->math == TFG_MATH_TF32X3;
   const int kind = x3 ? TFG_MATH_TF32 : m->math;      // element kind of the operands
   const bool bf = kind == TFG_MATH_BF16;
@@ -432,23 +463,72 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
     return make_map(&g.b, kind, Bp, N, K, ldb, block_n, b_mn);
   };
   const void *w2l = x3 ? wgt_lo(2) : nullptr, *w3l = x3 ? wgt_lo(4) : nullptr;
-  if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, w2, 64, true, s.y2, 64, 1,
-               tc::Epilogue{par(3), nullptr, 0, nullptr, 0}, t->col_lo, w2l))) return rc;
+  if (x3) {
+    // conv2 forward / data gradient / weight gradient as implicit GEMMs over shared-memory slabs
+    if ((rc = make_map_4d_f32(&t->c2f_x, s.a1, B, 14, 14, 32, 18, 18, false))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2f_x_lo, t->a1_lo, B, 14, 14, 32, 18, 18, false))) return rc;
+    if ((rc = make_map(&t->c2f_w, kind, w2, 64, 800, 64, 64, true))) return rc;          // boxes {32 n, 32 k lines}
+    if ((rc = make_map(&t->c2f_w_lo, kind, w2l, 64, 800, 64, 64, true))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2d_x, t->dy2_lp, B, 14, 14, 64, 18, 18, false))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2d_x_lo, t->dy2_lo, B, 14, 14, 64, 18, 18, false))) return rc;
+    if ((rc = make_map(&t->c2d_w, kind, w2, 800, 64, 64, 32, false))) return rc;         // boxes {32 k, 32 rows}
+    if ((rc = make_map(&t->c2d_w_lo, kind, w2l, 800, 64, 64, 32, false))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2w_x, s.a1, B, 14, 14, 32, 18, tc::kWTileRows + 4, true))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2w_x_lo, t->a1_lo, B, 14, 14, 32, 18, tc::kWTileRows + 4, true))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2w_dy, t->dy2_lp, B, 14, 14, 64, 18, tc::kWTileRows, true))) return rc;
+    if ((rc = make_map_4d_f32(&t->c2w_dy_lo, t->dy2_lo, B, 14, 14, 64, 18, tc::kWTileRows, true))) return rc;
+  } else if ((rc = mk(t->conv2_fwd, "tc gemm conv2 fwd", M2, 64, 800, t->col_lp, 800, false, w2, 64, true, s.y2, 64, 1,
+               tc::Epilogue{par(3), nullptr, 0, nullptr, 0}))) return rc;
   if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, a2, 3136, false, w3, 1024, true, s.h1, 64,
                kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1, nullptr, 0}, t->a2_lo, w3l))) return rc;
   if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, a2, 3136, true, dh1, 1024, true, grd(4),
                128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->a2_lo, t->dh1_lo))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
                64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dh1_lo, w3l))) return rc;
-  if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
-               64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->col_lo, t->dy2_lo))) return rc;
-  if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
-               128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dy2_lo, w2l))) return rc;
+  if (!x3) {
+    if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
+                 64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+    if ((rc = mk(t->conv2_dgrad, "tc gemm conv2 dgrad", M2, 800, 64, t->dy2_lp, 64, false, w2, 64, false, s.dcol,
+                 128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
+  }
   if (bf) {   // dcol is the step's largest tensor: keep it in bf16, written through the TMA store epilogue
     t->conv2_dgrad.epi.out_bf16 = s.dcol;
     t->conv2_dgrad.tma_out = 1;
     if ((rc = make_map(&t->conv2_dgrad.c, kind, s.dcol, M2, 800, 800, tc::kBlockM, false))) return rc;
   }
+  return TFG_OK;
+}
+
+template <bool DGRAD>
+static int launch_conv2_x3(tfg_job* j, const char* name, const CUtensorMap& x, const CUtensorMap& x_lo, const CUtensorMap& w,
+                           const CUtensorMap& w_lo, float* out, const float* bias, const float* mask, int B, cudaStream_t st) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_c2<DGRAD>();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::conv2_x3_kernel<DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail_cuda(j, e, name);
+    attr_set = true;
+  }
+  // a chunk = 2 K blocks of the main product: two taps of 32 input channels forward, one tap of 64 backward
+  tc::conv2_x3_kernel<DGRAD><<<std::min(B, kNumSMs), tc::kC2Threads, smem, st>>>(x, x_lo, w, w_lo, out, bias, mask, B,
+                                                                                  DGRAD ? 1 : 2);
+  TC_LAUNCH_OK(j, name);
+  return TFG_OK;
+}
+
+static int launch_conv2_wgrad_x3(tfg_job* j, TcSlot* t, float* dw, int B, cudaStream_t st) {
+  static bool attr_set = false;
+  constexpr size_t smem = tc::smem_bytes_c2_wgrad();
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc::conv2_wgrad_x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail_cuda(j, e, "conv2 wgrad x3");
+    attr_set = true;
+  }
+  tc::conv2_wgrad_x3_kernel<<<t->wplan.cta0[4], tc::kC2Threads, smem, st>>>(t->c2w_x, t->c2w_x_lo, t->c2w_dy, t->c2w_dy_lo,
+                                                                            t->wpartial, B, t->wplan);
+  TC_LAUNCH_OK(j, "conv2 wgrad x3");
+  tc::conv2_wgrad_reduce_kernel<<<(800 * 16 + 255) / 256, 256, 0, st>>>(t->wpartial, dw, t->wplan);
+  TC_LAUNCH_OK(j, "conv2 wgrad reduce");
   return TFG_OK;
 }
 
@@ -461,12 +541,17 @@ static int tc_forward_t(tfg_job* j, int slot) {
   const int B = m->B, M2 = B * 196;
   int rc = mnist_tc_prepare(j, slot);
   if (rc) return rc;
-  // conv2 as im2col GEMM
   const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
-  im2col_lp_kernel<T><<<blocks_for((long long)M2 * 25 * (32 / (16 / (int)sizeof(T)))), 256, 0, st>>>(s.a1, (T*)t->col_lp,
-                                                                                                    t->col_lo, B);
-  TC_LAUNCH_OK(j, "im2col_lp_kernel");
-  if ((rc = launch_tc(j, t->conv2_fwd, kind, st))) return rc;
+  if (m->math == TFG_MATH_TF32X3) {
+    const float* b2 = j->params + j->vars[m->var[3]].offset;
+    if ((rc = launch_conv2_x3<false>(j, "conv2 fwd x3", t->c2f_x, t->c2f_x_lo, t->c2f_w, t->c2f_w_lo, s.y2, b2, nullptr, B, st)))
+      return rc;
+  } else {
+    // conv2 as im2col GEMM
+    im2col_lp_kernel<T><<<blocks_for((long long)M2 * 25 * (32 / (16 / (int)sizeof(T)))), 256, 0, st>>>(s.a1, (T*)t->col_lp, B);
+    TC_LAUNCH_OK(j, "im2col_lp_kernel");
+    if ((rc = launch_tc(j, t->conv2_fwd, kind, st))) return rc;
+  }
   if ((rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) return rc;     // also drops the operand copy / low-order plane of a2
   return launch_tc(j, t->fc1_fwd, kind, st);
 }
@@ -484,8 +569,19 @@ static int tc_backward_t(tfg_job* j, int slot) {
   if ((rc = launch_tc(j, t->fc1_dgrad, kind, st))) return rc;
   unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
   TC_LAUNCH_OK(j, "unpool_lp_kernel");
+  if (m->math == TFG_MATH_TF32X3) {
+    if ((rc = launch_conv2_wgrad_x3(j, t, j->grads[slot] + j->vars[m->var[2]].offset, B, st))) return rc;
+    // dx straight into g1m, masked by a1 > 0: no dcol, no col2im
+    return launch_conv2_x3<true>(j, "conv2 dgrad x3", t->c2d_x, t->c2d_x_lo, t->c2d_w, t->c2d_w_lo, s.g1m, nullptr, s.a1, B, st);
+  }
   if ((rc = launch_tc(j, t->conv2_wgrad, kind, st))) return rc;
   return launch_tc(j, t->conv2_dgrad, kind, st);
+}
+
+float* mnist_tc_a1_lo(tfg_job* j, int slot) {
+  MnistModel* m = j->model;
+  if (!m || m->math != TFG_MATH_TF32X3 || !m->slots[slot].tc) return nullptr;
+  return static_cast<TcSlot*>(m->slots[slot].tc)->a1_lo;
 }
 
 int mnist_tc_forward(tfg_job* j, int slot) {

@@ -27,7 +27,7 @@ namespace tfg {
 __global__ void __launch_bounds__(256)
 conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1,
                        const float* __restrict__ b1, float* __restrict__ a1,
-                       uint8_t* __restrict__ idx1) {
+                       uint8_t* __restrict__ idx1, float* __restrict__ a1_lo /* 3xTF32: low-order plane of a1, or NULL */) {
   __shared__ float xs[32][33];   // image with a 2-pixel zero border
   __shared__ float ws[25][32];
   __shared__ float bs[32];
@@ -63,6 +63,7 @@ conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1
       }
     const size_t oi = (size_t)b * (14 * 14 * 32) + o;
     a1[oi] = fmaxf(best, 0.f);
+    if (a1_lo) a1_lo[oi] = tc::tf32_lo(fmaxf(best, 0.f));
     idx1[oi] = (uint8_t)arg;
   }
 }
@@ -703,7 +704,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   const bool tc = m->math != TFG_MATH_FP32;
 
   // ---------------- forward ----------------
-  conv1_pool_relu_kernel<<<B, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1);
+  conv1_pool_relu_kernel<<<B, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1, mnist_tc_a1_lo(j, slot));
   LAUNCH_OK(j, "conv1_pool_relu_kernel");
   if (tc) {
     if ((rc = mnist_tc_forward(j, slot))) return rc;   // conv2 + fc1 on the tensor path
@@ -757,12 +758,16 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   }
   // db2 = sum over pooled positions of the masked pooled gradient
   if ((rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
-  if (m->math == TFG_MATH_BF16)   // the tensor path's dgrad GEMM stored dcol as bf16 (mnist_tc_prepare)
+  if (m->math == TFG_MATH_TF32X3) {
+    // the implicit data-gradient kernel wrote g1m itself (conv_x3.cuh)
+  } else if (m->math == TFG_MATH_BF16) {   // the tensor path's dgrad GEMM stored dcol as bf16 (mnist_tc_prepare)
     col2im_mask_kernel<__nv_bfloat16><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(s.dcol), s.a1, s.g1m, B);
-  else
+    LAUNCH_OK(j, "col2im_mask_kernel");
+  } else {
     col2im_mask_kernel<float><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
-  LAUNCH_OK(j, "col2im_mask_kernel");
+    LAUNCH_OK(j, "col2im_mask_kernel");
+  }
   conv1_bwd_kernel<<<2 * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
