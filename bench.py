@@ -58,6 +58,8 @@ def parse_args(argv=None):
     ap.add_argument("--ps-params", type=int, default=256 << 20,
                     help="parameters of the PS-update roofline probe (BASELINE config 5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-resnet", dest="with_resnet", action="store_false",
+                    help="skip the ResNet-50 (BASELINE config 4) sub-measurement of the default line")
     a = ap.parse_args(argv)
     if a.batch <= 0:
         a.batch = BATCH if a.model == "mnist" else 256
@@ -255,12 +257,20 @@ def run_reference_resnet(a) -> dict:
     }
 
 
-def config_dict(a, n: int, math: str) -> dict:
-    if a.model == "resnet50":
+MATH_IMPL = {"tf32x3": "3xTF32 split products on tcgen05 (a_lo*b + a*b_lo + a*b; chunked fp32 accumulation, TMEM + registers): "
+                       "fp32-equivalent, parity-tested at the fp32 bounds",
+             "fp32": "CUDA-core FFMA", "bf16": "tcgen05 kind::f16, bf16 operands, fp32 accumulate",
+             "tf32": "tcgen05 kind::tf32, one MMA per product"}
+
+
+def config_dict(a, n: int, math: str, model: str = None, batch: int = None) -> dict:
+    model = model or a.model
+    batch = batch or a.batch
+    if model == "resnet50":
         return {
             "workload": "tf_cnn_benchmarks-style ResNet-50 v1.5, synthetic ImageNet %dx%d, %d classes, bf16, "
                         "%d replica(s) sync-PS on %d B200 (BASELINE config 4)" % (a.image, a.image, a.classes, n, n),
-            "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
+            "batch_per_replica": batch, "global_batch": batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
             "optimizer": a.opt, "lr": LR, "math": "bf16", "layout": a.layout, "params": 25557032,
             "parallelism": "dp%d + %d PS shards" % (n, n),
             "l2": "flushed between timed steps (256 MiB write, untimed)", "exchange": a.exchange,
@@ -269,7 +279,7 @@ def config_dict(a, n: int, math: str) -> dict:
         "workload": ("tf_sample MNIST CNN sync-PS step: %s" %
                      ("examples/tf_job_gpu.yaml shape, 1 MASTER on 1 B200, no PS exchange" if n == 1 else
                       "1 MASTER + %d WORKER + %d PS shards on %d B200 (BASELINE config 3 shape)" % (n - 1, n, n))),
-        "batch_per_replica": a.batch, "global_batch": a.batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
+        "batch_per_replica": batch, "global_batch": batch * n, "replicas": n, "ps_shards": 0 if n == 1 else n,
         # tf32x3 computes the fp32 model to fp32 accuracy (parity-tested at the fp32 bounds): the config is the
         # reference arm's; HOW the contractions run is the line's "math_impl" key
         "optimizer": a.opt, "lr": LR, "math": "fp32" if math == "tf32x3" else math, "layout": a.layout,
@@ -279,26 +289,42 @@ def config_dict(a, n: int, math: str) -> dict:
 
 
 # ---- algorithmic work per launch of every kernel in the step (DESIGN.md "Kernels") ----------
+X3_PEAK_NOTE = ("3xTF32 ceiling = measured bf16 peak / 6: kind::tf32 runs at half the bf16 rate and every product "
+                "takes three MMAs; achieved = fp32-equivalent (algorithmic) FLOPs / time")
+
+
 def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int, math: str = "bf16",
                      peaks: dict | None = None):
-    """-> (bound, amount per launch): FLOPs ("tensor") or bytes ("hbm").  B = examples per replica.
-    A contraction is charged to whichever of its two rooflines takes longer at the measured peaks
-    (operands read once + output written once against HBM, 2 M N K against the tensor pipe): the
-    thin-K GEMMs of this model (conv2 dgrad: K = 64, an 800-wide output) are HBM-bound."""
+    """-> (bound, amount per launch, peak note): FLOPs ("tensor") or bytes ("hbm").  B = examples per
+    replica.  A contraction is charged to whichever of its two rooflines takes longer at the measured
+    peaks (operands read once + output written once against HBM, 2 M N K against the tensor pipe): the
+    thin-K GEMMs of this model (conv2 dgrad: K = 64, an 800-wide output) are HBM-bound.  In tf32x3 math
+    the FLOPs are the fp32-equivalent 2 M N K and the tensor ceiling is the bf16 peak / 6 (peak note)."""
     M2 = B * 196
     gemm = {"gemm conv2 fwd": (M2, 64, 800), "gemm conv2 dgrad": (M2, 800, 64), "gemm conv2 wgrad": (800, 64, M2),
             "gemm fc1 fwd": (B, 1024, 3136), "gemm fc1 dgrad": (B, 3136, 1024), "gemm fc1 wgrad": (3136, 1024, B),
             "gemm fc2 fwd": (B, 10, 1024), "gemm fc2 dgrad": (B, 1024, 10), "gemm fc2 wgrad": (1024, 10, B)}
+    # the implicit 3xTF32 conv2 kernels: same contraction, operands = the activations themselves (+ low-order planes)
+    conv_x3 = {"conv2 fwd x3": (M2 * 32 * 2 + 800 * 64 * 2, M2 * 64), "conv2 dgrad x3": (M2 * 64 * 2 + 800 * 64 * 2 + M2 * 32, M2 * 32),
+               "conv2 wgrad x3": (M2 * 32 * 2 + M2 * 64 * 2, 42 * 800 * 64)}
+    if name in conv_x3:
+        flops = 2.0 * M2 * 64 * 800
+        rd, wr = conv_x3[name]
+        nbytes = 4.0 * (rd + wr)
+        if peaks and nbytes / (peaks["hbm_gbs"] * 1e9) > flops / (peaks["bf16_tflops_sustained"] / 6 * 1e12):
+            return "hbm", nbytes, None
+        return "tensor", flops, X3_PEAK_NOTE
     name = name[3:] if name.startswith("tc ") else name     # the tensor-path GEMMs carry a "tc " prefix
     if name in gemm:
         m, n, k = gemm[name]
         flops = 2.0 * m * n * k
-        esz = 2 if math == "bf16" else 4
+        esz = 2 if math == "bf16" else 8 if math == "tf32x3" else 4     # tf32x3 reads each operand and its low-order plane
         out = 2 if (math == "bf16" and name == "gemm conv2 dgrad") else 4   # dcol is kept in bf16, the rest fp32
         nbytes = float((m * k + n * k) * esz + m * n * out)
-        if peaks and nbytes / (peaks["hbm_gbs"] * 1e9) > flops / (peaks["bf16_tflops_sustained"] * 1e12):
-            return "hbm", nbytes
-        return "tensor", flops
+        tensor_peak = peaks["bf16_tflops_sustained"] / (6.0 if math == "tf32x3" else 1.0) if peaks else None
+        if peaks and nbytes / (peaks["hbm_gbs"] * 1e9) > flops / (tensor_peak * 1e12):
+            return "hbm", nbytes, None
+        return "tensor", flops, (X3_PEAK_NOTE if math == "tf32x3" else None)
     f = 4
     hbm = {
         "conv1_pool_relu_kernel": B * 784 * f + B * 6272 * (f + 1),
@@ -315,18 +341,22 @@ def algorithmic_work(name: str, B: int, n_params: int, opt: str, n_replicas: int
         "split-K reduce": f * ((21 + 1) * 800 * 64 + (7 + 1) * B * 1024 + (3 + 1) * B * 3136) / 3.0,
     }
     if name in hbm:
-        return "hbm", float(hbm[name])
-    return "hbm", None
+        return "hbm", float(hbm[name]), None
+    return "hbm", None, None
 
 
 def measured_traffic(model: str, kernel: str):
-    """DRAM bytes per launch of `kernel` from this round's ncu capture (profiles/r1_traffic.json), at the
+    """DRAM bytes per launch of `kernel` from the ncu captures (profiles/r2_traffic.json, else r1's), at the
     default batch sizes; None when that kernel was not captured."""
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-            return json.load(f).get("%s:%s" % (model, kernel))
-    except (OSError, ValueError):
-        return None
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", name)) as f:
+                v = json.load(f).get("%s:%s" % (model, kernel))
+            if v is not None:
+                return v
+        except (OSError, ValueError):
+            pass
+    return None
 
 
 def resnet_work(name: str, B: int, image: int, classes: int):
@@ -390,49 +420,64 @@ def ps_update_probe(lib, L, torch, stream, n_params: int, opt: str, peaks: dict)
             "peak_source": peaks["source"]}
 
 
-def run_graft(a) -> dict:
-    import torch
-    import torch.distributed as dist
-    from k8s_b200 import lib as L
+def parity_check(a, n, rank, local, math, torch, dist, stream) -> dict:
+    """N > 1, before any timing: three synchronous steps of a small job (16 examples per replica) over
+    the real peers.  Step-1 mean loss and the accumulated update after step 3 against the oracle's
+    sync_step on the same batches (rank 0; the oracle is the checker here, nothing of it is timed),
+    and whether every rank ends with bit-identical parameters (crc32 of the flat buffer, all-gathered)."""
+    import zlib
+    from k8s_b200.syncps import SyncPSJob, mnist_init, synthetic_batch
+    pb = 16
+    job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
+    job.build_mnist(pb, math=math, layout=a.layout)
+    job.optimizer(a.opt, LR, 0.9)
+    job.connect_peers(dist)
+    losses = []
+    for step in range(3):
+        xs, ys = zip(*[synthetic_batch(r, pb, step) for r in job.local_replicas])
+        losses.append(job.step(list(xs), list(ys)))
+    mine = np.concatenate([job.get_var(v) for v in range(8)])
+    crcs = [None] * n
+    dist.all_gather_object(crcs, zlib.crc32(mine.tobytes()))
+    out = {"layout": a.layout, "math": math, "batch_per_replica": pb, "steps": 3,
+           "ranks_bit_identical": all(c == crcs[0] for c in crcs), "loss_step1": losses[0]}
+    if rank == 0:
+        from oracle import model_ref as M
+        params = mnist_init(0)
+        init = np.concatenate([p.ravel() for p in params])
+        accum = [np.zeros_like(p) for p in params]
+        ref_losses = []
+        for step in range(3):
+            batches = [synthetic_batch(r, pb, step) for r in range(n)]
+            ref_losses.append(M.sync_step(params, accum, batches, a.opt, LR, 0.9, math=math)[0])
+        ref = np.concatenate([p.ravel() for p in params])
+        upd = float(np.linalg.norm((mine - init) - (ref - init)) / np.linalg.norm(ref - init))
+        fp32_like = math in ("fp32", "tf32x3")
+        out.update(oracle_loss_step1=ref_losses[0], loss_rel_err_step1=abs(losses[0] - ref_losses[0]) / abs(ref_losses[0]),
+                   update_rel_l2_after_3_steps=upd, update_tolerance=3e-3 if fp32_like else 0.15,
+                   loss_tolerance=1e-5 if fp32_like else 5e-3)
+        out["ok"] = bool(out["ranks_bit_identical"] and upd <= out["update_tolerance"] and
+                         out["loss_rel_err_step1"] <= out["loss_tolerance"])
+    job.close()
+    dist.barrier()
+    return out
+
+
+def measure(a, model: str, n: int, rank: int, local: int, lib, L, torch, dist, stream, peaks, steps: int) -> dict:
+    """Build `model`'s job on this rank, time `steps` device-resident steps and `steps` end-to-end steps
+    (max over ranks), then the per-kernel profile; returns the JSON line's body for that model."""
     from k8s_b200.syncps import SyncPSJob, synthetic_batch, synthetic_images
-
-    n = a.gpus
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != n:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torchrun --nproc-per-node %d" % (n, world, n))
-    lib = L.load()
-    if lib.device_count_checked() <= local:
-        raise SystemExit("no CUDA device %d: the CUDA path has no CPU fallback" % local)
-    torch.cuda.set_device(local)
-    if n > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    stream = torch.cuda.Stream()
-    peaks = measured_peaks()
-
-    resnet = a.model == "resnet50"
-    math = a.math
-    job = None
+    resnet = model == "resnet50"
+    B = a.batch if model == a.model else (256 if resnet else BATCH)
+    math = "bf16" if resnet else ("tf32x3" if a.math == "auto" else a.math)
+    job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
     if resnet:
-        job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
-        job.build_resnet50(a.batch, a.image, a.classes, layout=a.layout)
-        math = "bf16"
-    for cand in ([] if resnet else ["tf32x3"] if math == "auto" else [math]):
-        job = SyncPSJob(tf_config_for_rank(n, rank), rank, n, cuda_device=local, stream=stream.cuda_stream)
-        try:
-            job.build_mnist(a.batch, math=cand, layout=a.layout)
-            math = cand
-            break
-        except L.TfgError as e:
-            job.close()
-            job = None
-            if math != "auto" or "not built yet" not in e.message:
-                raise
+        job.build_resnet50(B, a.image, a.classes, layout=a.layout)
+    else:
+        job.build_mnist(B, math=math, layout=a.layout)
     job.optimizer(a.opt, LR, 0.9)
     job.connect_peers(dist if n > 1 else None)
     slots = job.local_replicas
-    B = a.batch
 
     # synthetic inputs: resident in HBM for `value`, in pinned host memory for `e2e`
     host, dev = [], []
@@ -452,12 +497,12 @@ def run_graft(a) -> dict:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, k_steps):
         """K steps, each bracketed by events on the job's stream, L2 flushed (untimed) in
         between; returns the summed device time in ms, max over ranks."""
         evs = []
         barrier()
-        for k in range(steps):
+        for k in range(k_steps):
             with torch.cuda.stream(stream):
                 flush.fill_(k & 0xFF)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -502,7 +547,6 @@ def run_graft(a) -> dict:
     # replayed after).  Capturing is set-up work (tens of ms of host time for the 560-launch ResNet
     # step, which at N > 1 the other ranks would spend inside their barrier kernel): it is done
     # here, before the W warm-up steps, so warm-up and timed steps are all graph replays.
-    # set-up, not warm-up: every resident input set is stepped twice so that its graph exists
     for k in range(2 * N_INPUT_SETS):
         step_dev(k)
     job.sync()
@@ -511,82 +555,120 @@ def run_graft(a) -> dict:
         step_dev(k)
     job.sync()
     launches0 = job.launches
-    ms_dev = timed(step_dev, a.steps)
+    ms_dev = timed(step_dev, steps)
     launches_timed = job.launches - launches0
     if a.exchange == "nccl":
         ms_e2e = float("nan")      # the baseline arm is timed device-resident only
     else:
-        for k in range(3):
+        for k in range(2 * N_INPUT_SETS + 3):      # the host-buffer path stages into its own buffers: its own graph
             step_e2e(k)
-        ms_e2e = timed(step_e2e, a.steps)
+        ms_e2e = timed(step_e2e, steps)
     clocks = sampler.stop()
 
     # per-kernel device time over another K steps (events behind every launch)
     job.profile(True)
-    for k in range(a.steps):
+    for k in range(steps):
         step_dev(k)
     prof = job.profile_report()
     job.profile(False)
-    examples = a.steps * B * n
-    value = examples / (ms_dev * 1e-3)
-    e2e = examples / (ms_e2e * 1e-3)
+    examples = steps * B * n
+    unit = "images/s" if resnet else "examples/s"
     out = {
         "metric": "images/sec sync-PS step (ResNet-50)" if resnet else "examples/sec sync-PS step",
-        "value": value, "unit": "images/s" if resnet else "examples/s", "n_gpus": n,
-        "steps": a.steps, "warmup": warm, "ms_per_step": ms_dev / a.steps,
+        "value": examples / (ms_dev * 1e-3), "unit": unit, "n_gpus": n,
+        "steps": steps, "warmup": warm, "ms_per_step": ms_dev / steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         # tf32x3 = fp32 operands, three tf32 MMAs per product, fp32 accumulate: fp32-equivalent results (held
         # to the fp32 parity bounds in tests/test_gpu_model.py), hence "f32" like the reference arm
         "dtype": {"fp32": "f32", "tf32x3": "f32", "bf16": "bf16", "tf32": "tf32"}[math], "data": "synthetic",
-        "config": config_dict(a, n, math),
-        "e2e": {"value": e2e, "unit": "images/s" if resnet else "examples/s", "ms_per_step": ms_e2e / a.steps,
+        "config": config_dict(a, n, math, model, B),
+        "e2e": {"value": examples / (ms_e2e * 1e-3), "unit": unit, "ms_per_step": ms_e2e / steps,
                 "h2d_bytes_per_step": n * B * ((a.image * a.image * 3 if resnet else 784) * 4 + 4),
                 "d2h_bytes_per_step": 4 * n, "last_loss": losses[-1] if losses else None},
         "gpu_launches": int(launches_timed),
-        "math_impl": {"tf32x3": "3xTF32 split products on tcgen05 (a_lo*b + a*b_lo + a*b, fp32 accumulate in TMEM): "
-                                "fp32-equivalent, parity-tested at the fp32 bounds",
-                      "fp32": "CUDA-core FFMA", "bf16": "tcgen05 kind::f16, bf16 operands, fp32 accumulate",
-                      "tf32": "tcgen05 kind::tf32, one MMA per product"}[math],
+        "math_impl": MATH_IMPL[math],
         "clocks": clocks,
     }
     if rank == 0:
         total = sum(v["ms"] for v in prof.values()) or 1.0
-        top = max(prof, key=lambda k_: prof[k_]["ms"])
-        bound, amount = algorithmic_work(top, B, 3274634, a.opt, n, math, peaks)
+        # the cross-rank barrier is waiting time (the slowest rank's skew), not work: it is reported as its
+        # share of the step, and the roofline kernel is the largest one that moves bytes or does math
+        work = {k_: v for k_, v in prof.items() if k_ != "barrier_kernel"} or prof
+        top = max(work, key=lambda k_: work[k_]["ms"])
+        bound, amount, peak_note = algorithmic_work(top, B, 3274634, a.opt, n, math, peaks)
         per_launch_ms = prof[top]["ms"] / prof[top]["count"]
         if resnet:   # per-layer launches share a name: work = the sum over the 53 convolutions, per step
             bound, amount = resnet_work(top, B, a.image, a.classes)
-            per_launch_ms = prof[top]["ms"] / a.steps
+            peak_note = None
+            per_launch_ms = prof[top]["ms"] / steps
         roof = {"kernel": top, "bound": bound, "share_of_step": prof[top]["ms"] / total,
-                "ms_per_launch": per_launch_ms, "traffic": (measured_traffic("resnet50" if resnet else "mnist", top)
+                "ms_per_launch": per_launch_ms, "traffic": (measured_traffic(model, top)
                             if n == 1 and B == (256 if resnet else 128) else None),   # captured at these sizes only
                 "peak_source": peaks["source"]}
         if amount is not None and bound == "tensor":
             ach = amount / (per_launch_ms * 1e-3) / 1e12
-            roof.update(achieved=ach, peak=peaks["bf16_tflops_sustained"], unit="TFLOP/s",
-                        frac=ach / peaks["bf16_tflops_sustained"], algorithmic_flops=amount)
+            peak = peaks["bf16_tflops_sustained"] / (6.0 if peak_note else 1.0)
+            roof.update(achieved=ach, peak=peak, unit="TFLOP/s", frac=ach / peak, algorithmic_flops=amount)
+            if peak_note:
+                roof["peak_source"] = peaks["source"] + "; " + peak_note
         elif amount is not None:
             ach = amount / (per_launch_ms * 1e-3) / 1e9
             roof.update(achieved=ach, peak=peaks["hbm_gbs"], unit="GB/s", frac=ach / peaks["hbm_gbs"],
                         algorithmic_bytes=amount)
+        if "barrier_kernel" in prof:
+            roof["barrier_share_of_step"] = prof["barrier_kernel"]["ms"] / total
         out["roofline"] = roof
         out["kernels"] = {k_: {"count": v["count"], "ms_per_launch": v["ms"] / v["count"],
                                "share": v["ms"] / total} for k_, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
     job.close()
-    del dev, flush
+    del dev, flush, host
     torch.cuda.empty_cache()
+    return out
+
+
+def run_graft(a) -> dict:
+    import torch
+    import torch.distributed as dist
+    from k8s_b200 import lib as L
+
+    n = a.gpus
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != n:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torchrun --nproc-per-node %d" % (n, world, n))
+    lib = L.load()
+    if lib.device_count_checked() <= local:
+        raise SystemExit("no CUDA device %d: the CUDA path has no CPU fallback" % local)
+    torch.cuda.set_device(local)
+    if n > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stream = torch.cuda.Stream()
+    peaks = measured_peaks()
+
+    parity = None
+    if n > 1 and a.model == "mnist" and a.exchange == "peer":
+        parity = parity_check(a, n, rank, local, "tf32x3" if a.math == "auto" else a.math, torch, dist, stream)
+    out = measure(a, a.model, n, rank, local, lib, L, torch, dist, stream, peaks, a.steps)
+    if parity is not None:
+        out["parity"] = parity
+    # BASELINE config 4 rides along on the default line so that the driver's clock covers it too
+    if a.model == "mnist" and a.with_resnet and a.exchange == "peer":
+        r = measure(a, "resnet50", n, rank, local, lib, L, torch, dist, stream, peaks, min(a.steps, 10))
+        out["resnet50"] = {k: r[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "dtype", "config",
+                                             "e2e", "gpu_launches", "clocks", "roofline") if k in r}
     if rank == 0:
         out["ps_update"] = ps_update_probe(lib, L, torch, stream, a.ps_params, a.opt, peaks)
         if n == 1 and not a.no_cpu_baseline:
-            if resnet:
+            if a.model == "resnet50":
                 v, ms, cores = cpu_resnet_rate(a, 8, 2)
                 out["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
                                        "sample": "2 forward+backward passes of 8 images (oracle/resnet_ref.py, fp32)"}
             else:
-                v, ms, cores = cpu_step_rate(1, B, a.opt, 250, 3)
+                v, ms, cores = cpu_step_rate(1, a.batch, a.opt, 250, 3)
                 out["cpu_baseline"] = {"value": v, "unit": "examples/s", "cores": cores, "kind": "port",
                                        "sample": "250 full steps of 1 replica x %d examples (oracle port, "
-                                                 "torch-CPU fwd/bwd + C apply)" % B}
+                                                 "torch-CPU fwd/bwd + C apply)" % a.batch}
     if n > 1:
         dist.barrier()
         dist.destroy_process_group()

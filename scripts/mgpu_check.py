@@ -1,7 +1,7 @@
 """Multi-GPU parity check, one process per GPU (run under torchrun on an N-GPU box):
 N replicas + N PS shards of the MNIST CNN for 3 synchronous steps through the peer-memory
 push/apply/pull kernel; every rank's parameters must be bit-identical across ranks and match
-the oracle's step (fp32 math: max-norm 2e-4 of scale on the accumulated update)."""
+the oracle's step (fp32 and tf32x3 math: relative L2 1e-3 per step on the accumulated update)."""
 import json
 import os
 import sys
@@ -22,7 +22,7 @@ def main():
 
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     layout = sys.argv[1] if len(sys.argv) > 1 else "balanced"
-    math = sys.argv[2] if len(sys.argv) > 2 else "fp32"
+    math = sys.argv[2] if len(sys.argv) > 2 else "tf32x3"
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     batch = 16
@@ -45,7 +45,7 @@ def main():
         ref = np.concatenate([p.ravel() for p in params])
         ini = np.concatenate([p.ravel() for p in init])
         upd_err = np.linalg.norm((mine - ini) - (ref - ini)) / np.linalg.norm(ref - ini)
-        tol = 1e-3 if math == "fp32" else 5e-2
+        tol = 1e-3 if math in ("fp32", "tf32x3") else 5e-2
         good = same and upd_err <= tol * (step + 1) and abs(loss - loss_ref) <= 5e-3 * abs(loss_ref)
         ok = ok and good
         if rank == 0:
