@@ -149,6 +149,19 @@ int tfg_job_buffer(tfg_job* job, int which, int slot, void** dev_out, size_t* by
 int tfg_opt_config(tfg_job* job, int kind, float lr, float momentum);
 int64_t tfg_global_step(const tfg_job* job);
 
+/* ---- checkpoint of the sharded variables (SURVEY.md par. 8f row 3) -------------------
+ * The reference's operator keeps no training state (its only resume hook is "setup is skipped
+ * if Phase != None", pkg/trainer/training.go:252-257); TF 1.3's Saver would write the PS
+ * variables.  Here a GPU rank reads / writes raw ranges of the flat fp32 space: the element
+ * ranges whose update it applies (tfg_owned_ranges: offsets / counts of up to `cap` ranges,
+ * *n_out = how many there are), parameters or optimizer slots (which = TFG_BUF_PARAMS /
+ * TFG_BUF_ACCUM).  A write to the parameters also refreshes the operand-precision shadow.
+ * k8s_b200/checkpoint.py builds the file format (one flat file per shard + placement table). */
+int tfg_owned_ranges(const tfg_job* job, int64_t* offsets_out, int64_t* counts_out, int cap, int* n_out);
+int tfg_flat_read(tfg_job* job, int which, int64_t offset, int64_t count, void* host);
+int tfg_flat_write(tfg_job* job, int which, int64_t offset, int64_t count, const void* host);
+int tfg_global_step_set(tfg_job* job, int64_t step);
+
 /* ---- cross-rank peer mapping (one process per GPU) ---------------------------------
  * Each rank exports CUDA IPC handles of its buffers; the host exchanges the blobs
  * (torch.distributed all_gather) and every rank opens every peer's.  Replaces the

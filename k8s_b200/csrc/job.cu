@@ -512,6 +512,56 @@ int tfg_opt_config(tfg_job* j, int kind, float lr, float momentum) {
 
 int64_t tfg_global_step(const tfg_job* j) { return j ? j->global_step : -1; }
 
+// ---- raw access to the flat space (checkpoint of the sharded variables) ---------------------
+int tfg_global_step_set(tfg_job* j, int64_t step) {
+  if (!j || step < 0) return fail(j, TFG_EINVAL, "bad argument");
+  j->global_step = step;
+  return TFG_OK;
+}
+
+int tfg_owned_ranges(const tfg_job* j, int64_t* offsets_out, int64_t* counts_out, int cap, int* n_out) {
+  if (!j || !n_out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  if (!j->finalized) return fail(nullptr, TFG_ESTATE, "variables are not finalized");
+  *n_out = (int)j->segs.size();
+  if (cap < (int)j->segs.size()) return (offsets_out || counts_out) ? fail(nullptr, TFG_ELIMIT, "range arrays too small") : TFG_OK;
+  for (size_t i = 0; i < j->segs.size(); ++i) {
+    if (offsets_out) offsets_out[i] = j->segs[i].off;
+    if (counts_out) counts_out[i] = j->segs[i].cnt;
+  }
+  return TFG_OK;
+}
+
+static int flat_io(tfg_job* j, int which, int64_t offset, int64_t count, void* host_out, const void* host_in) {
+  if (!j) return fail(nullptr, TFG_EINVAL, "job is NULL");
+  if (!j->finalized) return fail(j, TFG_ESTATE, "variables are not finalized");
+  if (which != TFG_BUF_PARAMS && which != TFG_BUF_ACCUM) return fail(j, TFG_EINVAL, "flat access takes TFG_BUF_PARAMS or TFG_BUF_ACCUM");
+  if (offset < 0 || count < 0 || offset + count > j->flat_count) return fail(j, TFG_EINVAL, "range outside the flat space");
+  if (count == 0) return TFG_OK;
+  if (!host_out && !host_in) return fail(j, TFG_EINVAL, "NULL host buffer");
+  float* base = which == TFG_BUF_PARAMS ? j->params : j->accum;
+  TFG_CUDA(j, cudaSetDevice(j->device));
+  const size_t bytes = sizeof(float) * (size_t)count;
+  if (host_in) {
+    TFG_CUDA(j, cudaMemcpyAsync(base + offset, host_in, bytes, cudaMemcpyHostToDevice, j->stream));
+    if (which == TFG_BUF_PARAMS && j->params_lp) {   // keep the operand-precision shadow current
+      const size_t es = j->lp_mode == 2 ? 4 : 2;
+      if (launch_cast_lp(j->params + offset, static_cast<char*>(j->params_lp) + es * offset, count, j->lp_mode, j->stream))
+        return fail(j, TFG_ECUDA, "parameter shadow cast failed");
+    }
+  } else {
+    TFG_CUDA(j, cudaMemcpyAsync(host_out, base + offset, bytes, cudaMemcpyDeviceToHost, j->stream));
+  }
+  TFG_CUDA(j, cudaStreamSynchronize(j->stream));
+  return TFG_OK;
+}
+
+int tfg_flat_read(tfg_job* j, int which, int64_t offset, int64_t count, void* host) {
+  return flat_io(j, which, offset, count, host, nullptr);
+}
+int tfg_flat_write(tfg_job* j, int which, int64_t offset, int64_t count, const void* host) {
+  return flat_io(j, which, offset, count, nullptr, host);
+}
+
 // ---- peer mapping --------------------------------------------------------------------
 // blob = [n_local_replicas:int32][global replica ids...] then handles in the order
 // params, loss, flags, grads[slot]...

@@ -10,6 +10,7 @@ to block in, so ``main`` resolves which GPU owns task ``task_id`` and returns.
 from __future__ import annotations
 
 import argparse
+import os
 import sys
 from collections import OrderedDict
 from typing import Dict, List
@@ -69,6 +70,9 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--verbose", type="bool", nargs="?", const=True, default=False)
     parser.add_argument("--n_gpus", type=int, default=0,
                         help="GPUs of this box (0 = ask the driver); not a reference flag")
+    parser.add_argument("--join", action="store_true",
+                        help="block like server.join() (grpc_tensorflow_server.py:115) until the launcher's "
+                             "rendezvous reports the job finished; not a reference flag")
     return parser
 
 
@@ -87,7 +91,16 @@ def main(argv=None) -> int:
     rm = RankMap(cluster_lists(cluster), n_gpus)
     gpu = rm.gpu_of(flags.job_name, flags.task_id)
     print("/job:%s/task:%d -> shard owner on GPU rank %d of %d"
-          % (flags.job_name, flags.task_id, gpu, n_gpus))
+          % (flags.job_name, flags.task_id, gpu, n_gpus), flush=True)
+    if flags.join:
+        # server.join(): the shard itself lives in the tfg_job of GPU rank `gpu`'s host process; this
+        # process stays up, like the reference's PS pod, until the job is over
+        from . import rendezvous
+        if rendezvous.ENV in os.environ:
+            return rendezvous.Client(0, 1).wait_done()
+        import time
+        while True:
+            time.sleep(3600)
     return 0
 
 

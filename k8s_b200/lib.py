@@ -83,6 +83,10 @@ _SIGS = {
     "tfg_job_buffer": (C.c_int, [_p, C.c_int, C.c_int, C.POINTER(_p), C.POINTER(C.c_size_t)]),
     "tfg_opt_config": (C.c_int, [_p, C.c_int, C.c_float, C.c_float]),
     "tfg_global_step": (C.c_int64, [_p]),
+    "tfg_global_step_set": (C.c_int, [_p, C.c_int64]),
+    "tfg_owned_ranges": (C.c_int, [_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_int)]),
+    "tfg_flat_read": (C.c_int, [_p, C.c_int, C.c_int64, C.c_int64, _p]),
+    "tfg_flat_write": (C.c_int, [_p, C.c_int, C.c_int64, C.c_int64, _p]),
     "tfg_job_ipc_export": (C.c_int, [_p, _p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "tfg_job_ipc_open": (C.c_int, [_p, C.c_int, _p, C.c_size_t]),
     "tfg_job_attach_local_peer": (C.c_int, [_p, C.c_int, _p]),

@@ -185,6 +185,28 @@ class SyncPSJob:
     def global_step(self) -> int:
         return self.lib.global_step(self.h)
 
+    @global_step.setter
+    def global_step(self, step: int) -> None:
+        self._ck(self.lib.global_step_set(self.h, int(step)))
+
+    # -- raw flat-space access (checkpoints) -------------------------------------------------
+    def owned_ranges(self):
+        """[(offset, count)] of the flat-space ranges whose update this GPU rank applies."""
+        n = C.c_int()
+        self._ck(self.lib.owned_ranges(self.h, None, None, 0, C.byref(n)))
+        offs, cnts = (C.c_int64 * max(1, n.value))(), (C.c_int64 * max(1, n.value))()
+        self._ck(self.lib.owned_ranges(self.h, offs, cnts, n.value, C.byref(n)))
+        return [(offs[i], cnts[i]) for i in range(n.value)]
+
+    def flat_read(self, which: int, offset: int, count: int) -> np.ndarray:
+        out = np.empty(count, dtype=np.float32)
+        self._ck(self.lib.flat_read(self.h, which, offset, count, out.ctypes.data))
+        return out
+
+    def flat_write(self, which: int, offset: int, values: np.ndarray) -> None:
+        a = np.ascontiguousarray(values, dtype=np.float32)
+        self._ck(self.lib.flat_write(self.h, which, offset, a.size, a.ctypes.data))
+
     # -- model + step ----------------------------------------------------------------------
     def build_mnist(self, batch_per_replica: int = 128, math: str = "fp32",
                     layout: str = "logical", seed: Optional[int] = 0) -> None:
