@@ -18,6 +18,7 @@ import (
 	"encoding/json"
 	"errors"
 	"fmt"
+	"runtime"
 	"strings"
 	"unsafe"
 )
@@ -70,7 +71,8 @@ func (s *TFReplicaSet) CreateOnGpuRanks(index int32, rank int, nGpus int) (*GpuR
 // BuildMnist registers the variables of the tf_sample CNN under round-robin placement over the
 // job's PS tasks and allocates them (balanced = the physical layout that spreads bytes evenly).
 func (r *GpuRank) BuildMnist(batchPerReplica int, balanced bool) error {
-	if rc := C.tfg_model_mnist_cnn(r.job, C.int(batchPerReplica), C.TFG_MATH_BF16); rc != C.TFG_OK {
+	// TFG_MATH_TF32X3: the fp32 model on the tensor cores (3xTF32 split products), held to the fp32 bounds
+	if rc := C.tfg_model_mnist_cnn(r.job, C.int(batchPerReplica), C.TFG_MATH_TF32X3); rc != C.TFG_OK {
 		return lastError(r.job, rc)
 	}
 	layout := C.int(0)
@@ -83,6 +85,38 @@ func (r *GpuRank) BuildMnist(batchPerReplica int, balanced bool) error {
 	return nil
 }
 
+// Optimizer selects SGD (0), momentum (1) or Nesterov momentum (2) and its constants; it may be called
+// between steps (a learning-rate schedule).
+func (r *GpuRank) Optimizer(kind int, lr float32, momentum float32) error {
+	if rc := C.tfg_opt_config(r.job, C.int(kind), C.float(lr), C.float(momentum)); rc != C.TFG_OK {
+		return lastError(r.job, rc)
+	}
+	return nil
+}
+
+// ExportPeerHandles returns this rank's CUDA-IPC blob.  With nGpus > 1 every rank must hand its blob
+// to every other rank (the launcher's rendezvous does the exchange) and call ConnectPeer for each
+// before the first Step; without it Step fails with TFG_ESTATE ("GPU rank g is not mapped").
+func (r *GpuRank) ExportPeerHandles() ([]byte, error) {
+	buf := make([]byte, 8+4*C.TFG_MAX_REPLICAS+C.TFG_IPC_HANDLE_BYTES*(4+C.TFG_MAX_REPLICAS))
+	var n C.size_t
+	if rc := C.tfg_job_ipc_export(r.job, unsafe.Pointer(&buf[0]), C.size_t(len(buf)), &n); rc != C.TFG_OK {
+		return nil, lastError(r.job, rc)
+	}
+	return buf[:int(n)], nil
+}
+
+// ConnectPeer maps the buffers of GPU rank `peer` (its blob from ExportPeerHandles) into this rank.
+func (r *GpuRank) ConnectPeer(peer int, blob []byte) error {
+	if len(blob) == 0 {
+		return errors.New("empty peer blob")
+	}
+	if rc := C.tfg_job_ipc_open(r.job, C.int(peer), unsafe.Pointer(&blob[0]), C.size_t(len(blob))); rc != C.TFG_OK {
+		return lastError(r.job, rc)
+	}
+	return nil
+}
+
 // Step runs one synchronous step for the replicas this rank hosts: images[i] / labels[i] are the
 // host batches of local replica i.  Returns the mean loss over all replicas of the job.
 func (r *GpuRank) Step(images [][]float32, labels [][]int32) (float32, error) {
@@ -90,12 +124,21 @@ func (r *GpuRank) Step(images [][]float32, labels [][]int32) (float32, error) {
 		return 0, errors.New("one image batch and one label batch per local replica")
 	}
 	n := len(images)
-	// the C side reads the arrays of pointers during the call only; C memory keeps cgo's pointer rules
+	// cgo's pointer-passing rules: a Go pointer may be stored in C memory only while the Go object is
+	// pinned.  The batches are pinned for the duration of the call (runtime.Pinner, Go 1.21+), the two
+	// arrays of pointers live in C memory, and the C side keeps nothing after it returns.
+	var pin runtime.Pinner
+	defer pin.Unpin()
 	ip := (*[1 << 20]*C.float)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
 	lp := (*[1 << 20]*C.int32_t)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
 	defer C.free(unsafe.Pointer(ip))
 	defer C.free(unsafe.Pointer(lp))
 	for i := 0; i < n; i++ {
+		if len(images[i]) == 0 || len(labels[i]) == 0 {
+			return 0, errors.New("empty batch")
+		}
+		pin.Pin(&images[i][0])
+		pin.Pin(&labels[i][0])
 		ip[i] = (*C.float)(unsafe.Pointer(&images[i][0]))
 		lp[i] = (*C.int32_t)(unsafe.Pointer(&labels[i][0]))
 	}
