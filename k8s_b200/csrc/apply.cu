@@ -4,6 +4,7 @@
 // HBM-bound.  Algorithmic bytes per parameter on the owner: 4*n_grads read (remote over
 // NVLink when n_gpus > 1) + 4 read var (+4 accum) + 4 written per pull destination
 // (+4 accum).  Single GPU, SGD: 12 B/param; momentum: 20 B/param.
+#include <algorithm>
 #include <type_traits>
 
 #include <cuda_bf16.h>
@@ -14,7 +15,13 @@
 namespace tfg {
 
 constexpr int kApplyThreads = 256;
-constexpr int kChunk = 4096;            // elements per work chunk = 4 float4 per thread
+constexpr int kChunkBig = 4096;         // elements per work chunk: 4 float4 per thread (large shards: bytes in flight)
+constexpr int kChunkSmall = 1024;       // 1 float4 per thread (small shards: enough CTAs to cover the chip)
+// replicas whose gradients are requested before the first add.  Large shards (VEC = 4) already keep
+// four 16-byte loads per thread and four CTAs per SM in flight -- 10 MB chip-wide, several times
+// what NVLink's latency x bandwidth needs -- and a second group costs a CTA of occupancy (measured:
+// 0.97 -> 0.88 of HBM peak on one GPU); small shards (VEC = 1) take eight.
+template <int VEC> constexpr int load_group() { return VEC == 4 ? 1 : 8; }
 
 struct ApplyArgs {
   const float* grads[TFG_MAX_REPLICAS];
@@ -32,6 +39,12 @@ struct ApplyArgs {
   int n_grads, n_pull, n_lp, n_loss, kind;
   long long n_chunks;
   float divisor, lr, mu;
+  // Cross-rank synchronisation folded into the kernel (sync != 0, n_ranks > 1), see push_apply_pull_kernel
+  int sync, me, n_ranks;
+  uint32_t* flags[TFG_MAX_GPUS];     // every rank's flag block (own one local, others peer-mapped): kFlagsReady / kFlagsPulled rows
+  uint32_t* epoch;                   // device-resident step counter of this rank: a captured launch replays correctly
+  unsigned int* done;                // CTAs of this launch that have finished their stores
+  int* err_out;                      // error word to set when a peer does not show up
 };
 
 __device__ __forceinline__ float4 ld_stream(const float* p) {
@@ -56,19 +69,69 @@ __device__ __forceinline__ void update1(float g, float& v, float& a, float lr, f
   }
 }
 
-template <int KIND>
-__global__ void __launch_bounds__(kApplyThreads)
+// wait until every other rank has stored an epoch >= `epoch` into this rank's row `row` of the flag
+// block; false after 20 s (a peer rank died: fail, do not hang)
+__device__ __forceinline__ bool wait_peers(const ApplyArgs& a, int row, uint32_t epoch, int t) {
+  bool ok = true;
+  if (t < a.n_ranks && t != a.me) {
+    const uint32_t* f = a.flags[a.me] + row * TFG_MAX_GPUS + t;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      uint32_t seen;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+      if ((int32_t)(seen - epoch) >= 0) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 20ull * 1000 * 1000 * 1000) { ok = false; break; }
+      __nanosleep(100);
+    }
+  }
+  return ok;
+}
+__device__ __forceinline__ void signal_peers(const ApplyArgs& a, int row, uint32_t epoch, int t) {
+  if (t < a.n_ranks && t != a.me)
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.flags[t] + row * TFG_MAX_GPUS + a.me), "r"(epoch) : "memory");
+}
+
+// The whole exchange of one step in ONE launch per rank.  With a.sync the two cross-rank barriers
+// that used to bracket it as launches of their own are part of the kernel:
+//   1. CTA 0 tells every peer "my gradients (and my forward's reads of the parameters) are done"
+//      (release store of the step's epoch into the peer's `ready` row), and every CTA waits until all
+//      peers have said so before it loads a remote gradient or overwrites a remote parameter;
+//   2. the CTA that finishes last tells every peer "my stores into your parameter buffer have landed"
+//      and waits for the same word from every peer before the kernel ends, so the next forward on
+//      this stream reads complete parameters.
+// VEC = float4 per thread and chunk (4: large shards, bytes in flight; 1: small shards, more CTAs).
+template <int KIND, int VEC, bool SYNC>
+__global__ void __launch_bounds__(kApplyThreads, SYNC ? 3 : 1)
 push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
-  // a peer rank is gone (the barrier in front of this launch gave up): its gradients are stale, so
-  // no parameter may change; the host reports TFG_EPEER when it reads the error word
-  if (a.err && *reinterpret_cast<const volatile int*>(a.err) != 0) return;
+  constexpr int kChunk = VEC * 4 * kApplyThreads;
+  constexpr int kLoadGroup = load_group<VEC>();
+  constexpr bool sync = SYNC;
+  uint32_t epoch = 0;
+  if (sync) {
+    __shared__ int peers_ok;
+    epoch = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1;   // advanced by the last CTA, after every CTA has read it
+    if (threadIdx.x == 0) peers_ok = 1;
+    __syncthreads();
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      signal_peers(a, kFlagsReady, epoch, threadIdx.x);
+    }
+    if (!wait_peers(a, kFlagsReady, epoch, threadIdx.x)) { peers_ok = 0; atomicExch(a.err_out, 1); }
+    __syncthreads();
+    // a peer rank is gone: its gradients are stale, so no parameter may change; the host reports
+    // TFG_EPEER when it reads the error word
+    if (!peers_ok) return;
+  } else if (a.err && *reinterpret_cast<const volatile int*>(a.err) != 0) {
+    return;   // the barrier launched in front of this kernel gave up
+  }
   // mean loss over replicas, replica order (the step's scalar result)
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.n_loss > 0) {
     float s = a.loss_src[0][0];
     for (int r = 1; r < a.n_loss; ++r) s = __fadd_rn(s, a.loss_src[r][0]);
     a.loss_dst[0] = __fdiv_rn(s, (float)a.n_loss);
   }
-  constexpr int kVecPerThread = kChunk / 4 / kApplyThreads;  // 4
   for (long long c = blockIdx.x; c < a.n_chunks; c += gridDim.x) {
     Segment sg = a.seg0;
     if (a.segs) {  // few segments: binary search on the first chunk index
@@ -81,35 +144,66 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
     }
     const long long base = sg.off + (c - sg.chunk0) * (long long)kChunk;
     const long long end = sg.off + sg.cnt;
-    float4 g[kVecPerThread];
-    long long idx[kVecPerThread];
+    float4 g[VEC];
+    long long idx[VEC];
 #pragma unroll
-    for (int u = 0; u < kVecPerThread; ++u) {
+    for (int u = 0; u < VEC; ++u) {
       idx[u] = base + 4ll * (threadIdx.x + u * kApplyThreads);
       g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (idx[u] < end) g[u] = ld_stream(a.grads[0] + idx[u]);
     }
-    for (int r = 1; r < a.n_grads; ++r) {
-      float4 t[kVecPerThread];
+    // the replicas' gradients kLoadGroup at a time: all loads of a group are in flight before the first
+    // add (remote loads are NVLink round trips), and the sum still runs in replica order
+    if constexpr (kLoadGroup == 1) {
 #pragma unroll
-      for (int u = 0; u < kVecPerThread; ++u)
-        if (idx[u] < end) t[u] = ld_stream(a.grads[r] + idx[u]);
+      for (int u = 0; u < VEC; ++u)
+        if (idx[u] < end) g[u] = ld_stream(a.grads[0] + idx[u]);
+      for (int r = 1; r < a.n_grads; ++r) {
+        float4 t[VEC];
 #pragma unroll
-      for (int u = 0; u < kVecPerThread; ++u)
-        if (idx[u] < end) {
-          g[u].x = __fadd_rn(g[u].x, t[u].x); g[u].y = __fadd_rn(g[u].y, t[u].y);
-          g[u].z = __fadd_rn(g[u].z, t[u].z); g[u].w = __fadd_rn(g[u].w, t[u].w);
-        }
+        for (int u = 0; u < VEC; ++u)
+          if (idx[u] < end) t[u] = ld_stream(a.grads[r] + idx[u]);
+#pragma unroll
+        for (int u = 0; u < VEC; ++u)
+          if (idx[u] < end) {
+            g[u].x = __fadd_rn(g[u].x, t[u].x); g[u].y = __fadd_rn(g[u].y, t[u].y);
+            g[u].z = __fadd_rn(g[u].z, t[u].z); g[u].w = __fadd_rn(g[u].w, t[u].w);
+          }
+      }
+    } else {
+      for (int r0 = 0; r0 < a.n_grads; r0 += kLoadGroup) {
+        float4 t[kLoadGroup][VEC];
+  #pragma unroll
+        for (int rr = 0; rr < kLoadGroup; ++rr)
+          if (r0 + rr < a.n_grads) {
+  #pragma unroll
+            for (int u = 0; u < VEC; ++u)
+              if (idx[u] < end) t[rr][u] = ld_stream(a.grads[r0 + rr] + idx[u]);
+          }
+  #pragma unroll
+        for (int rr = 0; rr < kLoadGroup; ++rr)
+          if (r0 + rr < a.n_grads) {
+  #pragma unroll
+            for (int u = 0; u < VEC; ++u)
+              if (idx[u] < end) {
+                if (r0 + rr == 0) {
+                  g[u] = t[rr][u];
+                } else {
+                  g[u].x = __fadd_rn(g[u].x, t[rr][u].x); g[u].y = __fadd_rn(g[u].y, t[rr][u].y);
+                  g[u].z = __fadd_rn(g[u].z, t[rr][u].z); g[u].w = __fadd_rn(g[u].w, t[rr][u].w);
+                }
+              }
+          }
+      }
     }
-    float4 v[kVecPerThread], m[kVecPerThread];
+    float4 v[VEC], m[VEC];
 #pragma unroll
-    for (int u = 0; u < kVecPerThread; ++u)
+    for (int u = 0; u < VEC; ++u)
       if (idx[u] < end) {
         v[u] = *reinterpret_cast<const float4*>(a.var + idx[u]);
         if (KIND != TFG_OPT_SGD) m[u] = *reinterpret_cast<const float4*>(a.accum + idx[u]);
       }
 #pragma unroll
-    for (int u = 0; u < kVecPerThread; ++u)
+    for (int u = 0; u < VEC; ++u)
       if (idx[u] < end) {
         float4 gg = g[u];
         gg.x = __fdiv_rn(gg.x, a.divisor); gg.y = __fdiv_rn(gg.y, a.divisor);
@@ -132,6 +226,20 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
           for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<float4*>(static_cast<float*>(a.lp[p]) + idx[u]) = lo;
         }
       }
+  }
+  if (sync) {
+    __shared__ int last;
+    __threadfence_system();            // this thread's peer stores, before the ticket
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(a.done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last) {                        // every CTA's stores are out: tell the peers, wait for theirs
+      __threadfence_system();
+      signal_peers(a, kFlagsPulled, epoch, threadIdx.x);
+      if (!wait_peers(a, kFlagsPulled, epoch, threadIdx.x)) atomicExch(a.err_out, 1);
+      __syncthreads();
+      if (threadIdx.x == 0) { *a.done = 0u; *a.epoch = epoch; }
+    }
   }
 }
 
@@ -157,6 +265,24 @@ static int grid_for(long long n_chunks) {
   return (int)(g < 1 ? 1 : g);
 }
 
+template <int KIND, int VEC>
+static void launch_apply_kv(int grid, cudaStream_t s, const ApplyArgs& a) {
+  if (a.sync) push_apply_pull_kernel<KIND, VEC, true><<<grid, kApplyThreads, 0, s>>>(a);
+  else push_apply_pull_kernel<KIND, VEC, false><<<grid, kApplyThreads, 0, s>>>(a);
+}
+
+static cudaError_t launch_apply(int kind, int vec, int grid, cudaStream_t s, const ApplyArgs& a) {
+  switch (kind * 2 + (vec == 4 ? 1 : 0)) {
+    case TFG_OPT_SGD * 2: launch_apply_kv<TFG_OPT_SGD, 1>(grid, s, a); break;
+    case TFG_OPT_SGD * 2 + 1: launch_apply_kv<TFG_OPT_SGD, 4>(grid, s, a); break;
+    case TFG_OPT_MOMENTUM * 2: launch_apply_kv<TFG_OPT_MOMENTUM, 1>(grid, s, a); break;
+    case TFG_OPT_MOMENTUM * 2 + 1: launch_apply_kv<TFG_OPT_MOMENTUM, 4>(grid, s, a); break;
+    case TFG_OPT_NESTEROV * 2: launch_apply_kv<TFG_OPT_NESTEROV, 1>(grid, s, a); break;
+    default: launch_apply_kv<TFG_OPT_NESTEROV, 4>(grid, s, a); break;
+  }
+  return cudaGetLastError();
+}
+
 template <typename K>
 static cudaError_t launch_kind(int kind, K&& f) {
   switch (kind) {
@@ -167,7 +293,7 @@ static cudaError_t launch_kind(int kind, K&& f) {
   return cudaGetLastError();
 }
 
-int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole) {
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole, bool sync) {
   ApplyArgs a = {};
   if (summed_local) {
     a.grads[0] = j->grads[0];
@@ -197,21 +323,30 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole) {
   a.segs = j->d_segs;
   a.n_segs = (int)j->segs.size();
   a.n_chunks = j->n_chunks;
+  int vec = j->chunk_elems == kChunkBig ? 4 : 1;
   if (whole) {   // every rank applies the whole flat space (the all-reduce baseline)
     a.segs = nullptr;
     a.seg0 = Segment{0, j->flat_count, 0};
     a.n_segs = 1;
-    a.n_chunks = (j->flat_count + kChunk - 1) / kChunk;
+    vec = 4;
+    a.n_chunks = (j->flat_count + kChunkBig - 1) / kChunkBig;
   }
   a.kind = j->opt_kind;
   a.lr = j->lr;
   a.mu = j->mu;
-  if (a.n_segs == 0 && a.n_loss == 0) return TFG_OK;  // this rank owns nothing
+  a.sync = sync && j->n_gpus > 1 && !summed_local;
+  if (a.sync) {
+    a.me = j->gpu_rank;
+    a.n_ranks = j->n_gpus;
+    for (int g = 0; g < j->n_gpus; ++g) a.flags[g] = j->peer_flags[g];
+    a.epoch = j->dev_epoch + 1;
+    a.done = reinterpret_cast<unsigned int*>(j->dev_epoch + 2);
+    a.err_out = j->dev_err;
+  }
+  if (a.n_segs == 0 && a.n_loss == 0 && !a.sync) return TFG_OK;  // this rank owns nothing and has nobody to wait for
+  if (a.n_segs == 0) a.n_chunks = 0;
   int grid = grid_for(a.n_chunks);
-  cudaStream_t s = j->stream;
-  cudaError_t e = launch_kind(j->opt_kind, [&](auto k) {
-    push_apply_pull_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(a);
-  });
+  cudaError_t e = launch_apply(j->opt_kind, vec, grid, j->stream, a);
   prof_mark(j, "push_apply_pull_kernel");
   if (e != cudaSuccess) return fail_cuda(j, e, "push_apply_pull_kernel");
   return TFG_OK;
@@ -247,11 +382,11 @@ int launch_dense_apply(int kind, float* var, float* accum, const float* const* g
     a.segs = nullptr;
     a.seg0 = Segment{0, vec_count, 0};
     a.n_segs = 1;
-    a.n_chunks = (vec_count + kChunk - 1) / kChunk;
+    const int vec = vec_count >= (long long)kChunkBig * 2 * kNumSMs ? 4 : 1;
+    const int chunk = vec == 4 ? kChunkBig : kChunkSmall;
+    a.n_chunks = (vec_count + chunk - 1) / chunk;
     int grid = grid_for(a.n_chunks);
-    e = launch_kind(kind, [&](auto k) {
-      push_apply_pull_kernel<decltype(k)::value><<<grid, kApplyThreads, 0, s>>>(a);
-    });
+    e = launch_apply(kind, vec, grid, s, a);
     if (e != cudaSuccess) return fail_cuda(nullptr, e, "push_apply_pull_kernel");
   }
   if (vec_count < count) {

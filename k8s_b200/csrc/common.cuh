@@ -13,6 +13,9 @@ namespace tfg {
 
 constexpr int kPadFloats = 32;          // every variable starts on a 128-B boundary
 constexpr int kNumSMs = 148;            // B200
+// rows of a rank's flag block (each TFG_MAX_GPUS words, written by the peers): the standalone barrier,
+// and the two synchronisation points folded into the push/apply/pull kernel
+constexpr int kFlagsBarrier = 0, kFlagsReady = 1, kFlagsPulled = 2, kFlagRows = 3;
 
 void set_thread_error(const std::string& s);
 const char* thread_error();
@@ -53,6 +56,7 @@ struct tfg_job {
   int64_t flat_count = 0;
   std::vector<tfg::Segment> segs;
   int64_t n_chunks = 0;
+  int chunk_elems = 4096;              // elements per work chunk of the apply kernel (1024 for small shards)
   // device state
   int device = 0;
   bool bound = false, own_stream = false;
@@ -75,7 +79,8 @@ struct tfg_job {
   uint32_t* peer_flags[TFG_MAX_GPUS] = {};
   float* peer_grads[TFG_MAX_REPLICAS] = {};
   std::vector<void*> ipc_opened;
-  uint32_t* dev_epoch = nullptr;       // barrier epoch counter, advanced by the barrier kernel itself
+  uint32_t* dev_epoch = nullptr;       // [0] barrier epoch (advanced by the barrier kernel), [1] epoch and [2] finished-CTA
+                                       // counter of the push/apply/pull kernel
   // optimizer
   int opt_kind = TFG_OPT_SGD;
   float lr = 0.01f, mu = 0.9f;
@@ -128,7 +133,7 @@ cudaStream_t side_fork(tfg_job* j);
 void side_join(tfg_job* j);
 
 // apply.cu
-int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole = false);
+int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole = false, bool sync = false);
 int launch_barrier(tfg_job* j);
 int launch_dense_apply(int kind, float* var, float* accum, const float* const* grads, int n_grads,
                        float divisor, int64_t count, float lr, float mu, float* const* pull,

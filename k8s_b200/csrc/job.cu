@@ -78,17 +78,16 @@ static int ensure_bound(tfg_job* j) {
   return tfg_job_bind(j, j->gpu_rank, nullptr) == TFG_OK ? TFG_OK : TFG_ECUDA;
 }
 
-static void build_segments(tfg_job* j) {
-  j->segs.clear();
-  constexpr int64_t kChunk = 4096;  // elements per work chunk of the apply kernel
-  int64_t chunk = 0;
+// owned ranges of this rank inside [lo, hi) of the flat space, cut into work chunks
+static std::vector<Segment> segments_in(tfg_job* j, int64_t lo_lim, int64_t hi_lim, int64_t kChunk, int64_t* n_chunks) {
+  std::vector<Segment> segs;
   auto add = [&](int64_t off, int64_t cnt) {
-    if (cnt <= 0) return;
-    if (!j->segs.empty() && j->segs.back().off + j->segs.back().cnt == off &&
-        (j->segs.back().cnt % kChunk) == 0) {
-      j->segs.back().cnt += cnt;  // merge only when chunk boundaries stay aligned
+    const int64_t lo = std::max(off, lo_lim), hi = std::min(off + cnt, hi_lim);
+    if (hi <= lo) return;
+    if (!segs.empty() && segs.back().off + segs.back().cnt == lo && (segs.back().cnt % kChunk) == 0) {
+      segs.back().cnt += hi - lo;  // merge only when chunk boundaries stay aligned
     } else {
-      j->segs.push_back({off, cnt, 0});
+      segs.push_back({lo, hi - lo, 0});
     }
   };
   if (j->layout == TFG_LAYOUT_BALANCED) {
@@ -103,11 +102,28 @@ static void build_segments(tfg_job* j) {
       if (owner == j->gpu_rank) add(v.offset, v.padded);
     }
   }
-  for (auto& s : j->segs) {
-    s.chunk0 = chunk;
-    chunk += (s.cnt + kChunk - 1) / kChunk;
+  int64_t chunk = 0;
+  for (auto& sg : segs) {
+    sg.chunk0 = chunk;
+    chunk += (sg.cnt + kChunk - 1) / kChunk;
   }
-  j->n_chunks = chunk;
+  *n_chunks = chunk;
+  return segs;
+}
+
+static void build_segments(tfg_job* j) {
+  // elements per work chunk of the apply kernel: small shards take small chunks so that the kernel
+  // still has a few CTAs per SM (the MNIST model on 8 ranks: 409 k parameters per rank)
+  int64_t owned = 0;
+  if (j->layout == TFG_LAYOUT_BALANCED) {
+    owned = (j->flat_count + j->n_gpus - 1) / j->n_gpus;
+  } else {
+    for (auto& v : j->vars)
+      if (v.offset >= 0 && (v.ps_task < 0 ? 0 : v.ps_task % j->n_gpus) == j->gpu_rank) owned += v.padded;
+  }
+  const int64_t kChunk = owned >= 4096ll * 2 * kNumSMs ? 4096 : 1024;
+  j->chunk_elems = (int)kChunk;
+  j->segs = segments_in(j, 0, j->flat_count, kChunk, &j->n_chunks);
 }
 
 }  // namespace tfg
@@ -232,10 +248,10 @@ int tfg_job_bind(tfg_job* j, int cuda_device, void* stream) {
   TFG_CUDA(j, cudaMalloc(&j->loss, sizeof(float) * (TFG_MAX_REPLICAS + 2)));
   TFG_CUDA(j, cudaMemset(j->loss, 0, sizeof(float) * (TFG_MAX_REPLICAS + 2)));
   j->dev_err = reinterpret_cast<int*>(j->loss + TFG_MAX_REPLICAS + 1);
-  TFG_CUDA(j, cudaMalloc(&j->flags, sizeof(uint32_t) * TFG_MAX_GPUS));
-  TFG_CUDA(j, cudaMemset(j->flags, 0, sizeof(uint32_t) * TFG_MAX_GPUS));
-  TFG_CUDA(j, cudaMalloc(&j->dev_epoch, sizeof(uint32_t)));
-  TFG_CUDA(j, cudaMemset(j->dev_epoch, 0, sizeof(uint32_t)));
+  TFG_CUDA(j, cudaMalloc(&j->flags, sizeof(uint32_t) * TFG_MAX_GPUS * kFlagRows));
+  TFG_CUDA(j, cudaMemset(j->flags, 0, sizeof(uint32_t) * TFG_MAX_GPUS * kFlagRows));
+  TFG_CUDA(j, cudaMalloc(&j->dev_epoch, sizeof(uint32_t) * 4));
+  TFG_CUDA(j, cudaMemset(j->dev_epoch, 0, sizeof(uint32_t) * 4));
   if (const char* g = getenv("TFGRAFT_GRAPH")) j->use_graphs = atoi(g) != 0;
   TFG_CUDA(j, cudaMallocHost(&j->h_loss, sizeof(float) * (TFG_MAX_REPLICAS + 2)));   // same layout, pinned
   j->h_err = reinterpret_cast<int*>(j->h_loss + TFG_MAX_REPLICAS + 1);
@@ -480,7 +496,7 @@ int tfg_job_buffer(tfg_job* j, int which, int slot, void** dev_out, size_t* byte
       if (slot < 0 || slot >= (int)j->grads.size()) return fail(j, TFG_EINVAL, "bad replica slot");
       p = j->grads[slot]; b = flat; break;
     case TFG_BUF_LOSS: p = j->loss; b = sizeof(float) * (TFG_MAX_REPLICAS + 1); break;
-    case TFG_BUF_FLAGS: p = j->flags; b = sizeof(uint32_t) * TFG_MAX_GPUS; break;
+    case TFG_BUF_FLAGS: p = j->flags; b = sizeof(uint32_t) * TFG_MAX_GPUS * kFlagRows; break;
     default: return fail(j, TFG_EINVAL, "unknown buffer");
   }
   if (!p) return fail(j, TFG_ESTATE, "buffer is not allocated yet");
@@ -682,9 +698,8 @@ int tfg_push_apply_pull(tfg_job* j, int with_barriers) {
   int rc = check_peers(j);
   if (rc) return rc;
   TFG_CUDA(j, cudaSetDevice(j->device));
-  if (with_barriers && j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
-  if ((rc = launch_job_apply(j, false, j->n_replicas))) return rc;
-  if (with_barriers && j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
+  // with_barriers: the two cross-rank synchronisation points are part of the kernel itself
+  if ((rc = launch_job_apply(j, false, j->n_replicas, false, with_barriers != 0))) return rc;
   j->global_step += 1;
   return TFG_OK;
 }
@@ -784,16 +799,14 @@ int tfg_logits_get(tfg_job* j, int slot, float* host, size_t bytes) {
   return j->resnet ? resnet_logits(j, slot, host, bytes) : mnist_logits(j, slot, host, bytes);
 }
 
-// Device work of one step: forward/backward of every hosted replica, then barrier, fused
-// push+apply+pull, barrier.  Pure stream work with fixed pointers, hence capturable.
+// Device work of one step: forward/backward of every hosted replica, then the fused push + apply +
+// pull kernel, which also carries both cross-rank synchronisation points.  Pure stream work with
+// fixed pointers, hence capturable.
 static int step_device_work(tfg_job* j, const float* const* images, const int32_t* const* labels) {
   int rc;
   for (size_t s = 0; s < j->grads.size(); ++s)
     if ((rc = model_fb(j, (int)s, images[s], labels[s]))) return rc;
-  if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
-  if ((rc = launch_job_apply(j, false, j->n_replicas))) return rc;
-  if (j->n_gpus > 1 && (rc = launch_barrier(j))) return rc;
-  return TFG_OK;
+  return launch_job_apply(j, false, j->n_replicas, false, true);   // the cross-rank synchronisation is inside the kernel
 }
 
 // Runs the step eagerly the first time a set of input pointers is seen (this also performs
