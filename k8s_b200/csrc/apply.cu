@@ -5,6 +5,8 @@
 // NVLink when n_gpus > 1) + 4 read var (+4 accum) + 4 written per pull destination
 // (+4 accum).  Single GPU, SGD: 12 B/param; momentum: 20 B/param.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <type_traits>
 
 #include <cuda_bf16.h>
@@ -243,6 +245,173 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
   }
 }
 
+// ---- the same exchange with the operands streamed through shared memory by the bulk-copy engine ------
+// Multi-GPU ranks.  Register loads from a peer's memory are NVLink round trips that a thread can keep
+// only a few of in flight (measured, 2 ranks, 256 M parameters: 0.43 of the link).  Here a producer
+// warp requests, per 1024-element chunk, one 4-KB bulk copy (cp.async.bulk, the TMA unit's linear mode)
+// per replica gradient -- local or peer memory alike -- plus the owner's parameter and slot values, into
+// a ring of shared-memory stages that complete on mbarriers; up to ~200 KB per SM are in flight however
+// long the link's latency is.  The 256 consumer threads read their float4 of every array from the
+// stage, sum the replicas in replica order, apply the optimizer (update1: no FMA contraction, identical
+// bits to the register kernel) and store the new values to the local and peer buffers.
+constexpr int kTmaChunk = 1024;                       // elements per chunk and array
+constexpr int kTmaThreads = kApplyThreads + 32;       // consumers + the producer warp
+constexpr int kTmaSmemBudget = 200 * 1024;
+
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+}
+
+template <int KIND, bool SYNC>
+__global__ void __launch_bounds__(kTmaThreads, 1)
+push_apply_pull_tma_kernel(const __grid_constant__ ApplyArgs a, int stages) {
+  extern __shared__ __align__(128) uint8_t smem_dyn[];
+  const int n_arr = a.n_grads + 1 + (KIND != TFG_OPT_SGD ? 1 : 0);   // gradients, var, (accum)
+  const int stage_floats = n_arr * kTmaChunk;
+  float* ring = reinterpret_cast<float*>(smem_dyn);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_dyn + static_cast<size_t>(stages) * stage_floats * 4);
+  uint64_t* empty = full + stages;
+  const int t = threadIdx.x;
+  uint32_t epoch = 0;
+  if (t == 0) {
+    for (int s = 0; s < stages; ++s) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], kApplyThreads / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (SYNC) {
+    __shared__ int peers_ok;
+    epoch = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1;
+    if (t == 0) peers_ok = 1;
+    __syncthreads();
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      signal_peers(a, kFlagsReady, epoch, t);
+    }
+    if (!wait_peers(a, kFlagsReady, epoch, t)) { peers_ok = 0; atomicExch(a.err_out, 1); }
+    __syncthreads();
+    if (!peers_ok) return;
+  } else {
+    __syncthreads();
+    if (a.err && *reinterpret_cast<const volatile int*>(a.err) != 0) return;
+  }
+  if (blockIdx.x == 0 && t == 0 && a.n_loss > 0) {
+    float s = a.loss_src[0][0];
+    for (int r = 1; r < a.n_loss; ++r) s = __fadd_rn(s, a.loss_src[r][0]);
+    a.loss_dst[0] = __fdiv_rn(s, (float)a.n_loss);
+  }
+  auto chunk_range = [&](long long c, long long* base, long long* end) {
+    Segment sg = a.seg0;
+    if (a.segs) {
+      int lo = 0, hi = a.n_segs - 1;
+      while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (a.segs[mid].chunk0 <= c) lo = mid; else hi = mid - 1;
+      }
+      sg = a.segs[lo];
+    }
+    *base = sg.off + (c - sg.chunk0) * (long long)kTmaChunk;
+    *end = sg.off + sg.cnt;
+  };
+  if (t >= kApplyThreads) {
+    // ===== producer warp: one lane requests the chunk's arrays =====
+    if (t == kApplyThreads) {
+      uint32_t it = 0;
+      for (long long c = blockIdx.x; c < a.n_chunks; c += gridDim.x, ++it) {
+        const int s = it % stages;
+        tc::mbar_wait(&empty[s], ((it / stages) & 1) ^ 1);
+        long long base, end;
+        chunk_range(c, &base, &end);
+        const uint32_t bytes = static_cast<uint32_t>(min((long long)kTmaChunk, end - base)) * 4u;
+        tc::mbar_expect_tx(&full[s], bytes * n_arr);
+        float* dst = ring + static_cast<size_t>(s) * stage_floats;
+        for (int r = 0; r < a.n_grads; ++r) bulk_load(dst + r * kTmaChunk, a.grads[r] + base, bytes, &full[s]);
+        bulk_load(dst + a.n_grads * kTmaChunk, a.var + base, bytes, &full[s]);
+        if (KIND != TFG_OPT_SGD) bulk_load(dst + (a.n_grads + 1) * kTmaChunk, a.accum + base, bytes, &full[s]);
+      }
+    }
+  } else {
+    // ===== consumers =====
+    uint32_t it = 0;
+    for (long long c = blockIdx.x; c < a.n_chunks; c += gridDim.x, ++it) {
+      const int s = it % stages;
+      long long base, end;
+      chunk_range(c, &base, &end);
+      tc::mbar_wait(&full[s], (it / stages) & 1);
+      const long long idx = base + 4ll * t;
+      const float* src = ring + static_cast<size_t>(s) * stage_floats + 4 * t;
+      if (idx < end) {
+        float4 g = *reinterpret_cast<const float4*>(src);
+        for (int r = 1; r < a.n_grads; ++r) {
+          const float4 x = *reinterpret_cast<const float4*>(src + r * kTmaChunk);
+          g.x = __fadd_rn(g.x, x.x); g.y = __fadd_rn(g.y, x.y); g.z = __fadd_rn(g.z, x.z); g.w = __fadd_rn(g.w, x.w);
+        }
+        float4 v = *reinterpret_cast<const float4*>(src + a.n_grads * kTmaChunk);
+        float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (KIND != TFG_OPT_SGD) m = *reinterpret_cast<const float4*>(src + (a.n_grads + 1) * kTmaChunk);
+        g.x = __fdiv_rn(g.x, a.divisor); g.y = __fdiv_rn(g.y, a.divisor);
+        g.z = __fdiv_rn(g.z, a.divisor); g.w = __fdiv_rn(g.w, a.divisor);
+        update1<KIND>(g.x, v.x, m.x, a.lr, a.mu);
+        update1<KIND>(g.y, v.y, m.y, a.lr, a.mu);
+        update1<KIND>(g.z, v.z, m.z, a.lr, a.mu);
+        update1<KIND>(g.w, v.w, m.w, a.lr, a.mu);
+        if (KIND != TFG_OPT_SGD) *reinterpret_cast<float4*>(a.accum + idx) = m;
+        *reinterpret_cast<float4*>(a.var + idx) = v;
+        for (int p = 0; p < a.n_pull; ++p) *reinterpret_cast<float4*>(a.pull[p] + idx) = v;
+        if (a.n_lp > 0 && a.lp_mode == 1) {
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(a.lp[p]) + idx) = pk;
+        } else if (a.n_lp > 0) {
+          const float4 lo = make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w));
+          for (int p = 0; p < a.n_lp; ++p) *reinterpret_cast<float4*>(static_cast<float*>(a.lp[p]) + idx) = lo;
+        }
+      }
+      __syncwarp();
+      if ((t & 31) == 0) tc::mbar_arrive(&empty[s]);      // this warp has read its part of the stage
+    }
+  }
+  if (SYNC) {
+    __shared__ int last;
+    __threadfence_system();
+    __syncthreads();
+    if (t == 0) last = atomicAdd(a.done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last) {
+      __threadfence_system();
+      signal_peers(a, kFlagsPulled, epoch, t);
+      if (!wait_peers(a, kFlagsPulled, epoch, t)) atomicExch(a.err_out, 1);
+      __syncthreads();
+      if (t == 0) { *a.done = 0u; *a.epoch = epoch; }
+    }
+  }
+}
+
+// ring depth that fits the budget for this many arrays per stage; < 2 = use the register kernel
+static int tma_stages(int n_arr) { return std::min(8, kTmaSmemBudget / (n_arr * kTmaChunk * 4)); }
+
+template <int KIND>
+static cudaError_t launch_apply_tma_k(int grid, size_t smem, int stages, cudaStream_t s, const ApplyArgs& a) {
+  static bool attr[2] = {false, false};
+  const int sy = a.sync ? 1 : 0;
+  if (!attr[sy]) {
+    cudaError_t e = a.sync ? cudaFuncSetAttribute(push_apply_pull_tma_kernel<KIND, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBudget + 256)
+                           : cudaFuncSetAttribute(push_apply_pull_tma_kernel<KIND, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBudget + 256);
+    if (e != cudaSuccess) return e;
+    attr[sy] = true;
+  }
+  if (a.sync) push_apply_pull_tma_kernel<KIND, true><<<grid, kTmaThreads, smem, s>>>(a, stages);
+  else push_apply_pull_tma_kernel<KIND, false><<<grid, kTmaThreads, smem, s>>>(a, stages);
+  return cudaGetLastError();
+}
+
+static cudaError_t launch_apply_tma(int kind, int grid, size_t smem, int stages, cudaStream_t s, const ApplyArgs& a) {
+  if (kind == TFG_OPT_SGD) return launch_apply_tma_k<TFG_OPT_SGD>(grid, smem, stages, s, a);
+  if (kind == TFG_OPT_MOMENTUM) return launch_apply_tma_k<TFG_OPT_MOMENTUM>(grid, smem, stages, s, a);
+  return launch_apply_tma_k<TFG_OPT_NESTEROV>(grid, smem, stages, s, a);
+}
+
 // scalar path for caller buffers whose length or alignment rules out float4
 template <int KIND>
 __global__ void __launch_bounds__(kApplyThreads)
@@ -345,8 +514,24 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole, bo
   }
   if (a.n_segs == 0 && a.n_loss == 0 && !a.sync) return TFG_OK;  // this rank owns nothing and has nobody to wait for
   if (a.n_segs == 0) a.n_chunks = 0;
-  int grid = grid_for(a.n_chunks);
-  cudaError_t e = launch_apply(j->opt_kind, vec, grid, j->stream, a);
+  // ranks of a multi-GPU job stream their operands through shared memory (bulk copies); the segment
+  // table is cut into 1024-element chunks for it
+  const int n_arr = a.n_grads + 1 + (j->opt_kind != TFG_OPT_SGD ? 1 : 0);
+  const int stages = tma_stages(n_arr);
+  cudaError_t e;
+  static int use_tma = -1;
+  if (use_tma < 0) {
+    use_tma = 1;
+    if (const char* e = getenv("TFGRAFT_EXCHANGE")) use_tma = strcmp(e, "reg") != 0;
+  }
+  if (use_tma && j->n_gpus > 1 && !summed_local && !whole && j->chunk_elems == kTmaChunk && stages >= 2) {
+    const size_t smem = (size_t)stages * n_arr * kTmaChunk * 4 + 2 * stages * sizeof(uint64_t);
+    const int per_sm = std::max(1, (int)((227 * 1024) / (smem + 1024)));
+    const int grid = (int)std::max<long long>(1, std::min<long long>(a.n_chunks, (long long)kNumSMs * per_sm));
+    e = launch_apply_tma(j->opt_kind, grid, smem, stages, j->stream, a);
+  } else {
+    e = launch_apply(j->opt_kind, vec, grid_for(a.n_chunks), j->stream, a);
+  }
   prof_mark(j, "push_apply_pull_kernel");
   if (e != cudaSuccess) return fail_cuda(j, e, "push_apply_pull_kernel");
   return TFG_OK;

@@ -121,7 +121,9 @@ static void build_segments(tfg_job* j) {
     for (auto& v : j->vars)
       if (v.offset >= 0 && (v.ps_task < 0 ? 0 : v.ps_task % j->n_gpus) == j->gpu_rank) owned += v.padded;
   }
-  const int64_t kChunk = owned >= 4096ll * 2 * kNumSMs ? 4096 : 1024;
+  // multi-GPU ranks always use 1024-element chunks: their exchange kernel streams 4-KB pieces through
+  // shared memory (apply.cu, push_apply_pull_tma_kernel)
+  const int64_t kChunk = (owned >= 4096ll * 2 * kNumSMs && j->n_gpus == 1) ? 4096 : 1024;
   j->chunk_elems = (int)kChunk;
   j->segs = segments_in(j, 0, j->flat_count, kChunk, &j->n_chunks);
 }

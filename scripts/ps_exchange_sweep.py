@@ -149,7 +149,7 @@ def main():
                         stream.synchronize()
                     ms = timed(fn)    # nccl arm: the in-place reduce-scatter re-sums its own output; values drift, timing does not
                     bpp = 12 if opt == "sgd" else 20
-                    link_bytes = 4.0 * max_owned * (world - 1)
+                    link_bytes = 4.0 * max_owned * (world - 1) + 4.0 * (n - max_owned)
                     row = {"what": "ps_exchange", "n_gpus": world, "arm": arm, "params": n, "shards": S, "layout": layout,
                            "optimizer": opt, "ms": ms, "owned_max": max_owned,
                            "hbm_gbs": bpp * max_owned / (ms * 1e-3) / 1e9 if world == 1 else (4.0 * world + bpp - 4) * max_owned / (ms * 1e-3) / 1e9,
