@@ -230,6 +230,36 @@ int tfg_sparse_scatter_sub(float* table_dev, int64_t vocab, int dim, int n_shard
                            const float* rows_dev, float scale,
                            void* scratch_dev, size_t scratch_bytes, void* stream);
 
+/* The sparse path across the GPU ranks of a box (SURVEY.md par. 8e).  Shard k of a table is owned by
+ * the GPU of PS task k (tfg_ps_gpu).  With every rank's buffers mapped into every other rank
+ * (tfg_ipc_export / tfg_ipc_open) neither direction needs a collective:
+ *   - pull: a worker fetches the rows of ALL its ids in one launch, each straight from its owner's
+ *     shard (table_shards_dev: host array of n_shards device pointers, own shards local, others peer);
+ *   - push + apply: the owner of a shard applies [TF1.3] scatter_sub over the concatenation of all
+ *     n_sources replicas' batches (source after source, n_per_source ids each), reading the ids and the
+ *     update rows in place from the replicas' buffers (host arrays of device pointers).  Duplicates are
+ *     applied in (source, position) order, so the result is bit-identical to the sequential loop over
+ *     the concatenated batch.  scratch: tfg_sparse_scratch_bytes(n_sources * n_per_source).
+ * Replaces: embedding_lookup's per-shard gathers over gRPC and the IndexedSlices push to each PS
+ * (hosted by grpc_tensorflow_server.py:112-115). */
+int tfg_sparse_gather_multi(const float* const* table_shards_dev, int64_t vocab, int dim, int n_shards,
+                            int strategy, const int64_t* ids_dev, int64_t n, float* out_dev, int* bad_dev,
+                            void* stream);
+int tfg_sparse_scatter_sub_multi(float* table_dev, int64_t vocab, int dim, int n_shards, int shard,
+                                 int strategy, const int64_t* const* ids_devs, const float* const* rows_devs,
+                                 int n_sources, int64_t n_per_source, float scale, void* scratch_dev,
+                                 size_t scratch_bytes, void* stream);
+/* CUDA-IPC handle (TFG_IPC_HANDLE_BYTES) of a caller-owned buffer, and its mapping in another process
+ * of the same box; replaces the per-task Service DNS names (pkg/trainer/replicas.go:157-186) for
+ * buffers the job does not own itself.  dev_ptr must be the START of a cudaMalloc allocation (a handle
+ * names the whole allocation): tfg_dev_alloc / tfg_dev_free give such buffers (zero-filled) to hosts
+ * whose own allocator sub-allocates. */
+int tfg_dev_alloc(size_t bytes, void** dev_ptr_out);
+int tfg_dev_free(void* dev_ptr);
+int tfg_ipc_export(const void* dev_ptr, void* handle_out);
+int tfg_ipc_open(const void* handle, void** dev_ptr_out);
+int tfg_ipc_close(void* dev_ptr);
+
 /* Scatter-sub for callers that cannot allocate device memory.  No counterpart in the
  * reference: this entry point exists only for this library's users.
  *

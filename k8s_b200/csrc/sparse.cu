@@ -8,9 +8,31 @@
 // then one warp per distinct row walks its run in position order, keeping the row in
 // registers: table[row] = fl(table[row] - fl(scale * rows[i])) for each i in turn, which
 // is what a sequential CPU loop over i computes ([TF1.3] scatter_sub on the CPU).
+#include <cstring>
+
 #include "common.cuh"
 
 namespace tfg {
+
+// Where the ids and the update rows of a (possibly multi-source) batch live.  A batch is the
+// concatenation of n_src equally long pieces, source after source -- on several GPUs the pieces are the
+// replicas' own buffers, read in place through peer mappings (position p of the batch is element
+// p % per of source p / per).  per == 0: one source, position = index.
+struct IdSrc {
+  const long long* base[TFG_MAX_REPLICAS];
+  long long per;
+  __device__ __forceinline__ long long at(long long i) const { return per == 0 ? base[0][i] : base[i / per][i % per]; }
+};
+struct RowSrc {
+  const float* base[TFG_MAX_REPLICAS];
+  uint32_t per;
+  __device__ __forceinline__ const float* at(uint32_t v, int dim) const {
+    return per == 0 ? base[0] + (long long)v * dim : base[v / per] + (long long)(v % per) * dim;
+  }
+};
+struct TableSrc {               // the shards of one table: shard k's rows start at base[k] (local or peer memory)
+  const float* base[TFG_MAX_REPLICAS];
+};
 
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
@@ -86,13 +108,40 @@ gather_kernel(const float* __restrict__ table, Part pt, const long long* __restr
   }
 }
 
+// the same with every shard of the table addressable from this GPU (own shards local, the others
+// peer-mapped): a worker fetches the rows of all its ids in one launch, straight from their owners
+__global__ void __launch_bounds__(256)
+gather_multi_kernel(const __grid_constant__ TableSrc tables, Part pt, const long long* __restrict__ ids,
+                    long long n, int dim, float* __restrict__ out, int* bad) {
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long i = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+    long long id = ids[i];
+    if (id < 0 || id >= pt.vocab) {
+      if (lane == 0 && bad) atomicAdd(bad, 1);
+      continue;
+    }
+    int sh;
+    long long row;
+    locate(pt, id, &sh, &row);
+    const float* src = tables.base[sh] + row * (long long)dim;
+    float* dst = out + i * (long long)dim;
+    if ((dim & 3) == 0) {
+      for (int c = lane * 4; c < dim; c += 128)
+        *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+    } else {
+      for (int c = lane; c < dim; c += 32) dst[c] = src[c];
+    }
+  }
+}
+
 // ---- stable radix sort of (row key, position) ------------------------------------------
 __global__ void __launch_bounds__(256)
-make_keys_kernel(Part pt, const long long* __restrict__ ids, long long n, uint32_t sentinel,
+make_keys_kernel(Part pt, const __grid_constant__ IdSrc ids, long long n, uint32_t sentinel,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x) {
-    long long id = ids[i];
+    long long id = ids.at(i);
     uint32_t k = sentinel;
     if (id >= 0 && id < pt.vocab) {
       int sh;
@@ -212,7 +261,7 @@ template <int VEC>
 __global__ void __launch_bounds__(256)
 scatter_sub_runs_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
                         const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
-                        const float* __restrict__ rows, float scale) {
+                        const __grid_constant__ RowSrc rows, float scale) {
   const int lane = threadIdx.x & 31;
   const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
   for (long long p = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
@@ -233,7 +282,7 @@ scatter_sub_runs_kernel(float* __restrict__ table, int dim, const uint32_t* __re
         }
       }
       for (long long q = p; q < n && keys[q] == k; ++q) {
-        const float* g = rows + (long long)vals[q] * dim;
+        const float* g = rows.at(vals[q], dim);
         if (c < dim) {
           float gv[VEC];
           if (VEC == 4) {
@@ -298,7 +347,7 @@ template <int VEC>
 __global__ void __launch_bounds__(256)
 scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
                          const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
-                         const float* __restrict__ rows, float scale, LongRun* __restrict__ runs,
+                         const __grid_constant__ RowSrc rows, float scale, LongRun* __restrict__ runs,
                          ChunkDesc* __restrict__ chunks, uint32_t* __restrict__ counters) {
   const int lane = threadIdx.x & 31;
   const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
@@ -322,7 +371,7 @@ scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __r
         float acc[VEC], gv[VEC];
         if (c < dim) load_vec<VEC>(trow + c, acc);
         for (long long q = p; q < p + len; ++q) {
-          const float* g = rows + (long long)vals[q] * dim;
+          const float* g = rows.at(vals[q], dim);
           if (c < dim) {
             load_vec<VEC>(g + c, gv);
 #pragma unroll
@@ -359,7 +408,7 @@ scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __r
 
 template <int VEC>
 __global__ void __launch_bounds__(256)
-long_chunk_sum_kernel(int dim, const uint32_t* __restrict__ vals, const float* __restrict__ rows, float scale,
+long_chunk_sum_kernel(int dim, const uint32_t* __restrict__ vals, const __grid_constant__ RowSrc rows, float scale,
                       const ChunkDesc* __restrict__ chunks, const uint32_t* __restrict__ counters,
                       float* __restrict__ carry) {
   const int lane = threadIdx.x & 31;
@@ -376,7 +425,7 @@ long_chunk_sum_kernel(int dim, const uint32_t* __restrict__ vals, const float* _
         float gv[8][VEC];
 #pragma unroll
         for (int t = 0; t < 8; ++t)
-          if (i0 + t < d.len && c < dim) load_vec<VEC>(rows + (long long)vals[d.pos + i0 + t] * dim + c, gv[t]);
+          if (i0 + t < d.len && c < dim) load_vec<VEC>(rows.at(vals[d.pos + i0 + t], dim) + c, gv[t]);
 #pragma unroll
         for (int t = 0; t < 8; ++t)
           if (i0 + t < d.len && c < dim) {
@@ -486,14 +535,14 @@ size_t tfg_sparse_scratch_bytes_fast(int64_t n, int dim) {
   return tfg_sparse_scratch_bytes(n) + long_run_extra_bytes(n, dim, nullptr, nullptr);
 }
 
-int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
-                           const int64_t* ids, int64_t n, const float* rows, float scale,
-                           void* scratch, size_t scratch_bytes, void* stream) {
+static int scatter_sub_impl(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
+                            const IdSrc& ids, int64_t n, const RowSrc& rows, float scale,
+                            void* scratch, size_t scratch_bytes, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   int rc = check_sparse(vocab, dim, n_shards, shard, strategy, n);
   if (rc) return rc;
   if (n == 0) return TFG_OK;
-  if (!table || !ids || !rows || !scratch) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  if (!table || !scratch) return fail(nullptr, TFG_EINVAL, "NULL argument");
   if (n >= (1ll << 31)) return fail(nullptr, TFG_ELIMIT, "more than 2^31-1 ids in one call");
   if (scratch_bytes < tfg_sparse_scratch_bytes(n)) return fail(nullptr, TFG_EINVAL, "scratch too small");
   if ((uintptr_t)scratch % 256 != 0) return fail(nullptr, TFG_EINVAL, "scratch must be 256-B aligned");
@@ -509,7 +558,7 @@ int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, i
   uint32_t* hist = (uint32_t*)(base + 4 * arr);
   int kb = (int)((n + 255) / 256);
   if (kb > kNumSMs * 16) kb = kNumSMs * 16;
-  make_keys_kernel<<<kb, 256, 0, s>>>(pt, (const long long*)ids, n, sentinel, keys[0], vals[0]);
+  make_keys_kernel<<<kb, 256, 0, s>>>(pt, ids, n, sentinel, keys[0], vals[0]);
   int cur = 0;
   const int passes = (bits_for(sentinel) + 7) / 8;
   for (int p = 0; p < passes; ++p) {
@@ -554,6 +603,100 @@ int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, i
                                                            rows, scale);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(nullptr, e, "sparse scatter_sub kernels");
+  return TFG_OK;
+}
+
+int tfg_sparse_scatter_sub(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
+                           const int64_t* ids, int64_t n, const float* rows, float scale,
+                           void* scratch, size_t scratch_bytes, void* stream) {
+  if (n > 0 && (!ids || !rows)) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  IdSrc is = {};
+  RowSrc rs = {};
+  is.base[0] = (const long long*)ids;
+  rs.base[0] = rows;
+  return scatter_sub_impl(table, vocab, dim, n_shards, shard, strategy, is, n, rs, scale, scratch, scratch_bytes, stream);
+}
+
+int tfg_sparse_scatter_sub_multi(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
+                                 const int64_t* const* ids_devs, const float* const* rows_devs, int n_sources,
+                                 int64_t n_per_source, float scale, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n_sources < 1 || n_sources > TFG_MAX_REPLICAS) return fail(nullptr, TFG_ELIMIT, "n_sources out of range");
+  if (n_per_source < 0 || !ids_devs || !rows_devs) return fail(nullptr, TFG_EINVAL, "bad argument");
+  if (n_per_source * n_sources >= (1ll << 31)) return fail(nullptr, TFG_ELIMIT, "more than 2^31-1 ids in one call");
+  IdSrc is = {};
+  RowSrc rs = {};
+  for (int r = 0; r < n_sources; ++r) {
+    if (n_per_source > 0 && (!ids_devs[r] || !rows_devs[r])) return fail(nullptr, TFG_EINVAL, "NULL source pointer");
+    is.base[r] = (const long long*)ids_devs[r];
+    rs.base[r] = rows_devs[r];
+  }
+  is.per = n_sources > 1 ? n_per_source : 0;
+  rs.per = n_sources > 1 ? (uint32_t)n_per_source : 0;
+  return scatter_sub_impl(table, vocab, dim, n_shards, shard, strategy, is, n_per_source * n_sources, rs, scale, scratch,
+                          scratch_bytes, stream);
+}
+
+int tfg_sparse_gather_multi(const float* const* table_shards, int64_t vocab, int dim, int n_shards, int strategy,
+                            const int64_t* ids, int64_t n, float* out, int* bad, void* stream) {
+  int rc = check_sparse(vocab, dim, n_shards, 0, strategy, n);
+  if (rc) return rc;
+  if (n_shards > TFG_MAX_REPLICAS) return fail(nullptr, TFG_ELIMIT, "more than TFG_MAX_REPLICAS shards");
+  if (n == 0) return TFG_OK;
+  if (!table_shards || !ids || !out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  TableSrc ts = {};
+  for (int k = 0; k < n_shards; ++k) {
+    if (!table_shards[k] && shard_rows(vocab, n_shards, k, strategy) > 0) return fail(nullptr, TFG_EINVAL, "NULL shard pointer");
+    ts.base[k] = table_shards[k];
+  }
+  Part pt = make_part(vocab, n_shards, 0, strategy);
+  long long blocks = (n + 7) / 8;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  gather_multi_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(ts, pt, (const long long*)ids, n, dim, out, bad);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "gather_multi_kernel");
+  return TFG_OK;
+}
+
+// CUDA-IPC handles of caller-owned device buffers (table shards, id and row staging): how the
+// ranks of one box make them addressable from each other, as tfg_job_ipc_export does for a job's own.
+// cudaMalloc / cudaFree behind the C ABI: a CUDA-IPC handle names a whole allocation, so a buffer that
+// is to be shared must be an allocation of its own (a tensor carved out of a framework's caching
+// allocator is not: its handle opens at the base of the cached segment, not at the tensor)
+int tfg_dev_alloc(size_t bytes, void** dev_ptr_out) {
+  if (!dev_ptr_out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  cudaError_t e = cudaMalloc(dev_ptr_out, bytes ? bytes : 256);
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaMalloc");
+  e = cudaMemset(*dev_ptr_out, 0, bytes ? bytes : 256);
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaMemset");
+  return TFG_OK;
+}
+int tfg_dev_free(void* dev_ptr) {
+  if (!dev_ptr) return TFG_OK;
+  cudaError_t e = cudaFree(dev_ptr);
+  if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaFree");
+  return TFG_OK;
+}
+
+int tfg_ipc_export(const void* dev_ptr, void* handle_out) {
+  if (!dev_ptr || !handle_out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(dev_ptr));
+  if (e != cudaSuccess) { fail_cuda(nullptr, e, "cudaIpcGetMemHandle"); return TFG_EPEER; }
+  memcpy(handle_out, &h, sizeof h);
+  return TFG_OK;
+}
+int tfg_ipc_open(const void* handle, void** dev_ptr_out) {
+  if (!handle || !dev_ptr_out) return fail(nullptr, TFG_EINVAL, "NULL argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  cudaError_t e = cudaIpcOpenMemHandle(dev_ptr_out, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) { fail_cuda(nullptr, e, "cudaIpcOpenMemHandle"); return TFG_EPEER; }
+  return TFG_OK;
+}
+int tfg_ipc_close(void* dev_ptr) {
+  if (!dev_ptr) return TFG_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(dev_ptr);
+  if (e != cudaSuccess) { fail_cuda(nullptr, e, "cudaIpcCloseMemHandle"); return TFG_EPEER; }
   return TFG_OK;
 }
 

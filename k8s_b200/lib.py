@@ -103,6 +103,14 @@ _SIGS = {
     "tfg_sparse_scratch_bytes_fast": (C.c_size_t, [C.c_int64, C.c_int]),
     "tfg_sparse_scatter_sub": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
                                          C.c_int64, _p, C.c_float, _p, C.c_size_t, _p]),
+    "tfg_sparse_gather_multi": (C.c_int, [C.POINTER(_p), C.c_int64, C.c_int, C.c_int, C.c_int, _p, C.c_int64, _p, _p, _p]),
+    "tfg_sparse_scatter_sub_multi": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_p),
+                                               C.POINTER(_p), C.c_int, C.c_int64, C.c_float, _p, C.c_size_t, _p]),
+    "tfg_dev_alloc": (C.c_int, [C.c_size_t, C.POINTER(_p)]),
+    "tfg_dev_free": (C.c_int, [_p]),
+    "tfg_ipc_export": (C.c_int, [_p, _p]),
+    "tfg_ipc_open": (C.c_int, [_p, C.POINTER(_p)]),
+    "tfg_ipc_close": (C.c_int, [_p]),
     "tfg_sparse_scatter_sub_static": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
                                                 C.c_int64, _p, C.c_float, _p]),
     "tfg_model_mnist_cnn": (C.c_int, [_p, C.c_int, C.c_int]),

@@ -21,3 +21,13 @@ def test_two_ranks_match_oracle_and_each_other(lib, layout):
            layout]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0 and "MGPU_CHECK PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_two_ranks_sparse_embedding_matches_oracle(lib):
+    """The sparse path over real peers: CUDA-IPC mapped shards and staging buffers, stream-ordered barrier."""
+    if lib.device_count_or_zero() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29613", os.path.join(ROOT, "scripts", "mgpu_sparse_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert r.returncode == 0 and "MGPU_SPARSE_CHECK PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -138,3 +138,112 @@ def test_full_size_roundtrip_property(lib):
     torch.cuda.synchronize()
     assert not table[perm].any()
     assert torch.count_nonzero(table.abs().sum(1)) == vocab - n
+
+
+@pytest.mark.parametrize("strategy", ["mod", "div"])
+@pytest.mark.parametrize("n_gpus,n_shards,vocab,dim,batch,dist", [
+    (2, 2, 1000, 64, 512, "uniform"), (4, 8, 5003, 128, 1000, "zipf"), (4, 3, 300, 33, 257, "uniform"),
+    (2, 5, 64, 16, 2048, "one"), (8, 8, 100000, 128, 4096, "zipf"),
+])
+def test_sharded_embedding_across_emulated_ranks(lib, strategy, n_gpus, n_shards, vocab, dim, batch, dist):
+    """The sparse path across GPU ranks (SURVEY.md par. 8e), all ranks emulated on one device (peer
+    pointers are then ordinary device pointers): each rank looks its own batch up in ONE launch that
+    reads every owner's shard, and each shard owner applies scatter_sub over the concatenation of all
+    ranks' (ids, rows) in (rank, position) order.  Both bit-exact against the C oracle run on the
+    concatenated batch, twice (scratch reuse)."""
+    import json
+
+    from k8s_b200.sparse import ShardedEmbedding
+    from k8s_b200.syncps import SyncPSJob
+    cluster = {"master": ["m:1"], "ps": ["p%d:1" % i for i in range(n_shards)]}
+    if n_gpus > 1:
+        cluster["worker"] = ["w%d:1" % i for i in range(n_gpus - 1)]
+    jobs = [SyncPSJob(json.dumps({"cluster": cluster}), r, n_gpus, cuda_device=0) for r in range(n_gpus)]
+    embs = [ShardedEmbedding(j, vocab, dim, batch, strategy) for j in jobs]
+    for e in embs:
+        assert e.owned == [k for k in range(n_shards) if jobs[0].lib.ps_gpu(jobs[0].h, k) == e.rank]
+        e.attach_local([o for o in embs if o is not e])
+    rng = np.random.default_rng(vocab * 7 + batch)
+    strat = {"mod": L.PART_MOD, "div": L.PART_DIV}[strategy]
+    tables = {}
+    for e in embs:
+        for k in e.owned:
+            rows = lib.sparse_shard_rows(vocab, n_shards, k, strat)
+            tables[k] = rng.standard_normal((max(rows, 1), dim)).astype(np.float32)
+            e.set_shard(k, tables[k])
+    for rep in range(2):
+        ids = [make_ids(rng, vocab, batch, dist) for _ in range(n_gpus)]
+        grads = [rng.standard_normal((batch, dim)).astype(np.float32) for _ in range(n_gpus)]
+        for r, e in enumerate(embs):
+            e.stage_ids(ids[r])
+            got = e.lookup().cpu().numpy()
+            want = np.full((batch, dim), np.nan, dtype=np.float32)
+            for k in range(n_shards):
+                O.sparse_gather(tables[k], vocab, n_shards, k, strat, ids[r], want)
+            np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32))
+            assert int(e.bad.item()) == 0
+        for r, e in enumerate(embs):
+            e.stage_rows(grads[r])
+        torch.cuda.synchronize()
+        for e in embs:
+            e.apply_owned(0.05)
+        torch.cuda.synchronize()
+        all_ids, all_grads = np.concatenate(ids), np.concatenate(grads)
+        for k in range(n_shards):
+            O.sparse_scatter_sub(tables[k], vocab, n_shards, k, strat, all_ids, all_grads, 0.05)
+        for e in embs:
+            for k in e.owned:
+                np.testing.assert_array_equal(e.get_shard(k).view(np.uint32), tables[k].view(np.uint32))
+    for j in jobs:
+        j.close()
+
+
+def test_sharded_embedding_chunked_long_runs_is_deterministic_and_accurate(lib):
+    """chunk_long_runs=True on a heavy-tailed batch across 4 emulated ranks: rows hit <= 64 times stay
+    bit-exact, the hot rows are deterministic and as accurate as the sequential loop (vs float64)."""
+    import json
+
+    from k8s_b200.sparse import ShardedEmbedding
+    from k8s_b200.syncps import SyncPSJob
+    n_gpus, vocab, dim, batch = 4, 2000, 64, 8192
+    cluster = {"master": ["m:1"], "ps": ["p%d:1" % i for i in range(n_gpus)], "worker": ["w%d:1" % i for i in range(n_gpus - 1)]}
+    rng = np.random.default_rng(3)
+    ids = [make_ids(rng, vocab, batch, "zipf") for _ in range(n_gpus)]
+    grads = [rng.standard_normal((batch, dim)).astype(np.float32) for _ in range(n_gpus)]
+    table0 = rng.standard_normal((vocab, dim)).astype(np.float32)
+    all_ids, all_grads = np.concatenate(ids), np.concatenate(grads)
+    want = table0.copy()
+    O.sparse_scatter_sub(want, vocab, 1, 0, O.MOD, all_ids, all_grads, 0.05)
+    exact = table0.astype(np.float64)
+    np.subtract.at(exact, all_ids, (np.float32(0.05) * all_grads).astype(np.float64))
+    outs = []
+    for rep in range(2):
+        jobs = [SyncPSJob(json.dumps({"cluster": cluster}), r, n_gpus, cuda_device=0) for r in range(n_gpus)]
+        embs = [ShardedEmbedding(j, vocab, dim, batch, "mod", chunk_long_runs=True) for j in jobs]
+        for e in embs:
+            e.attach_local([o for o in embs if o is not e])
+            for k in e.owned:
+                e.set_shard(k, table0[k::n_gpus])
+        for r, e in enumerate(embs):
+            e.stage_ids(ids[r])
+            e.stage_rows(grads[r])
+        torch.cuda.synchronize()
+        for e in embs:
+            e.apply_owned(0.05)
+        torch.cuda.synchronize()
+        full = np.empty_like(table0)
+        for e in embs:
+            for k in e.owned:
+                full[k::n_gpus] = e.get_shard(k)
+        outs.append(full)
+        for j in jobs:
+            j.close()
+    np.testing.assert_array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+    mult = np.bincount(all_ids, minlength=vocab)
+    short, long_ = mult <= 64, mult > 64
+    assert long_.any()
+    np.testing.assert_array_equal(outs[0][short].view(np.uint32), want[short].view(np.uint32))
+    err_gpu = np.abs(outs[0][long_] - exact[long_]).max(axis=1)
+    err_seq = np.abs(want[long_] - exact[long_]).max(axis=1)
+    scale = np.abs(exact[long_]).max(axis=1) + 1.0
+    assert np.all(err_gpu <= 2.0 * err_seq + 4e-7 * scale), (err_gpu.max(), err_seq.max())
