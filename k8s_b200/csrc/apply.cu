@@ -5,8 +5,6 @@
 // NVLink when n_gpus > 1) + 4 read var (+4 accum) + 4 written per pull destination
 // (+4 accum).  Single GPU, SGD: 12 B/param; momentum: 20 B/param.
 #include <algorithm>
-#include <cstdlib>
-#include <cstring>
 #include <type_traits>
 
 #include <cuda_bf16.h>
@@ -246,8 +244,10 @@ push_apply_pull_kernel(const __grid_constant__ ApplyArgs a) {
 }
 
 // ---- the same exchange with the operands streamed through shared memory by the bulk-copy engine ------
-// Multi-GPU ranks.  Register loads from a peer's memory are NVLink round trips that a thread can keep
-// only a few of in flight (measured, 2 ranks, 256 M parameters: 0.43 of the link).  Here a producer
+// Multi-GPU ranks (measured against the register kernel above on the same buffers, 4 ranks, 256 M
+// parameters: 0.88 vs 0.81 of the measured peer-copy bandwidth per direction; the register kernel stays
+// for single-GPU jobs, where it holds 0.97 of HBM peak, and for jobs with too many replicas for the
+// stage budget).  Here a producer
 // warp requests, per 1024-element chunk, one 4-KB bulk copy (cp.async.bulk, the TMA unit's linear mode)
 // per replica gradient -- local or peer memory alike -- plus the owner's parameter and slot values, into
 // a ring of shared-memory stages that complete on mbarriers; up to ~200 KB per SM are in flight however
@@ -519,12 +519,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole, bo
   const int n_arr = a.n_grads + 1 + (j->opt_kind != TFG_OPT_SGD ? 1 : 0);
   const int stages = tma_stages(n_arr);
   cudaError_t e;
-  static int use_tma = -1;
-  if (use_tma < 0) {
-    use_tma = 1;
-    if (const char* e = getenv("TFGRAFT_EXCHANGE")) use_tma = strcmp(e, "reg") != 0;
-  }
-  if (use_tma && j->n_gpus > 1 && !summed_local && !whole && j->chunk_elems == kTmaChunk && stages >= 2) {
+  if (j->n_gpus > 1 && !summed_local && !whole && j->chunk_elems == kTmaChunk && stages >= 2) {
     const size_t smem = (size_t)stages * n_arr * kTmaChunk * 4 + 2 * stages * sizeof(uint64_t);
     const int per_sm = std::max(1, (int)((227 * 1024) / (smem + 1024)));
     const int grid = (int)std::max<long long>(1, std::min<long long>(a.n_chunks, (long long)kNumSMs * per_sm));
