@@ -22,8 +22,13 @@
 namespace tfg {
 
 // ===== conv1 forward, fused with bias + 2x2 max-pool + relu ===============================
-// One block per image.  Lane = output channel (32), so input reads broadcast and filter
-// reads are conflict-free.
+// kConv1Split blocks per image (each stages the whole 3-KB image and takes a quarter of the 14x14x32
+// outputs: one block per image left 20 of the 148 SMs idle and 8 warps per SM to hide the
+// shared-memory latency).  Lane = output channel (32), so input reads broadcast and filter reads are
+// conflict-free.
+constexpr int kConv1Split = 4;
+constexpr int kConv1Part = 14 * 14 * 32 / kConv1Split;     // 1568 outputs per block
+
 __global__ void __launch_bounds__(256)
 conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1,
                        const float* __restrict__ b1, float* __restrict__ a1,
@@ -31,7 +36,7 @@ conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1
   __shared__ float xs[32][33];   // image with a 2-pixel zero border
   __shared__ float ws[25][32];
   __shared__ float bs[32];
-  const int b = blockIdx.x, t = threadIdx.x;
+  const int b = blockIdx.x / kConv1Split, part = blockIdx.x % kConv1Split, t = threadIdx.x;
   for (int i = t; i < 32 * 32; i += 256) {
     int r = i >> 5, c = i & 31;
     int ir = r - 2, ic = c - 2;
@@ -40,7 +45,7 @@ conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1
   for (int i = t; i < 800; i += 256) ws[i >> 5][i & 31] = w1[i];
   if (t < 32) bs[t] = b1[t];
   __syncthreads();
-  for (int o = t; o < 14 * 14 * 32; o += 256) {
+  for (int o = part * kConv1Part + t; o < (part + 1) * kConv1Part; o += 256) {
     const int c = o & 31, pw = (o >> 5) % 14, ph = (o >> 5) / 14;
     float patch[6][6];
 #pragma unroll
@@ -72,10 +77,10 @@ conv1_pool_relu_kernel(const float* __restrict__ x, const float* __restrict__ w1
 // g1m = gradient at the pooled pre-relu map (already masked by a1 > 0).
 __global__ void __launch_bounds__(256)
 conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
-                 const uint8_t* __restrict__ idx1, float* __restrict__ partial /*[2B][832]*/) {
+                 const uint8_t* __restrict__ idx1, float* __restrict__ partial /*[kConv1Split * B][832]*/) {
   __shared__ float xs[32][33];
   __shared__ float red[8][26][32];
-  const int b = blockIdx.x >> 1, half = blockIdx.x & 1, t = threadIdx.x, w = t >> 5, c = t & 31;
+  const int b = blockIdx.x / kConv1Split, part = blockIdx.x % kConv1Split, t = threadIdx.x, w = t >> 5, c = t & 31;
   for (int i = t; i < 32 * 32; i += 256) {
     int r = i >> 5, q = i & 31;
     int ir = r - 2, ic = q - 2;
@@ -86,8 +91,8 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
   float accb = 0.f;
 #pragma unroll
   for (int k = 0; k < 25; ++k) acc[k] = 0.f;
-  // this block's half of the pooled map: rows [7*half, 7*half + 7)
-  for (int o = half * (7 * 14 * 32) + t; o < (half + 1) * (7 * 14 * 32); o += 256) {   // o & 31 == c
+  // this block's quarter of the pooled map
+  for (int o = part * kConv1Part + t; o < (part + 1) * kConv1Part; o += 256) {   // o & 31 == c
     const int pw = (o >> 5) % 14, ph = (o >> 5) / 14;
     const size_t oi = (size_t)b * (14 * 14 * 32) + o;
     const float g = g1m[oi];
@@ -108,7 +113,7 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
     float s = red[0][k][cc];
 #pragma unroll
     for (int ww = 1; ww < 8; ++ww) s += red[ww][k][cc];
-    partial[(size_t)blockIdx.x * 832 + i] = s;   // [25*32 dW | 32 db], two rows per image
+    partial[(size_t)blockIdx.x * 832 + i] = s;   // [25*32 dW | 32 db], kConv1Split rows per image
   }
 }
 
@@ -361,20 +366,6 @@ softmax_xent_kernel(const float* __restrict__ logits, const int32_t* __restrict_
   if (lane == 0) loss_vec[ex] = logf(sum) - (zl - mx);
 }
 
-// mean of loss_vec[B] in a fixed order -> *out
-__global__ void __launch_bounds__(256) loss_mean_kernel(const float* __restrict__ loss_vec, float* out, int B) {
-  __shared__ float part[256];
-  float s = 0.f;
-  for (int i = threadIdx.x; i < B; i += 256) s += loss_vec[i];
-  part[threadIdx.x] = s;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o];
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) *out = part[0] / (float)B;
-}
-
 
 // ===== classifier head, forward: logits = h1 * W4 + b4, softmax cross-entropy, dlogits ======
 // One block of 8 warps per example: warp w covers k in [128w, 128w+128), partial sums are
@@ -382,7 +373,7 @@ __global__ void __launch_bounds__(256) loss_mean_kernel(const float* __restrict_
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, const float* __restrict__ b4,
                 const int32_t* __restrict__ labels, float* __restrict__ logits, float* __restrict__ dlogits,
-                float* __restrict__ loss_vec, int B) {
+                float* __restrict__ loss_vec, int B, unsigned int* __restrict__ done, float* __restrict__ loss_out) {
   __shared__ float part[8][10];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int ex = blockIdx.x;
@@ -430,6 +421,22 @@ head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, cons
     dlogits[ex * 10 + lane] = (e / sum - (lane == lab ? 1.f : 0.f)) / (float)B;
   }
   if (lane == 0) loss_vec[ex] = logf(sum) - (zl - mx);
+  // the block that finishes last folds the per-example losses into the replica's mean, always in example
+  // order (a launch of its own used to do this)
+  __shared__ bool last;
+  if (lane == 0) {
+    __threadfence();
+    last = atomicAdd(done, 1u) == gridDim.x - 1;
+  }
+  __syncwarp();
+  if (last) {
+    __threadfence();
+    float s = 0.f;
+    for (int i = lane; i < B; i += 32) s += __ldcg(loss_vec + i);   // lane l: examples l, l + 32, ... in order
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) { *loss_out = s / (float)B; *done = 0u; }
+  }
 }
 
 // ===== classifier head, backward =========================================================
@@ -619,7 +626,7 @@ int mnist_build(tfg_job* j, int batch, int math) {
     A_(lab_stage, B, int32_t);
     A_(a1, B * 6272, float);
     A_(idx1, B * 6272, uint8_t);
-    A_(col, B * 196 * 800, float);
+    A_(col, math == TFG_MATH_FP32 ? B * 196 * 800 : 4, float);            // the im2col matrix: CUDA-core path only
     A_(y2, B * 196 * 64, float);
     A_(a2, B * 3136, float);
     A_(idx2, B * 3136, uint8_t);
@@ -627,15 +634,17 @@ int mnist_build(tfg_job* j, int batch, int math) {
     A_(logits, B * 10, float);
     A_(dlogits, B * 10, float);
     A_(loss_vec, B, float);
+    A_(head_done, 1, unsigned int);
+    if (e == cudaSuccess) e = cudaMemset(sl.head_done, 0, sizeof(unsigned int));
     A_(dh1, B * 1024, float);
     A_(da2, B * 3136, float);
     A_(da2m, B * 3136, float);
     A_(dy2, B * 196 * 64, float);
-    A_(dcol, B * 196 * 800, float);
+    A_(dcol, math == TFG_MATH_TF32X3 ? 4 : B * 196 * 800, float);         // 3xTF32 writes the input gradient directly
     A_(g1m, B * 6272, float);
     // scratch for deterministic reductions: split-K partials of dW2 (32 x 800 x 64), the
     // per-image conv1 partials (B x 832) and column-sum chunks
-    size_t sc = std::max<size_t>({(size_t)kSplitW2 * 800 * 64, 2 * B * 832, ((B + 15) / 16) * (size_t)(1024 * 11),
+    size_t sc = std::max<size_t>({(size_t)kSplitW2 * 800 * 64, kConv1Split * B * 832, ((B + 15) / 16) * (size_t)(1024 * 11),
                                   ((B * 49 + 63) / 64) * 1024, (size_t)3136 * 1024});
     sl.scratch_floats = sc;
     A_(scratch, sc, float);
@@ -659,7 +668,7 @@ void mnist_destroy(tfg_job* j) {
   if (!m) return;
   mnist_tc_destroy(j);
   for (auto& sl : m->slots) {
-    void* ps[] = {sl.x_stage, sl.lab_stage, sl.a1, sl.idx1, sl.col, sl.y2, sl.a2, sl.idx2, sl.h1,
+    void* ps[] = {sl.head_done, sl.x_stage, sl.lab_stage, sl.a1, sl.idx1, sl.col, sl.y2, sl.a2, sl.idx2, sl.h1,
                   sl.logits, sl.dlogits, sl.loss_vec, sl.dh1, sl.da2, sl.da2m, sl.dy2, sl.dcol,
                   sl.g1m, sl.scratch};
     for (void* p : ps) cudaFree(p);
@@ -704,7 +713,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   const bool tc = m->math != TFG_MATH_FP32;
 
   // ---------------- forward ----------------
-  conv1_pool_relu_kernel<<<B, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1, mnist_tc_a1_lo(j, slot));
+  conv1_pool_relu_kernel<<<B * kConv1Split, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1, mnist_tc_a1_lo(j, slot));
   LAUNCH_OK(j, "conv1_pool_relu_kernel");
   if (tc) {
     if ((rc = mnist_tc_forward(j, slot))) return rc;   // conv2 + fc1 on the tensor path
@@ -720,10 +729,9 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
   }
   // logits = h1 * W4 + b4, softmax cross-entropy and dlogits in one warp-shuffle kernel
-  head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B);
+  head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B, s.head_done,
+                                     j->loss + j->local_replicas[slot]);
   LAUNCH_OK(j, "head_fwd_kernel");
-  loss_mean_kernel<<<1, 256, 0, st>>>(s.loss_vec, j->loss + j->local_replicas[slot], B);
-  LAUNCH_OK(j, "loss_mean_kernel");
 
   // ---------------- backward ----------------
   // dW4, db4, dh1 (masked by h1 > 0) and db3 in one pass over the batch
@@ -768,10 +776,10 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     col2im_mask_kernel<float><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
     LAUNCH_OK(j, "col2im_mask_kernel");
   }
-  conv1_bwd_kernel<<<2 * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
+  conv1_bwd_kernel<<<kConv1Split * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  reduce_rows_kernel<<<(832 + 31) / 32, 256, 0, st>>>(s.scratch, 2 * B, 832, 832, grd(0), 800, grd(1));
+  reduce_rows_kernel<<<(832 + 31) / 32, 256, 0, st>>>(s.scratch, kConv1Split * B, 832, 832, grd(0), 800, grd(1));
   LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }

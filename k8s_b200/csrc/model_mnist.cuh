@@ -38,6 +38,7 @@ struct MnistSlot {       // activations of one local replica
   float* logits = nullptr;       // [B,10]
   float* dlogits = nullptr;
   float* loss_vec = nullptr;
+  unsigned int* head_done = nullptr;   // blocks of head_fwd_kernel that have finished (the last one takes the mean loss)
   float* dh1 = nullptr;
   float* da2 = nullptr;
   float* da2m = nullptr;
