@@ -60,27 +60,16 @@ int make_map_4d_box(CUtensorMap* map, const void* ptr, int N, int H, int W, int 
 // conv3x3_halo_kernel: 3x3, stride 1, 64-channel blocks, at least two image rows per 128-position tile
 // and a slab that fits its stage
 bool halo_fits(int OH, int OW, int C, int R, int stride) {
-  static int on = -1;
-  if (on < 0) {
-    on = 1;
-    if (const char* e = getenv("TFGRAFT_HALO")) on = atoi(e) != 0;
-  }
   const int PW = OW + 2;
-  return on == 1 && R == 3 && stride == 1 && C % 64 == 0 && OW >= 12 && PW <= tc::halo_max_pw<1>() && OH >= 2;
+  return R == 3 && stride == 1 && C % 64 == 0 && OW >= 12 && PW <= tc::halo_max_pw<1>() && OH >= 2;
 }
 
 // M tiles per CTA: two (256 positions, the accumulators share every weight tile) when the wider slab
 // fits its stage and the coarser tiles do not cost more in wave quantisation than the sharing returns
-// (ResNet stage 3: 512 double tiles are 4 waves of 2 units against 7 waves of 1: stay with one);
-// TFGRAFT_HALO_MT=1 keeps one everywhere
+// (ResNet stage 3: 512 double tiles are 4 waves of 2 units against 7 waves of 1: stay with one)
 int halo_mt(int Nimg, int OH, int OW, int tiles_n) {
-  static int want = -1;
-  if (want < 0) {
-    want = 2;
-    if (const char* e = getenv("TFGRAFT_HALO_MT")) want = atoi(e) == 1 ? 1 : 2;
-  }
   const int PW = OW + 2;
-  if (want == 1 || PW > tc::halo_max_pw<2>()) return 1;
+  if (PW > tc::halo_max_pw<2>()) return 1;
   auto waves = [&](int mt) {
     const int th = std::max(1, std::min(OH, 128 * mt / PW));
     const long long tiles = (long long)Nimg * ((OH + th - 1) / th) * tiles_n;
@@ -114,12 +103,8 @@ static cudaError_t launch_halo(const HaloConv& g, cudaStream_t s) {
   }
   // Descriptor base-offset field for the shifted slab views: measured on B200, the MMA unit applies
   // the 128-byte swizzle to absolute shared-memory address bits, so a start address that is a multiple
-  // of 128 B inside a 1024-B-aligned slab needs NO base offset (mode 1 = set it, gives wrong results).
-  static int base_mode = -1;
-  if (base_mode < 0) {
-    base_mode = 0;
-    if (const char* e = getenv("TFGRAFT_HALO_BASE")) base_mode = atoi(e);
-  }
+  // of 128 B inside a 1024-B-aligned slab needs NO base offset (setting it gives wrong results).
+  const int base_mode = 0;
   const int tiles_n = (g.N + BN - 1) / BN;
   const long long total = (long long)g.hs.m_tiles * tiles_n;
   tc::Epilogue epi = g.epi;

@@ -166,24 +166,9 @@ static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_block
   // Ring depth.  A shallow ring leaves shared memory for more CTAs per SM, whose prologues and
   // epilogues then overlap each other's loads: that wins whenever the grid is several waves deep
   // (measured on the ResNet-50 layers: +14 % end to end); a grid of about one wave needs the deep
-  // ring to overlap its own loads with its MMAs (the MNIST GEMMs).  TFGRAFT_STAGES=1|2|4 forces one.
-  static int forced = -1;
-  if (forced < 0) {
-    forced = 0;
-    if (const char* e = getenv("TFGRAFT_STAGES")) forced = atoi(e);
-  }
+  // ring to overlap its own loads with its MMAs (the MNIST GEMMs).
   const long long ctas = (long long)((g.N + BN - 1) / BN) * ((g.M + tc::kBlockM - 1) / tc::kBlockM) * splits;
-  static int persistent = -1;
-  if (persistent < 0) {
-    persistent = 1;
-    if (const char* e = getenv("TFGRAFT_PERSISTENT")) persistent = atoi(e);
-  }
-  static int min_kps = -1;
-  if (min_kps < 0) {
-    min_kps = 1;
-    if (const char* e = getenv("TFGRAFT_PERSISTENT_MIN_KPS")) min_kps = atoi(e);
-  }
-  if ((persistent == 1 && ctas >= 2ll * kNumSMs && kps >= min_kps) || persistent == 2 || epi.tma_out)
+  if (ctas >= 2ll * kNumSMs || epi.tma_out)   // at least two waves of tiles: one persistent CTA per SM
     return launch_persistent<BN, KIND, A_MN, B_MN>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   int stages = kps <= 1 ? 1 : kps <= 3 ? 2 : 4;
   if (ctas >= 4ll * kNumSMs) stages = 1;
@@ -191,7 +176,6 @@ static cudaError_t launch_inst(const TcGemm& g, float* dst, int ldc, int k_block
   // one wave of CTAs with a long K loop each (split-K weight gradients: K = all pixels): bandwidth is
   // bytes in flight over the 2 us TMA round trip, so take the deepest ring that fits
   if (stages == 4 && kps >= 48 && ctas <= kNumSMs) stages = 6;
-  if (forced == 1 || forced == 2 || forced == 4 || forced == 6) stages = forced;
   if (stages == 1) return launch_stage<BN, KIND, A_MN, B_MN, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   if (stages == 2) return launch_stage<BN, KIND, A_MN, B_MN, 2>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   if (stages == 6) return launch_stage<BN, KIND, A_MN, B_MN, 6>(g, dst, ldc, k_blocks, kps, splits, epi, s);
@@ -218,12 +202,8 @@ int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
   float* dst = splits > 1 ? g.partial : g.C;
   const int ldc = splits > 1 ? g.N : g.ldc;
   tc::Epilogue epi = splits > 1 ? tc::Epilogue{nullptr, nullptr, 0, nullptr, 0} : g.epi;
-  static int direct = -1;
-  if (direct < 0) {
-    direct = 1;   // measured on the ResNet-50 layers: 6100 vs 5230 images/s against the smem-transposed stores
-    if (const char* e = getenv("TFGRAFT_EPI_DIRECT")) direct = atoi(e);
-  }
-  epi.direct = direct;
+  epi.direct = 1;   // register-direct stores (measured on the ResNet-50 layers: 6100 vs 5230 images/s against the
+                    // smem-transposed stores, which remain the path for ragged tails)
   epi.tma_out = 0;
   if (g.tma_out) {
     if (splits > 1 || !g.epi.out_bf16 || g.epi.mask || kind != TFG_MATH_BF16)

@@ -40,12 +40,7 @@ void prof_mark(tfg_job* j, const char* what) {
 }
 
 cudaStream_t side_fork(tfg_job* j) {
-  static int on = -1;
-  if (on < 0) {
-    on = 1;
-    if (const char* e = getenv("TFGRAFT_SIDE")) on = atoi(e) != 0;
-  }
-  if (!on || j->prof_on || !j->side_stream) return j->stream;   // per-kernel timing attributes time on one stream
+  if (j->prof_on || !j->side_stream) return j->stream;   // per-kernel timing attributes time on one stream
   if (cudaEventRecord(j->ev_side[0], j->stream) != cudaSuccess ||
       cudaStreamWaitEvent(j->side_stream, j->ev_side[0], 0) != cudaSuccess) {
     cudaGetLastError();

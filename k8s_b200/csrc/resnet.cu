@@ -89,32 +89,18 @@ static inline int grid_for(long long n, int per = 256) {
 constexpr int kBnTargetBlocks = kNumSMs * 4;
 constexpr size_t kBnPartialFloats = (size_t)(kBnTargetBlocks + 32) * 64;   // chunks * C never exceeds this
 
-// bf16 GEMM outputs leave through TMA stores / reduce-adds (TFGRAFT_TMA_OUT=0: register-direct stores
-// plus a separate accumulate kernel)
-static bool tma_out_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    on = 1;
-    if (const char* e = getenv("TFGRAFT_TMA_OUT")) on = atoi(e) != 0;
-  }
-  return on == 1;
-}
+// bf16 GEMM outputs leave through TMA stores / reduce-adds wherever the shape allows it (measured against
+// register-direct stores plus a separate accumulate kernel: profiles/README.md, round 1)
+static constexpr bool tma_out_enabled() { return true; }
 
 // element-wise kernels with a grid-stride loop and three resident blocks per SM: one full wave
 static inline int grid_resident(long long n, int per = 256) {
   return (int)std::max<long long>(1, std::min<long long>((n + per - 1) / per, kNumSMs * 3));
 }
 
-// TFGRAFT_S2_DGRAD=0: stride-2 data gradients through dz x W^T and a col2im gather instead of the
-// parity-class GEMMs
-static bool s2_dgrad_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    on = 1;
-    if (const char* e = getenv("TFGRAFT_S2_DGRAD")) on = atoi(e) != 0;
-  }
-  return on == 1;
-}
+// stride-2 data gradients run as one implicit GEMM per parity class (measured against dz x W^T plus a
+// col2im gather: -1.6 ms per step, profiles/README.md, round 1)
+static constexpr bool s2_dgrad_enabled() { return true; }
 
 #define RN_OK(j, what)                                           \
   do {                                                           \
@@ -182,7 +168,7 @@ static int add_unit(tfg_job* j, ResnetModel* m, const std::string& name, int in,
   u.g.Kp = (R * R * u.g.C + 7) / 8 * 8;
   u.kout = kout; u.in = in; u.res = res; u.relu = relu;
   u.direct = (R == 1 && stride == 1);
-  u.implicit = !u.direct && (x.c % 64 == 0) && getenv("TFGRAFT_NO_IMPLICIT") == nullptr;
+  u.implicit = !u.direct && (x.c % 64 == 0);
   u.halo = u.implicit && tma_out_enabled() && halo_fits(u.g.OH, u.g.OW, u.g.C, R, stride);
   u.z = add_tensor(m, name + "/z", x.n, u.g.OH, u.g.OW, kout);
   u.y = add_tensor(m, name + "/y", x.n, u.g.OH, u.g.OW, kout);
@@ -522,15 +508,9 @@ static void bn_chunks(long long M, int C, int* chunks, int* rows) {
   *rows = r;
 }
 
-// TFGRAFT_BN_FUSED=0: batch-norm statistics from a pass over z instead of the GEMM epilogue's column sums
-static bool bn_fused_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    on = 1;
-    if (const char* e = getenv("TFGRAFT_BN_FUSED")) on = atoi(e) != 0;
-  }
-  return on == 1;
-}
+// batch-norm statistics come from the GEMM epilogue's column sums wherever the output went through the TMA
+// path (measured against a pass over z: profiles/README.md, round 1)
+static constexpr bool bn_fused_enabled() { return true; }
 
 // batch statistics of unit i's convolution output: folded from the GEMM epilogue's per-tile column
 // sums when the output went through the TMA path, else reduced from z
