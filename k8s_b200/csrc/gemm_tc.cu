@@ -462,7 +462,8 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
   if ((rc = mk(t->fc1_fwd, "tc gemm fc1 fwd", B, 1024, 3136, a2, 3136, false, w3, 1024, true, s.h1, 64,
                kSplitFc1Fwd, tc::Epilogue{par(5), nullptr, 1, nullptr, 0}, t->a2_lo, w3l))) return rc;
   if ((rc = mk(t->fc1_wgrad, "tc gemm fc1 wgrad", 3136, 1024, B, a2, 3136, true, dh1, 1024, true, grd(4),
-               x3 ? 64 : 128, 1,   // 3xTF32: 400 tiles of 128 x 64, two CTAs per SM (measured 20 vs 27 us for 200 of 128 x 128) tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->a2_lo, t->dh1_lo))) return rc;
+               // 3xTF32: 400 tiles of 128 x 64, two CTAs per SM (measured 20 vs 27 us for 200 tiles of 128 x 128)
+               x3 ? 64 : 128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->a2_lo, t->dh1_lo))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
                64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dh1_lo, w3l))) return rc;
   if (!x3) {
