@@ -281,7 +281,8 @@ int tfg_ipc_close(void* dev_ptr);
  *   - All calls on a device share the one array and it keeps the previous call's contents.
  *     Nothing in it has to start at zero (every word a call reads it has written first),
  *     but two calls that overlap on the GPU -- different streams, or different host
- *     threads -- race on it: issue them on one stream, or serialise them yourself. */
+ *     threads -- race on it: issue them on one stream, or serialise them yourself.  (The
+ *     address look-up itself is safe from several host threads.) */
 #define TFG_SPARSE_STATIC_MAX_IDS 65536
 #define TFG_SPARSE_STATIC_SCRATCH_BYTES 1081600
 int tfg_sparse_scatter_sub_static(float* table_dev, int64_t vocab, int dim, int n_shards,

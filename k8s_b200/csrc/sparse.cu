@@ -8,6 +8,7 @@
 // then one warp per distinct row walks its run in position order, keeping the row in
 // registers: table[row] = fl(table[row] - fl(scale * rows[i])) for each i in turn, which
 // is what a sequential CPU loop over i computes ([TF1.3] scatter_sub on the CPU).
+#include <atomic>
 #include <cstring>
 
 #include "common.cuh"
@@ -708,7 +709,9 @@ int tfg_ipc_close(void* dev_ptr) {
 // kernels receive.
 static __device__ __align__(256) unsigned char g_static_scratch[TFG_SPARSE_STATIC_SCRATCH_BYTES];
 
-static void* g_static_scratch_addr[64] = {};   // per CUDA device ordinal, filled on first use
+// per CUDA device ordinal, filled on first use; atomic because calls may come from several host threads
+// (two first calls on a device race only to store the same address)
+static std::atomic<void*> g_static_scratch_addr[64];
 
 int tfg_sparse_scatter_sub_static(float* table, int64_t vocab, int dim, int n_shards, int shard,
                                   int strategy, const int64_t* ids, int64_t n, const float* rows,
@@ -725,11 +728,11 @@ int tfg_sparse_scatter_sub_static(float* table, int64_t vocab, int dim, int n_sh
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetDevice");
   if (dev < 0 || dev >= 64) return fail(nullptr, TFG_ELIMIT, "CUDA device ordinal beyond 63");
-  void* scratch = g_static_scratch_addr[dev];
+  void* scratch = g_static_scratch_addr[dev].load(std::memory_order_acquire);
   if (!scratch) {  // once per device, with that device current
     e = cudaGetSymbolAddress(&scratch, g_static_scratch);
     if (e != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetSymbolAddress(g_static_scratch)");
-    g_static_scratch_addr[dev] = scratch;
+    g_static_scratch_addr[dev].store(scratch, std::memory_order_release);
   }
   // Hand over exactly the sort scratch this n needs: every duplicate is then applied in order,
   // whatever n is (with more scratch tfg_sparse_scatter_sub would switch long runs to its

@@ -49,6 +49,31 @@ def test_static_scratch_matches_caller_scratch_on_two_calls_in_a_row(lib):
         assert not np.array_equal(want.cpu().numpy(), table0)  # the update really happened
 
 
+def test_static_scratch_call_allocates_no_device_memory_and_takes_odd_row_widths(lib):
+    """What the entry point is for: once the first call on the device has looked up the built-in
+    array, a call must leave the amount of free device memory exactly where it was (no cudaMalloc
+    behind the caller's back).  Row width 33 is not a multiple of 4: the scalar load/store path."""
+    vocab, dim, n = 700, 33, 5000
+    rng = np.random.default_rng(7)
+    table0 = rng.standard_normal((vocab, dim)).astype(np.float32)
+    ids = rng.integers(0, vocab, size=n).astype(np.int64)
+    grads = rng.standard_normal((n, dim)).astype(np.float32)
+    want, got, d_ids, d_grads = dev(table0), dev(table0), dev(ids), dev(grads)
+    scratch = torch.empty(lib.sparse_scratch_bytes(n), dtype=torch.uint8, device="cuda")
+    lib.check(lib.sparse_scatter_sub(want.data_ptr(), vocab, dim, 1, 0, L.PART_MOD, d_ids.data_ptr(), n,
+                                     d_grads.data_ptr(), 0.05, scratch.data_ptr(), scratch.numel(), 0))
+    lib.check(lib.sparse_scatter_sub_static(got.data_ptr(), vocab, dim, 1, 0, L.PART_MOD, d_ids.data_ptr(), n,
+                                            d_grads.data_ptr(), 0.05, 0))      # first use on this device may set up
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(got.cpu().numpy().view(np.uint32), want.cpu().numpy().view(np.uint32))
+    free_before = torch.cuda.mem_get_info()[0]
+    for _ in range(3):
+        lib.check(lib.sparse_scatter_sub_static(got.data_ptr(), vocab, dim, 1, 0, L.PART_MOD, d_ids.data_ptr(), n,
+                                                d_grads.data_ptr(), 0.05, 0))
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free_before
+
+
 def test_static_scratch_rejects_oversized_batches_and_empty_is_a_noop(lib):
     table = torch.zeros((10, 4), device="cuda")
     ids = torch.zeros(1, dtype=torch.int64, device="cuda")
