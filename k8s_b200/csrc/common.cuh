@@ -1,6 +1,7 @@
 // Internal declarations shared by the libtfgraft translation units.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
@@ -112,6 +113,15 @@ struct tfg_job {
 };
 
 namespace tfg {
+
+// NVTX range over a phase of the step (forward, backward, push+apply+pull): visible in Nsight Systems /
+// Compute timelines, a no-op without a profiler attached (header-only NVTX 3)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 int fail(tfg_job* j, int rc, const std::string& msg);
 int fail_cuda(tfg_job* j, cudaError_t e, const char* what);

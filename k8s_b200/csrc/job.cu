@@ -803,6 +803,7 @@ static int step_device_work(tfg_job* j, const float* const* images, const int32_
   int rc;
   for (size_t s = 0; s < j->grads.size(); ++s)
     if ((rc = model_fb(j, (int)s, images[s], labels[s]))) return rc;
+  NvtxRange nvtx("push + apply + pull");
   return launch_job_apply(j, false, j->n_replicas, false, true);   // the cross-rank synchronisation is inside the kernel
 }
 

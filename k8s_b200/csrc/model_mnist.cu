@@ -713,6 +713,8 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   const bool tc = m->math != TFG_MATH_FP32;
 
   // ---------------- forward ----------------
+  {
+  NvtxRange nvtx_fwd("mnist forward");
   conv1_pool_relu_kernel<<<B * kConv1Split, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1, mnist_tc_a1_lo(j, slot));
   LAUNCH_OK(j, "conv1_pool_relu_kernel");
   if (tc) {
@@ -733,7 +735,9 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                                      j->loss + j->local_replicas[slot]);
   LAUNCH_OK(j, "head_fwd_kernel");
 
+  }
   // ---------------- backward ----------------
+  NvtxRange nvtx_bwd("mnist backward");
   // dW4, db4, dh1 (masked by h1 > 0) and db3 in one pass over the batch
   {
     const int chunks = (B + kFc2Chunk - 1) / kFc2Chunk;

@@ -547,6 +547,7 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
   const bool update_moving = slot == 0;
 
   // ================= forward =================
+  nvtxRangePushA("resnet50 forward");
   {
     const long long n = m->tensors[m->t_image].elems();
     rn::to_bf16_kernel<<<grid_for(n), 256, 0, st>>>(images, s.data[m->t_image], n);
@@ -598,7 +599,9 @@ int resnet_forward_backward(tfg_job* j, int slot, const float* images, const int
   rn::mean_kernel<<<1, 256, 0, st>>>(s.loss_vec, j->loss + j->local_replicas[slot], B);
   RN_OK(j, "rn loss mean");
 
+  nvtxRangePop();
   // ================= backward =================
+  NvtxRange nvtx_bwd("resnet50 backward");
   std::vector<char> written(m->tensors.size(), 0);   // has this tensor's gradient buffer been written yet?
   if ((rc = launch_tc(j, s.fc_wgrad, TFG_MATH_BF16, st))) return rc;
   rn::colsum_bf16_kernel<<<(m->classes + 255) / 256, 256, 0, st>>>(s.dlogits, grd(m->v_fcb), B, m->classes);
