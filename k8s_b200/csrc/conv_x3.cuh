@@ -15,9 +15,14 @@
 //   dgrad    dx[pix, c]  = sum_{r,s,n} dy[pix - (r,s) + 2, n] W[r,s,c,n], masked    A = dy slab (K-major, 2 channel blocks), B = W (K-major)
 //   wgrad    dW[(r,s,c), n] = sum_pix x[pix + (r,s) - 2, c] dy[pix, n]              A = x slab (MN-major views), B = dy (MN-major)
 //
-// Every operand comes with its low-order plane; per K step the MMA warp issues A_lo*B and A*B_lo
-// into the small-term accumulator S and A*B into one of two main accumulators that alternate per
-// chunk and are summed in registers by the epilogue warps (see gemm_x3.cuh for why).
+// Every operand comes with its low-order plane.  These MMAs are bound by shared-memory reads of the A
+// operand (N = 64 / 32 output channels: 4 KB of A per instruction against 2 / 1 KB of B), so forward and
+// data gradient put W and W_lo side by side along N: ONE instruction A x [W | W_lo] yields the main
+// product (columns [0, N)) and the small product A*W_lo (columns [N, 2N)) for one read of A, and a second
+// one adds A_lo x W into the small columns -- two reads of A-sized operands per K step instead of three.
+// The accumulator [main | small] alternates between two TMEM buffers per chunk of taps and is summed in
+// registers by the epilogue warps (gemm_x3.cuh explains why); the small columns accumulate at their own
+// magnitude, so the tensor core's truncation costs them nothing.
 #pragma once
 #include "gemm_x3.cuh"
 #include "conv_tc.cuh"
@@ -38,7 +43,9 @@ constexpr int kC2Threads = 64 + 256;                       // TMA warp, MMA warp
 // map_w / map_w_lo: W2 viewed [800, 64]; forward reads boxes {32 n, 32 k-lines} (MN-major), the data
 //                   gradient boxes {32 k, 32 rows = input channels of the tap} (K-major).
 // Output out[pixels, N_OUT] fp32 (+ bias[N_OUT]) (kept where mask[pixels, N_OUT] > 0).
-// One image per tile, persistent over images; B_STAGES weight stages of one tap each.
+// One image per tile, persistent over images; B_STAGES weight stages of one tap each:
+//   forward  [W n 0..31 | W n 32..63 | W_lo n 0..31 | W_lo n 32..63], MN-major boxes of 4 KB (group stride 4 KB)
+//   dgrad    per K block (32 of the 64 dy channels): [W rows c 0..31 | W_lo rows c 0..31], K-major, 8 KB
 template <bool DGRAD> constexpr int c2_b_stage_bytes() { return 2 /*planes*/ * 64 * 32 * 4; }   // 16 KB: [W | W_lo] of one tap
 template <bool DGRAD> constexpr int c2_b_stages() { return DGRAD ? 3 : 6; }
 template <bool DGRAD> constexpr int c2_slabs() { return DGRAD ? 4 : 2; }                        // planes x channel blocks
@@ -59,10 +66,10 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   constexpr int CBLOCKS = DGRAD ? 2 : 1;
   constexpr int kBStages = c2_b_stages<DGRAD>();
   constexpr int kBStage = c2_b_stage_bytes<DGRAD>();
-  constexpr int kBPlane = kBStage / 2;                       // 8 KB: forward 2 boxes {32 n, 32 k}; dgrad 2 boxes {32 k, 32 c} (one per K block)
-  constexpr int kAccCols = 2 * N_OUT;                        // two M tiles side by side
-  constexpr int kTmemCols = DGRAD ? 256 : 512;               // [S | M0 | M1] x two M tiles = 6 * N_OUT, as a power of two
-  constexpr uint32_t idesc = make_idesc(2, N_OUT, false, !DGRAD);
+  constexpr int kAccCols = 4 * N_OUT;                        // one chunk accumulator: [main | small] x two M tiles
+  constexpr int kTmemCols = 2 * kAccCols;                    // two of them: 512 (forward) / 256 (data gradient)
+  constexpr uint32_t idesc_wide = make_idesc(2, 2 * N_OUT, false, !DGRAD);   // A x [W | W_lo]
+  constexpr uint32_t idesc_narrow = make_idesc(2, N_OUT, false, !DGRAD);     // A_lo x W
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -74,9 +81,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   uint64_t* b_empty = b_full + kBStages;
   uint64_t* tmem_full = b_empty + kBStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;       // [2]
-  uint64_t* s_full = tmem_empty + 2;
-  uint64_t* s_empty = s_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chunks_per_tile = (25 + chunk_taps - 1) / chunk_taps;
@@ -98,7 +103,6 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
       mbar_init(slab_full, 1); mbar_init(slab_empty, 1);
       for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
       for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 8); }
-      mbar_init(s_full, 1); mbar_init(s_empty, 8);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -111,7 +115,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
-  // TMEM columns: S of M tile h at h * N_OUT; main accumulator a of M tile h at kAccCols * (1 + a) + h * N_OUT
+  // TMEM columns: chunk accumulator a, M tile h at a * kAccCols + h * 2 * N_OUT: [main N_OUT | small N_OUT]
 
   if (warp == 0) {
     // ===== TMA producer: one slab set per image, then the 25 taps' weight tiles =====
@@ -132,13 +136,13 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
 #pragma unroll
           for (int pl = 0; pl < 2; ++pl) {
             const CUtensorMap* mw = pl ? &map_w_lo : &map_w;
-            uint8_t* dst = smem_b + s * kBStage + pl * kBPlane;
-            if (!DGRAD) {            // rows = K (the tap's 32 input channels), columns = n: two MN-major boxes of 32 n
-              tma_load_2d(dst, mw, &b_full[s], 0, tap * 32);
-              tma_load_2d(dst + 4096, mw, &b_full[s], 32, tap * 32);
-            } else {                 // rows = the tap's 32 input channels (N of this GEMM), columns = K: one box per K block
-              tma_load_2d(dst, mw, &b_full[s], 0, tap * 32);
-              tma_load_2d(dst + 4096, mw, &b_full[s], 32, tap * 32);
+            uint8_t* dst = smem_b + s * kBStage;
+            if (!DGRAD) {            // rows = K (the tap's 32 input channels), columns = n: two MN-major boxes of 32 n per plane
+              tma_load_2d(dst + pl * 8192, mw, &b_full[s], 0, tap * 32);
+              tma_load_2d(dst + pl * 8192 + 4096, mw, &b_full[s], 32, tap * 32);
+            } else {                 // rows = the tap's 32 input channels (N of this GEMM), columns = K: per K block [W | W_lo]
+              tma_load_2d(dst + pl * 4096, mw, &b_full[s], 0, tap * 32);
+              tma_load_2d(dst + 8192 + pl * 4096, mw, &b_full[s], 32, tap * 32);
             }
           }
         }
@@ -153,11 +157,9 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     const uint32_t b_full0 = smem_u32(b_full), b_empty0 = smem_u32(b_empty);
     const uint32_t tmem_full0 = smem_u32(tmem_full), tmem_empty0 = smem_u32(tmem_empty);
     const uint32_t slab_full0 = smem_u32(slab_full), slab_empty0 = smem_u32(slab_empty);
-    const uint32_t s_full0 = smem_u32(s_full), s_empty0 = smem_u32(s_empty);
     uint32_t bs = 0, bph = 0, tile = 0, chunk = 0;
     for (int img = blockIdx.x; img < Nimg; img += gridDim.x, ++tile) {
       mbar_wait_addr(slab_full0, tile & 1);
-      if (tile > 0) mbar_wait_addr(s_empty0, (tile - 1) & 1);                    // S of the previous image has been read
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       for (int tap = 0; tap < 25; ++tap) {
         const bool chunk_start = tap % chunk_taps == 0;
@@ -174,21 +176,18 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         if (elect_one()) {
 #pragma unroll
           for (int cb = 0; cb < CBLOCKS; ++cb) {
-            // A: slab [plane 0 | plane 1][cb]; B: forward one [W | W_lo] tile per tap, dgrad K block cb of it
+            // A: slab [plane 0 | plane 1][cb]; B: [W | W_lo] of the tap (forward) / of K block cb of the tap (dgrad)
             const uint32_t ax = desc_lo(slab0 + cb * kC2SlabBytes, 16) + shift;
             const uint32_t ax_lo = desc_lo(slab0 + (CBLOCKS + cb) * kC2SlabBytes, 16) + shift;
-            const uint32_t bx = bw + (DGRAD ? cb * (4096 >> 4) : 0);
-            const uint32_t bx_lo = bx + (kBPlane >> 4);
+            const uint32_t bx = bw + (DGRAD ? cb * (8192 >> 4) : 0);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-              const uint32_t d_small = tmem_base + h * N_OUT;
-              const uint32_t d_main = tmem_base + kAccCols * (1 + acc) + h * N_OUT;
+              const uint32_t d = tmem_base + acc * kAccCols + h * 2 * N_OUT;
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint32_t ak = h * 1024 + 2 * k, bk = kStepB * k;
-                umma2<1>(d_small, ax_lo + ak, hi_a, bx + bk, hi_b, idesc, !(tap == 0 && cb == 0 && k == 0));
-                umma2<1>(d_small, ax + ak, hi_a, bx_lo + bk, hi_b, idesc, true);
-                umma2<1>(d_main, ax + ak, hi_a, bx + bk, hi_b, idesc, !(chunk_start && cb == 0 && k == 0));
+                umma2<1>(d, ax + ak, hi_a, bx + bk, hi_b, idesc_wide, !(chunk_start && cb == 0 && k == 0));   // main | A*W_lo
+                umma2<1>(d + N_OUT, ax_lo + ak, hi_a, bx + bk, hi_b, idesc_narrow, true);                      // += A_lo*W
               }
             }
           }
@@ -199,7 +198,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         if ((tap + 1) % chunk_taps == 0 || tap == 24) {
           if (elect_one()) {
             umma_commit_addr(tmem_full0 + acc * 8);
-            if (tap == 24) { umma_commit_addr(s_full0); umma_commit_addr(slab_empty0); }
+            if (tap == 24) umma_commit_addr(slab_empty0);
           }
           __syncwarp();
           ++chunk;
@@ -209,13 +208,13 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   } else {
     // ===== accumulate in registers + epilogue: warp = (TMEM lane quarter q, M tile h), thread = one grid position =====
     const int q = warp & 3, h = (warp - 2) >> 2;
-    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + h * N_OUT;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + h * 2 * N_OUT;
     const int m = h * 128 + q * 32 + lane;
     const int oh = m / kC2PW, ow = m - oh * kC2PW;
     const bool valid = oh < kC2H && ow < kC2W;
     Epilogue epi = {bias, nullptr, 0, nullptr, 1, 0, nullptr};
-    uint32_t tile = 0, chunk = 0;
-    for (int img = blockIdx.x; img < Nimg; img += gridDim.x, ++tile) {
+    uint32_t chunk = 0;
+    for (int img = blockIdx.x; img < Nimg; img += gridDim.x) {
       float sum[N_OUT];
 #pragma unroll
       for (int u = 0; u < N_OUT; ++u) sum[u] = 0.f;
@@ -224,28 +223,16 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         mbar_wait(&tmem_full[acc], (chunk >> 1) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-        for (int c0 = 0; c0 < N_OUT; c0 += 32) {
+        for (int c0 = 0; c0 < 2 * N_OUT; c0 += 32) {           // main columns, then the small ones
           uint32_t rr[32];
-          tmem_ld32(lane_base + kAccCols * (1 + acc) + c0, rr);
+          tmem_ld32(lane_base + acc * kAccCols + c0, rr);
 #pragma unroll
-          for (int u = 0; u < 32; ++u) sum[c0 + u] = __fadd_rn(sum[c0 + u], __uint_as_float(rr[u]));
+          for (int u = 0; u < 32; ++u) sum[(c0 + u) % N_OUT] = __fadd_rn(sum[(c0 + u) % N_OUT], __uint_as_float(rr[u]));
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       }
-      mbar_wait(s_full, tile & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
-      for (int c0 = 0; c0 < N_OUT; c0 += 32) {
-        uint32_t rr[32];
-        tmem_ld32(lane_base + c0, rr);
-#pragma unroll
-        for (int u = 0; u < 32; ++u) sum[c0 + u] = __fadd_rn(sum[c0 + u], __uint_as_float(rr[u]));
-      }
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_empty);
       if (valid) {
         const size_t row = (static_cast<size_t>(img) * kC2H + oh) * kC2W + ow;
         store_row_regs<N_OUT>(sum, out + row * N_OUT, mask ? mask + row * N_OUT : nullptr, 0, N_OUT, true, epi);

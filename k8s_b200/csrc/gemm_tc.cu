@@ -490,9 +490,11 @@ static int launch_conv2_x3(tfg_job* j, const char* name, const CUtensorMap& x, c
     if (e != cudaSuccess) return fail_cuda(j, e, name);
     attr_set = true;
   }
-  // a chunk = 2 K blocks of the main product: two taps of 32 input channels forward, one tap of 64 backward
+  // a chunk of the main product: three taps of 32 input channels forward (12 accumulating MMAs; the [main |
+  // small] accumulator is twice as wide to read back, so the chunk is longer than the GEMM's), one tap of 64
+  // channels backward (8)
   tc::conv2_x3_kernel<DGRAD><<<std::min(B, kNumSMs), tc::kC2Threads, smem, st>>>(x, x_lo, w, w_lo, out, bias, mask, B,
-                                                                                  DGRAD ? 1 : 2);
+                                                                                  DGRAD ? 1 : 3);
   TC_LAUNCH_OK(j, name);
   return TFG_OK;
 }
