@@ -293,6 +293,87 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
   }
 }
 
+// ---- 3xTF32 path: 2x2 max-pool + relu and its gradient, four channels per thread ---------------------
+// y2[B,14,14,64] (bias included) -> a2[B,7,7,64] (+ low-order plane) and the 2-bit argmax.  16-byte loads
+// and stores; a thread owns one pooled position and four channels.
+__global__ void __launch_bounds__(256)
+pool_relu_x3_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t* __restrict__ idx,
+                    float* __restrict__ a_lo, int B) {
+  const long long total = (long long)B * 49 * 16;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i & 15);
+    const long long pos = i >> 4;
+    const int pw = (int)(pos % 7), ph = (int)((pos / 7) % 7);
+    const long long b = pos / 49;
+    float best[4];
+    int arg[4];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const float4 v4 = *reinterpret_cast<const float4*>(y + ((b * 14 + 2 * ph + dy) * 14 + 2 * pw + dx) * 64 + q * 4);
+        const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if ((dy | dx) == 0 || v[u] > best[u]) { best[u] = v[u]; arg[u] = dy * 2 + dx; }
+      }
+    float r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = fmaxf(best[u], 0.f);
+    *reinterpret_cast<float4*>(a + i * 4) = make_float4(r[0], r[1], r[2], r[3]);
+    *reinterpret_cast<float4*>(a_lo + i * 4) = make_float4(tc::tf32_lo(r[0]), tc::tf32_lo(r[1]), tc::tf32_lo(r[2]), tc::tf32_lo(r[3]));
+    *reinterpret_cast<uchar4*>(idx + i * 4) = make_uchar4((unsigned char)arg[0], (unsigned char)arg[1], (unsigned char)arg[2],
+                                                          (unsigned char)arg[3]);
+  }
+}
+
+// Gradient of the above: gp[B,7,7,64] (gradient at the pooled, post-relu map) -> the dense gradient
+// gy[B,14,14,64] at the convolution output (+ low-order plane): the masked value at the argmax position, 0 at
+// the other three.  The masked pooled gradient is also what the bias gradient sums: every thread keeps the sum
+// of its four channels over its positions, a block adds its 16 position lanes in lane order, and
+// bias_partial[block][64] goes to reduce_rows_kernel -- the separate column-sum pass over da2 is gone.
+constexpr int kUnpoolBlocks = 2 * kNumSMs;
+__global__ void __launch_bounds__(256)
+unpool_x3_kernel(const float* __restrict__ gp, const float* __restrict__ a, const uint8_t* __restrict__ idx,
+                 float* __restrict__ gy, float* __restrict__ gy_lo, float* __restrict__ bias_partial, int B) {
+  __shared__ float4 red[16][16];
+  const long long total = (long long)B * 49 * 16;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int q = (int)(i & 15);                      // == threadIdx.x & 15: the stride is a multiple of 16
+    const long long pos = i >> 4;
+    const int pw = (int)(pos % 7), ph = (int)((pos / 7) % 7);
+    const long long b = pos / 49;
+    const float4 g4 = *reinterpret_cast<const float4*>(gp + i * 4), a4 = *reinterpret_cast<const float4*>(a + i * 4);
+    const uchar4 k4 = *reinterpret_cast<const uchar4*>(idx + i * 4);
+    const float g[4] = {a4.x > 0.f ? g4.x : 0.f, a4.y > 0.f ? g4.y : 0.f, a4.z > 0.f ? g4.z : 0.f, a4.w > 0.f ? g4.w : 0.f};
+    const int k[4] = {k4.x, k4.y, k4.z, k4.w};
+    acc.x += g[0]; acc.y += g[1]; acc.z += g[2]; acc.w += g[3];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int w = dy * 2 + dx;
+        const long long m = ((b * 14 + 2 * ph + dy) * 14 + 2 * pw + dx) * 64 + q * 4;
+        float v[4], l[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { v[u] = k[u] == w ? g[u] : 0.f; l[u] = k[u] == w ? tc::tf32_lo(g[u]) : 0.f; }
+        *reinterpret_cast<float4*>(gy + m) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(gy_lo + m) = make_float4(l[0], l[1], l[2], l[3]);
+      }
+  }
+  red[threadIdx.x >> 4][threadIdx.x & 15] = acc;
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    float4 s = red[0][threadIdx.x];
+#pragma unroll
+    for (int r = 1; r < 16; ++r) {
+      const float4 v = red[r][threadIdx.x];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(bias_partial + blockIdx.x * 64 + threadIdx.x * 4) = s;
+  }
+}
 
 // ---- model state of the tensor path --------------------------------------------------------
 // Operands are the row-major buffers themselves, cast to operand precision; which index is
@@ -323,7 +404,7 @@ struct TcSlot {            // per replica slot: operand copies of activations + 
 };
 
 constexpr int kSplitW2Tc = 21;   // 7 M-tiles x 21 K-splits = 147 CTAs on 148 SMs
-constexpr int kSplitFc1Fwd = 7;  // B = 128: 16 N-tiles x 7 K-splits = 112 CTAs instead of 16
+constexpr int kSplitFc1Fwd = 9;  // B = 128: 16 N-tiles x 9 K-splits = 144 CTAs on 148 SMs
 constexpr int kSplitFc1Dgrad = 3;  // 49 N-tiles x 3 = 147 CTAs
 
 static inline int blocks_for(long long n, int per = 256) {
@@ -535,7 +616,12 @@ static int tc_forward_t(tfg_job* j, int slot) {
     TC_LAUNCH_OK(j, "im2col_lp_kernel");
     if ((rc = launch_tc(j, t->conv2_fwd, kind, st))) return rc;
   }
-  if ((rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) return rc;     // also drops the operand copy / low-order plane of a2
+  if (m->math == TFG_MATH_TF32X3) {
+    pool_relu_x3_kernel<<<blocks_for((long long)B * 49 * 16), 256, 0, st>>>(s.y2, s.a2, s.idx2, t->a2_lo, B);
+    TC_LAUNCH_OK(j, "pool_relu_x3_kernel");
+  } else if ((rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) {     // also drops the operand copy of a2
+    return rc;
+  }
   return launch_tc(j, t->fc1_fwd, kind, st);
 }
 
@@ -550,8 +636,14 @@ static int tc_backward_t(tfg_job* j, int slot) {
   const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
   if ((rc = launch_tc(j, t->fc1_wgrad, kind, st))) return rc;   // dh1 (bf16 / low-order plane) came from fc2_bwd_kernel
   if ((rc = launch_tc(j, t->fc1_dgrad, kind, st))) return rc;
-  unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
-  TC_LAUNCH_OK(j, "unpool_lp_kernel");
+  if (m->math == TFG_MATH_TF32X3) {
+    unpool_x3_kernel<<<kUnpoolBlocks, 256, 0, st>>>(s.da2, s.a2, s.idx2, (float*)t->dy2_lp, t->dy2_lo, t->partial, B);
+    TC_LAUNCH_OK(j, "unpool_x3_kernel");
+    if ((rc = mnist_reduce_rows(j, t->partial, kUnpoolBlocks, 64, j->grads[slot] + j->vars[m->var[3]].offset))) return rc;   // db2
+  } else {
+    unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
+    TC_LAUNCH_OK(j, "unpool_lp_kernel");
+  }
   if (m->math == TFG_MATH_TF32X3) {
     if ((rc = launch_conv2_wgrad_x3(j, t, j->grads[slot] + j->vars[m->var[2]].offset, B, st))) return rc;
     // dx straight into g1m, masked by a1 > 0: no dcol, no col2im

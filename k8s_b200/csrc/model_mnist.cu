@@ -690,6 +690,12 @@ int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes) {
   return TFG_OK;
 }
 
+int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out) {
+  reduce_rows_kernel<<<(C + 31) / 32, 256, 0, j->stream>>>(in, R, C, C, out, C, nullptr);
+  LAUNCH_OK(j, "reduce_rows_kernel");
+  return TFG_OK;
+}
+
 int mnist_pool2(tfg_job* j, int slot, void* a2_bf16, float* a2_lo) {
   MnistModel* m = j->model;
   MnistSlot& s = m->slots[slot];
@@ -768,8 +774,8 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     if ((rc = sgemm(j, "gemm conv2 dgrad", s.dy2, true, 64, 1, par(2), false, 1, 64, s.dcol, M2, 800, 64,
                     GemmEpi{nullptr, nullptr, 0}, 1, nullptr))) return rc;
   }
-  // db2 = sum over pooled positions of the masked pooled gradient
-  if ((rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
+  // db2 = sum over pooled positions of the masked pooled gradient (3xTF32: taken by the un-pooling kernel)
+  if (m->math != TFG_MATH_TF32X3 && (rc = colsum(j, s.da2, s.a2, grd(3), B * 49, 64, s.scratch))) return rc;
   if (m->math == TFG_MATH_TF32X3) {
     // the implicit data-gradient kernel wrote g1m itself (conv_x3.cuh)
   } else if (m->math == TFG_MATH_BF16) {   // the tensor path's dgrad GEMM stored dcol as bf16 (mnist_tc_prepare)

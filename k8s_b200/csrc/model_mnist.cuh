@@ -60,6 +60,8 @@ struct MnistModel {
 
 // model_mnist.cu: y2 -> a2, idx2 (shared by both math paths)
 int mnist_pool2(tfg_job* j, int slot, void* a2_bf16, float* a2_lo);
+// out[c] = sum over the R rows of in[R, C], rows added in a fixed order (reduce_rows_kernel)
+int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out);
 
 // gemm_tc.cu
 int mnist_tc_build(tfg_job* j);
