@@ -449,19 +449,36 @@ conv2_wgrad_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
   }
 }
 
-// dW[row, :] = sum over the partials of the row's M-tile group, in z order (deterministic)
+// dW[row, :] = sum over the partials of the row's M-tile group.  Four lanes share an output float4: lane l
+// adds the partials of its quarter of the z range in z order, and the four lane sums are combined as
+// (l0 + l1) + (l2 + l3) -- a fixed order, so the result is reproducible; four times the CTAs and a
+// quarter of the dependent-load chain of one thread per output (this reduction is latency-bound).
 __global__ void __launch_bounds__(256)
 conv2_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, const __grid_constant__ WgradPlan plan) {
-  const int i = blockIdx.x * 256 + threadIdx.x;              // float4 index into [800][64]
-  if (i >= 800 * 16) return;
-  const int g = c2_wgrad_group_of_row(i >> 4);
-  const int nz = plan.cta0[g + 1] - plan.cta0[g];
+  const int gi = blockIdx.x * 256 + threadIdx.x;
+  const int i = gi >> 2, l = gi & 3;                          // float4 index into [800][64], lane of the group
+  const bool live = i < 800 * 16;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int zz = 0; zz < nz; ++zz) {
-    const float4 v = reinterpret_cast<const float4*>(partial)[static_cast<size_t>(zz) * (800 * 16) + i];
-    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  if (live) {
+    const int g = c2_wgrad_group_of_row(i >> 4);
+    const int nz = plan.cta0[g + 1] - plan.cta0[g];
+    const int per = (nz + 3) >> 2;
+    for (int zz = l * per; zz < min(nz, (l + 1) * per); ++zz) {
+      const float4 v = reinterpret_cast<const float4*>(partial)[static_cast<size_t>(zz) * (800 * 16) + i];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
   }
-  reinterpret_cast<float4*>(dw)[i] = s;
+  // (l0 + l1), (l2 + l3), then their sum; lanes of a group are adjacent threads of one warp
+  float4 o;
+  o.x = __shfl_xor_sync(0xffffffffu, s.x, 1); o.y = __shfl_xor_sync(0xffffffffu, s.y, 1);
+  o.z = __shfl_xor_sync(0xffffffffu, s.z, 1); o.w = __shfl_xor_sync(0xffffffffu, s.w, 1);
+  if (l & 1) { float4 t = s; s = o; o = t; }                   // s = the even lane's sum, o = the odd lane's: same operand order in both lanes
+  s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
+  o.x = __shfl_xor_sync(0xffffffffu, s.x, 2); o.y = __shfl_xor_sync(0xffffffffu, s.y, 2);
+  o.z = __shfl_xor_sync(0xffffffffu, s.z, 2); o.w = __shfl_xor_sync(0xffffffffu, s.w, 2);
+  if (l & 2) { float4 t = s; s = o; o = t; }
+  s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
+  if (live && l == 0) reinterpret_cast<float4*>(dw)[i] = s;
 }
 
 }  // namespace tc

@@ -591,7 +591,7 @@ static int launch_conv2_wgrad_x3(tfg_job* j, TcSlot* t, float* dw, int B, cudaSt
   tc::conv2_wgrad_x3_kernel<<<t->wplan.cta0[4], tc::kC2Threads, smem, st>>>(t->c2w_x, t->c2w_x_lo, t->c2w_dy, t->c2w_dy_lo,
                                                                             t->wpartial, B, t->wplan);
   TC_LAUNCH_OK(j, "conv2 wgrad x3");
-  tc::conv2_wgrad_reduce_kernel<<<(800 * 16 + 255) / 256, 256, 0, st>>>(t->wpartial, dw, t->wplan);
+  tc::conv2_wgrad_reduce_kernel<<<(800 * 16 * 4 + 255) / 256, 256, 0, st>>>(t->wpartial, dw, t->wplan);
   TC_LAUNCH_OK(j, "conv2 wgrad reduce");
   return TFG_OK;
 }

@@ -520,24 +520,25 @@ colsum_wide_kernel(const float* __restrict__ in, const float* __restrict__ mask,
   if (ry == 0 && c < C) partial[(size_t)blockIdx.y * C + c] = ((red[0][cx] + red[1][cx]) + red[2][cx]) + red[3][cx];
 }
 
-// out[c] = sum over rows r of in[r*stride + c], rows added in a fixed order (lane ty takes rows
-// ty, ty+8, ...; the 8 lane sums are then added 0..7).  Columns below split_c go to out0, the
-// rest to out1.  Block = 32 columns x 8 row lanes, so reads stay 128-byte coalesced.
-__global__ void __launch_bounds__(256)
+// out[c] = sum over rows r of in[r*stride + c], rows added in a fixed order (row lane ty takes rows
+// ty, ty+32, ...; the 32 lane sums are then added 0..31).  Columns below split_c go to out0, the
+// rest to out1.  Block = 32 columns x 32 row lanes, so reads stay 128-byte coalesced and a thread's
+// chain is R / 32 loads long (these reductions are latency-bound: few columns, a few hundred rows).
+__global__ void __launch_bounds__(1024)
 reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long stride, float* __restrict__ out0,
                    int split_c, float* __restrict__ out1) {
-  __shared__ float red[8][32];
+  __shared__ float red[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
   float s = 0.f;
   if (c < C)
-    for (int r = ty; r < R; r += 8) s += in[(size_t)r * stride + c];
+    for (int r = ty; r < R; r += 32) s += in[(size_t)r * stride + c];
   red[ty][tx] = s;
   __syncthreads();
   if (ty == 0 && c < C) {
     float t = red[0][tx];
 #pragma unroll
-    for (int k = 1; k < 8; ++k) t += red[k][tx];
+    for (int k = 1; k < 32; ++k) t += red[k][tx];
     if (c < split_c) out0[c] = t; else out1[c - split_c] = t;
   }
 }
@@ -590,7 +591,7 @@ static int colsum(tfg_job* j, const float* in, const float* mask, float* out, in
   cudaStream_t s = j->stream;
   colsum_wide_kernel<<<dim3(col_blocks, chunks), 256, 0, s>>>(in, mask, partial, R, C, rows_per_chunk);
   LAUNCH_OK(j, "colsum_wide_kernel");
-  reduce_rows_kernel<<<(C + 31) / 32, 256, 0, s>>>(partial, chunks, C, C, out, C, nullptr);
+  reduce_rows_kernel<<<(C + 31) / 32, 1024, 0, s>>>(partial, chunks, C, C, out, C, nullptr);
   LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
@@ -691,7 +692,7 @@ int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes) {
 }
 
 int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out) {
-  reduce_rows_kernel<<<(C + 31) / 32, 256, 0, j->stream>>>(in, R, C, C, out, C, nullptr);
+  reduce_rows_kernel<<<(C + 31) / 32, 1024, 0, j->stream>>>(in, R, C, C, out, C, nullptr);
   LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
@@ -789,7 +790,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   conv1_bwd_kernel<<<kConv1Split * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  reduce_rows_kernel<<<(832 + 31) / 32, 256, 0, st>>>(s.scratch, kConv1Split * B, 832, 832, grd(0), 800, grd(1));
+  reduce_rows_kernel<<<(832 + 31) / 32, 1024, 0, st>>>(s.scratch, kConv1Split * B, 832, 832, grd(0), 800, grd(1));
   LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
