@@ -593,7 +593,10 @@ def measure(a, model: str, n: int, rank: int, local: int, lib, L, torch, dist, s
         total = sum(v["ms"] for v in prof.values()) or 1.0
         # the cross-rank barrier is waiting time (the slowest rank's skew), not work: it is reported as its
         # share of the step, and the roofline kernel is the largest one that moves bytes or does math
-        work = {k_: v for k_, v in prof.items() if k_ != "barrier_kernel"} or prof
+        # ... and so is, at N > 1, the exchange kernel's time in this per-kernel pass (it waits inside the kernel
+        # for the slowest rank; its bandwidth against the NVLink roofline is scripts/ps_exchange_sweep.py's job)
+        waits = ("barrier_kernel",) + (("push_apply_pull_kernel",) if n > 1 else ())
+        work = {k_: v for k_, v in prof.items() if k_ not in waits} or prof
         top = max(work, key=lambda k_: work[k_]["ms"])
         bound, amount, peak_note = algorithmic_work(top, B, 3274634, a.opt, n, math, peaks)
         per_launch_ms = prof[top]["ms"] / prof[top]["count"]
@@ -617,6 +620,15 @@ def measure(a, model: str, n: int, rank: int, local: int, lib, L, torch, dist, s
                         algorithmic_bytes=amount)
         if "barrier_kernel" in prof:
             roof["barrier_share_of_step"] = prof["barrier_kernel"]["ms"] / total
+        if n > 1 and "push_apply_pull_kernel" in prof:
+            # bytes one GPU sends (and receives) per step over NVLink: its shard's gradient from the N-1 other
+            # replicas, the new values (and their operand shadow) to the N-1 other ranks
+            n_params = 25557032 if resnet else 3274634
+            shadow = 2 if math == "bf16" else 4 if math == "tf32x3" else 0
+            roof["exchange"] = {"share_of_step_incl_wait": prof["push_apply_pull_kernel"]["ms"] / total,
+                                "nvlink_bytes_per_gpu_per_direction": (8 + shadow) * n_params * (n - 1) / n,
+                                "note": "the kernel waits in-kernel for the slowest rank; see scripts/ps_exchange_sweep.py "
+                                        "for its bandwidth against the measured link"}
         out["roofline"] = roof
         out["kernels"] = {k_: {"count": v["count"], "ms_per_launch": v["ms"] / v["count"],
                                "share": v["ms"] / total} for k_, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
