@@ -269,7 +269,7 @@ int tfg_ipc_close(void* dev_ptr);
  * per_process_gpu_memory_fraction = 1.0, so a later cudaMalloc in that process fails), or
  * a step loop that must not take the device-wide synchronisation cudaMalloc/cudaFree
  * imply.  For them the scratch lives inside the library image, in a fixed device array of
- * TFG_SPARSE_STATIC_SCRATCH_BYTES (about 1.03 MiB) that every GPU using the library keeps
+ * TFG_SPARSE_STATIC_SCRATCH_BYTES (about 1.15 MiB) that every GPU using the library keeps
  * until the process exits.  The caller still passes table, ids and rows; results are
  * identical to tfg_sparse_scatter_sub given tfg_sparse_scratch_bytes(n) of scratch (every
  * duplicate applied in order).
@@ -284,7 +284,7 @@ int tfg_ipc_close(void* dev_ptr);
  *     threads -- race on it: issue them on one stream, or serialise them yourself.  (The
  *     address look-up itself is safe from several host threads.) */
 #define TFG_SPARSE_STATIC_MAX_IDS 65536
-#define TFG_SPARSE_STATIC_SCRATCH_BYTES 1081600
+#define TFG_SPARSE_STATIC_SCRATCH_BYTES 1204480
 int tfg_sparse_scatter_sub_static(float* table_dev, int64_t vocab, int dim, int n_shards,
                                   int shard, int strategy, const int64_t* ids_dev, int64_t n,
                                   const float* rows_dev, float scale, void* stream);

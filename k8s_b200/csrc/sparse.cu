@@ -11,9 +11,12 @@
 #include <atomic>
 #include <cstring>
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace tfg {
+namespace cg = cooperative_groups;
 
 // Where the ids and the update rows of a (possibly multi-source) batch live.  A batch is the
 // concatenation of n_src equally long pieces, source after source -- on several GPUs the pieces are the
@@ -37,8 +40,11 @@ struct TableSrc {               // the shards of one table: shard k's rows start
 
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
-constexpr int kKeysPerWarp = 256;
-constexpr int kSortTile = kSortWarps * kKeysPerWarp;  // 2048 keys per block
+constexpr int kKeysPerWarp = 512;
+constexpr int kSortTile = kSortWarps * kKeysPerWarp;  // 4096 keys per block (2048: 10 % slower at a million ids, measured)
+constexpr int kMaxDigitBits = 11;                     // 2048 bins: 8 warps x 2048 counters = 64 KB of shared memory
+constexpr int kMaxBins = 1 << kMaxDigitBits;
+constexpr int kMaxPasses = 3;                         // 32-bit keys
 
 struct Part {
   long long vocab;
@@ -155,44 +161,55 @@ make_keys_kernel(Part pt, const __grid_constant__ IdSrc ids, long long n, uint32
   }
 }
 
-// digit counts of this warp's 256-key sub-tile into cnt[warp][256]
-__device__ __forceinline__ void warp_digit_counts(const uint32_t* keys, long long n, int shift,
-                                                  uint32_t (*cnt)[256]) {
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int d = lane; d < 256; d += 32) cnt[w][d] = 0;
-  __syncwarp();
-  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
-  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
-    long long i = base + c * 32 + lane;
-    if (i < n) atomicAdd(&cnt[w][(keys[i] >> shift) & 255u], 1u);
-  }
-  __syncwarp();
-}
-
+// ---- owned ids only ---------------------------------------------------------------------------
+// With several shards most ids of a batch belong to other shards (all but 1/N of them when every GPU
+// of the box owns one).  Three small kernels keep the owned ones, in batch order, before anything is
+// sorted: (1) row keys of every id (sentinel = not mine) and the count per tile, (2) scan of the tile
+// counts, (3) stable compaction of (key, position).  The number kept stays on the device (*n_live);
+// the kernels after this read it there, under launch shapes sized for the whole batch.
 __global__ void __launch_bounds__(kSortThreads)
-sort_hist_kernel(const uint32_t* __restrict__ keys, long long n, int shift, uint32_t* __restrict__ hist,
-                 int n_blocks) {
-  __shared__ uint32_t cnt[kSortWarps][256];
-  warp_digit_counts(keys, n, shift, cnt);
-  __syncthreads();
-  for (int d = threadIdx.x; d < 256; d += kSortThreads) {
-    uint32_t s = 0;
+owned_keys_kernel(Part pt, const __grid_constant__ IdSrc ids, long long n, uint32_t sentinel,
+                  uint32_t* __restrict__ keys_all, uint32_t* __restrict__ tile_count) {
+  __shared__ uint32_t warp_cnt[kSortWarps];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
+  uint32_t mine = 0;
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    const long long i = base + c * 32 + lane;
+    if (i >= n) break;
+    const long long id = ids.at(i);
+    uint32_t k = sentinel;
+    if (id >= 0 && id < pt.vocab) {
+      int sh;
+      long long row;
+      locate(pt, id, &sh, &row);
+      if (sh == pt.shard) { k = (uint32_t)row; ++mine; }
+    }
+    keys_all[i] = k;
+  }
 #pragma unroll
-    for (int w = 0; w < kSortWarps; ++w) s += cnt[w][d];
-    hist[(size_t)d * n_blocks + blockIdx.x] = s;  // digit-major
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if (lane == 0) warp_cnt[w] = mine;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int x = 0; x < kSortWarps; ++x) t += warp_cnt[x];
+    tile_count[blockIdx.x] = t;
   }
 }
 
-// exclusive scan of hist[256 * n_blocks] in place (one block; n_blocks is n / 2048)
-__global__ void __launch_bounds__(1024) sort_scan_kernel(uint32_t* hist, long long total) {
+// exclusive scan of the tile counts in place (one block); the total goes to *n_live
+__global__ void __launch_bounds__(1024) owned_scan_kernel(uint32_t* tile_count, int n_tiles, uint32_t* n_live) {
   __shared__ uint32_t warp_sums[32];
   __shared__ uint32_t carry;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (long long base = 0; base < total; base += 1024) {
-    long long i = base + threadIdx.x;
-    uint32_t v = i < total ? hist[i] : 0u, x = v;
+  for (int base = 0; base < n_tiles; base += 1024) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < n_tiles ? tile_count[i] : 0u;
+    uint32_t x = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
@@ -201,54 +218,155 @@ __global__ void __launch_bounds__(1024) sort_scan_kernel(uint32_t* hist, long lo
     if (lane == 31) warp_sums[w] = x;
     __syncthreads();
     if (w == 0) {
-      uint32_t s = warp_sums[lane], t = s;
+      uint32_t sm = warp_sums[lane], t = sm;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         uint32_t y = __shfl_up_sync(0xffffffffu, t, o);
         if (lane >= o) t += y;
       }
-      warp_sums[lane] = t - s;  // exclusive prefix of warp totals
+      warp_sums[lane] = t - sm;
     }
     __syncthreads();
-    uint32_t excl = carry + warp_sums[w] + x - v;
-    if (i < total) hist[i] = excl;
+    const uint32_t excl = carry + warp_sums[w] + x - v;
+    if (i < n_tiles) tile_count[i] = excl;
     __syncthreads();
     if (threadIdx.x == 1023) carry = excl + v;
     __syncthreads();
+  }
+  if (threadIdx.x == 0) *n_live = carry;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+owned_compact_kernel(const uint32_t* __restrict__ keys_all, long long n, uint32_t sentinel,
+                     const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  __shared__ uint32_t warp_cnt[kSortWarps];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
+  uint32_t mine = 0;
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    const long long i = base + c * 32 + lane;
+    mine += __popc(__ballot_sync(0xffffffffu, i < n && keys_all[i] != sentinel));
+  }
+  if (lane == 0) warp_cnt[w] = mine;
+  __syncthreads();
+  uint32_t pos = tile_off[blockIdx.x];
+  for (int x = 0; x < w; ++x) pos += warp_cnt[x];
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    const long long i = base + c * 32 + lane;
+    const uint32_t k = i < n ? keys_all[i] : sentinel;
+    const uint32_t keep = __ballot_sync(0xffffffffu, k != sentinel);
+    if (k != sentinel) {
+      const uint32_t at = pos + __popc(keep & ((1u << lane) - 1u));
+      keys[at] = k;
+      vals[at] = (uint32_t)i;
+    }
+    pos += __popc(keep);
+  }
+}
+
+// digit counts of this warp's sub-tile into cnt[warp * bins + digit]
+// *n_live, when given, is the number of keys (fewer than the launch was shaped for)
+__device__ __forceinline__ long long live_count(long long n, const uint32_t* n_live) { return n_live ? (long long)*n_live : n; }
+
+__device__ __forceinline__ void warp_digit_counts(const uint32_t* keys, long long n, int shift, int bins,
+                                                  uint32_t* cnt) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t* mine = cnt + w * bins;
+  for (int d = lane; d < bins; d += 32) mine[d] = 0;
+  __syncwarp();
+  const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
+  const uint32_t mask = (uint32_t)bins - 1u;
+  for (int c = 0; c < kKeysPerWarp / 32; ++c) {
+    long long i = base + c * 32 + lane;
+    if (i < n) atomicAdd(&mine[(keys[i] >> shift) & mask], 1u);
+  }
+  __syncwarp();
+}
+
+// hist[digit][block] (digit-major) and the digit totals of the whole array
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_kernel(const uint32_t* __restrict__ keys, long long n, const uint32_t* __restrict__ n_live, int shift, int bins,
+                 uint32_t* __restrict__ hist, int n_blocks, uint32_t* __restrict__ totals) {
+  extern __shared__ uint32_t cnt[];
+  n = live_count(n, n_live);
+  if (blockIdx.x * (long long)kSortTile >= n) return;   // tiles past the live keys: their hist columns are never read
+  warp_digit_counts(keys, n, shift, bins, cnt);
+  __syncthreads();
+  for (int d = threadIdx.x; d < bins; d += kSortThreads) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) s += cnt[w * bins + d];
+    hist[(size_t)d * n_blocks + blockIdx.x] = s;
+    if (s) atomicAdd(&totals[d], s);
+  }
+}
+
+// Exclusive scan of hist in place, one warp per digit: the digit's base is the sum of the totals of
+// the digits below it, then the warp scans its own row of n_blocks counts.  (The first version scanned
+// all bins * n_blocks entries with one block: 128 dependent iterations per pass for a million ids,
+// more time than the rest of the sort together.)
+__global__ void __launch_bounds__(kSortThreads)
+sort_scan_kernel(uint32_t* __restrict__ hist, long long n, const uint32_t* __restrict__ n_live, int n_blocks, int bins,
+                 const uint32_t* __restrict__ totals) {
+  const int live_blocks = (int)((live_count(n, n_live) + kSortTile - 1) / kSortTile);
+  const int lane = threadIdx.x & 31;
+  const int d = blockIdx.x * kSortWarps + (threadIdx.x >> 5);
+  if (d >= bins) return;
+  uint32_t run = 0;
+  for (int e = lane; e < d; e += 32) run += totals[e];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) run += __shfl_xor_sync(0xffffffffu, run, o);
+  uint32_t* row = hist + (size_t)d * n_blocks;
+  for (int b0 = 0; b0 < live_blocks; b0 += 32) {
+    const int b = b0 + lane;
+    const uint32_t v = b < live_blocks ? row[b] : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (b < live_blocks) row[b] = run + x - v;
+    run += __shfl_sync(0xffffffffu, x, 31);
   }
 }
 
 __global__ void __launch_bounds__(kSortThreads)
 sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                    long long n, int shift, const uint32_t* __restrict__ hist, int n_blocks,
+                    long long n, const uint32_t* __restrict__ n_live, int shift, int bins,
+                    const uint32_t* __restrict__ hist, int n_blocks,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
-  __shared__ uint32_t cnt[kSortWarps][256];
-  warp_digit_counts(keys_in, n, shift, cnt);
+  extern __shared__ uint32_t cnt[];
+  n = live_count(n, n_live);
+  if (blockIdx.x * (long long)kSortTile >= n) return;
+  warp_digit_counts(keys_in, n, shift, bins, cnt);
   __syncthreads();
   // cnt[w][d] <- global position of the first key of digit d in warp w's sub-tile
-  for (int d = threadIdx.x; d < 256; d += kSortThreads) {
+  for (int d = threadIdx.x; d < bins; d += kSortThreads) {
     uint32_t run = hist[(size_t)d * n_blocks + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < kSortWarps; ++w) {
-      uint32_t c = cnt[w][d];
-      cnt[w][d] = run;
+      uint32_t c = cnt[w * bins + d];
+      cnt[w * bins + d] = run;
       run += c;
     }
   }
   __syncthreads();
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t* mine = cnt + w * bins;
+  const uint32_t mask = (uint32_t)bins - 1u;
   const long long base = blockIdx.x * (long long)kSortTile + w * kKeysPerWarp;
   for (int c = 0; c < kKeysPerWarp / 32; ++c) {
     long long i = base + c * 32 + lane;
     bool live = i < n;
     uint32_t k = live ? keys_in[i] : 0u, v = live ? vals_in[i] : 0u;
-    uint32_t d = live ? ((k >> shift) & 255u) : 256u + lane;  // dead lanes match nobody
+    uint32_t d = live ? ((k >> shift) & mask) : (uint32_t)bins + lane;  // dead lanes match nobody
     uint32_t peers = __match_any_sync(0xffffffffu, d);
     uint32_t before = __popc(peers & ((1u << lane) - 1u));
     uint32_t pos = 0;
-    if (live) pos = cnt[w][d] + before;
+    if (live) pos = mine[d] + before;
     __syncwarp();
-    if (live && before == 0) cnt[w][d] += __popc(peers);  // lowest lane of the group
+    if (live && before == 0) mine[d] += __popc(peers);  // lowest lane of the group
     __syncwarp();
     if (live) {
       keys_out[pos] = k;
@@ -261,8 +379,9 @@ sort_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
 template <int VEC>
 __global__ void __launch_bounds__(256)
 scatter_sub_runs_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
-                        const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
-                        const __grid_constant__ RowSrc rows, float scale) {
+                        const uint32_t* __restrict__ vals, long long n, const uint32_t* __restrict__ n_live,
+                        uint32_t sentinel, const __grid_constant__ RowSrc rows, float scale) {
+  n = live_count(n, n_live);
   const int lane = threadIdx.x & 31;
   const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
   for (long long p = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
@@ -342,32 +461,37 @@ __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
   }
 }
 
-// One warp per sorted position; only run heads act.  Runs of at most kLongRun ids are applied
-// here, one id after another; longer runs are registered for the two kernels below.
-template <int VEC>
+// One group of LANES threads per sorted position (a whole warp for rows of more than 64 floats, fewer
+// lanes for narrower rows so that no lane idles); only run heads act.  Runs of at most kLongRun ids
+// are applied here, one id after another; longer runs are registered for the two kernels below.
+template <int VEC, int LANES>
 __global__ void __launch_bounds__(256)
 scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __restrict__ keys,
-                         const uint32_t* __restrict__ vals, long long n, uint32_t sentinel,
-                         const __grid_constant__ RowSrc rows, float scale, LongRun* __restrict__ runs,
+                         const uint32_t* __restrict__ vals, long long n, const uint32_t* __restrict__ n_live,
+                         uint32_t sentinel, const __grid_constant__ RowSrc rows, float scale, LongRun* __restrict__ runs,
                          ChunkDesc* __restrict__ chunks, uint32_t* __restrict__ counters) {
-  const int lane = threadIdx.x & 31;
-  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
-  for (long long p = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
+  static_assert(kLongRun % LANES == 0, "the probe walks whole groups");
+  n = live_count(n, n_live);
+  const auto tile = cg::tiled_partition<LANES>(cg::this_thread_block());
+  const int lane = tile.thread_rank();
+  constexpr uint32_t kAll = LANES == 32 ? 0xffffffffu : (1u << LANES) - 1u;
+  const long long groups = (long long)gridDim.x * (blockDim.x / LANES);
+  for (long long p = blockIdx.x * (long long)(blockDim.x / LANES) + threadIdx.x / LANES; p < n; p += groups) {
     const uint32_t k = keys[p];
     if (k == sentinel) continue;
     if (p > 0 && keys[p - 1] == k) continue;  // not the head of its run
     // run length, probing kLongRun positions ahead
     long long len = 1;
     bool is_long = true;
-    for (int blk = 0; blk < kLongRun / 32; ++blk) {
-      const long long q = p + 1 + blk * 32 + lane;
-      const uint32_t same = __ballot_sync(0xffffffffu, q < n && keys[q] == k);
-      if (same != 0xffffffffu) { len += __ffs(~same) - 1; is_long = false; break; }
-      len += 32;
+    for (int blk = 0; blk < kLongRun / LANES; ++blk) {
+      const long long q = p + 1 + blk * LANES + lane;
+      const uint32_t same = tile.ballot(q < n && keys[q] == k);
+      if (same != kAll) { len += __ffs(~same) - 1; is_long = false; break; }
+      len += LANES;
     }
     float* trow = table + (long long)k * dim;
     if (!is_long) {
-      for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {  // column panel kept in registers
+      for (int c0 = 0; c0 < dim; c0 += LANES * VEC) {  // column panel kept in registers
         const int c = c0 + lane * VEC;
         float acc[VEC], gv[VEC];
         if (c < dim) load_vec<VEC>(trow + c, acc);
@@ -397,10 +521,10 @@ scatter_sub_heads_kernel(float* __restrict__ table, int dim, const uint32_t* __r
       base = atomicAdd(&counters[1], nch);
       runs[r] = LongRun{(uint32_t)p, (uint32_t)len, k, base};
     }
-    len = __shfl_sync(0xffffffffu, len, 0);
-    base = __shfl_sync(0xffffffffu, base, 0);
+    len = tile.shfl(len, 0);
+    base = tile.shfl(base, 0);
     const uint32_t nch = (uint32_t)((len + kRunChunk - 1) / kRunChunk);
-    for (uint32_t jc = lane; jc < nch; jc += 32) {
+    for (uint32_t jc = lane; jc < nch; jc += LANES) {
       const long long off = (long long)jc * kRunChunk;
       chunks[base + jc] = ChunkDesc{(uint32_t)(p + off), (uint32_t)min((long long)kRunChunk, len - off)};
     }
@@ -516,9 +640,10 @@ int tfg_sparse_gather(const float* table, int64_t vocab, int dim, int n_shards, 
 
 size_t tfg_sparse_scratch_bytes(int64_t n) {
   if (n < 0) return 0;
+  // two (key, position) array pairs, hist[kMaxBins][blocks], the digit totals of every pass
   size_t nb = (size_t)((n + kSortTile - 1) / kSortTile);
   size_t arr = ((size_t)n * 4 + 255) / 256 * 256;
-  return 4 * arr + ((nb * 256 * 4 + 255) / 256 * 256) + 256;
+  return 4 * arr + nb * kMaxBins * 4 + kMaxPasses * kMaxBins * 4 + 256;
 }
 
 // scratch for the chunk-parallel treatment of long runs, on top of tfg_sparse_scratch_bytes(n)
@@ -535,6 +660,9 @@ size_t tfg_sparse_scratch_bytes_fast(int64_t n, int dim) {
   if (n < 0 || dim < 1) return 0;
   return tfg_sparse_scratch_bytes(n) + long_run_extra_bytes(n, dim, nullptr, nullptr);
 }
+
+// per CUDA device ordinal: the sort kernels may use 64 KB of dynamic shared memory
+static std::atomic<bool> g_sort_attr_set[64];
 
 static int scatter_sub_impl(float* table, int64_t vocab, int dim, int n_shards, int shard, int strategy,
                             const IdSrc& ids, int64_t n, const RowSrc& rows, float scale,
@@ -557,16 +685,46 @@ static int scatter_sub_impl(float* table, int64_t vocab, int dim, int n_shards, 
   uint32_t* keys[2] = {(uint32_t*)base, (uint32_t*)(base + arr)};
   uint32_t* vals[2] = {(uint32_t*)(base + 2 * arr), (uint32_t*)(base + 3 * arr)};
   uint32_t* hist = (uint32_t*)(base + 4 * arr);
-  int kb = (int)((n + 255) / 256);
-  if (kb > kNumSMs * 16) kb = kNumSMs * 16;
-  make_keys_kernel<<<kb, 256, 0, s>>>(pt, ids, n, sentinel, keys[0], vals[0]);
+  uint32_t* totals = hist + (size_t)n_blocks * kMaxBins;
+  uint32_t* n_live = nullptr;
+  if (n_shards > 1) {
+    // most ids belong to other shards: keep the owned ones (in order) and sort only those
+    n_live = totals + (size_t)kMaxPasses * kMaxBins;          // the trailing 256 B of the scratch
+    owned_keys_kernel<<<n_blocks, kSortThreads, 0, s>>>(pt, ids, n, sentinel, keys[1], hist);
+    owned_scan_kernel<<<1, 1024, 0, s>>>(hist, n_blocks, n_live);
+    owned_compact_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[1], n, sentinel, hist, keys[0], vals[0]);
+  } else {
+    int kb = (int)((n + 255) / 256);
+    if (kb > kNumSMs * 16) kb = kNumSMs * 16;
+    make_keys_kernel<<<kb, 256, 0, s>>>(pt, ids, n, sentinel, keys[0], vals[0]);
+  }
+  // the fewest passes of at most kMaxDigitBits bits that cover the key: two for up to 2^22 rows per shard
+  const int key_bits = bits_for(sentinel);
+  const int passes = (key_bits + kMaxDigitBits - 1) / kMaxDigitBits;
+  const int bits = (key_bits + passes - 1) / passes, bins = 1 << bits;
+  const size_t smem = (size_t)kSortWarps * bins * sizeof(uint32_t);
+  if (smem > 48 * 1024) {
+    int dev = -1;
+    cudaError_t ea = cudaGetDevice(&dev);
+    if (ea != cudaSuccess) return fail_cuda(nullptr, ea, "cudaGetDevice");
+    if (dev < 0 || dev >= 64) return fail(nullptr, TFG_ELIMIT, "CUDA device ordinal beyond 63");
+    if (!g_sort_attr_set[dev].load(std::memory_order_acquire)) {
+      const int most = kSortWarps * kMaxBins * (int)sizeof(uint32_t);
+      ea = cudaFuncSetAttribute(sort_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, most);
+      if (ea == cudaSuccess) ea = cudaFuncSetAttribute(sort_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, most);
+      if (ea != cudaSuccess) return fail_cuda(nullptr, ea, "cudaFuncSetAttribute(sort kernels)");
+      g_sort_attr_set[dev].store(true, std::memory_order_release);
+    }
+  }
+  cudaError_t ez = cudaMemsetAsync(totals, 0, (size_t)passes * kMaxBins * sizeof(uint32_t), s);
+  if (ez != cudaSuccess) return fail_cuda(nullptr, ez, "cudaMemsetAsync(digit totals)");
   int cur = 0;
-  const int passes = (bits_for(sentinel) + 7) / 8;
   for (int p = 0; p < passes; ++p) {
-    sort_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur], n, 8 * p, hist, n_blocks);
-    sort_scan_kernel<<<1, 1024, 0, s>>>(hist, 256ll * n_blocks);
-    sort_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur], vals[cur], n, 8 * p, hist, n_blocks,
-                                                          keys[cur ^ 1], vals[cur ^ 1]);
+    uint32_t* tot = totals + (size_t)p * kMaxBins;
+    sort_hist_kernel<<<n_blocks, kSortThreads, smem, s>>>(keys[cur], n, n_live, bits * p, bins, hist, n_blocks, tot);
+    sort_scan_kernel<<<(bins + kSortWarps - 1) / kSortWarps, kSortThreads, 0, s>>>(hist, n, n_live, n_blocks, bins, tot);
+    sort_scatter_kernel<<<n_blocks, kSortThreads, smem, s>>>(keys[cur], vals[cur], n, n_live, bits * p, bins, hist,
+                                                             n_blocks, keys[cur ^ 1], vals[cur ^ 1]);
     cur ^= 1;
   }
   long long blocks = (n + 7) / 8;
@@ -585,22 +743,29 @@ static int scatter_sub_impl(float* table, int64_t vocab, int dim, int n_shards, 
     cudaError_t em = cudaMemsetAsync(counters, 0, 8, s);     // the two counters must start at zero
     if (em != cudaSuccess) return fail_cuda(nullptr, em, "cudaMemsetAsync(counters)");
     const int gl = kNumSMs * 8;
-    if ((dim & 3) == 0) {
-      scatter_sub_heads_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel, rows,
-                                                              scale, runs, chunks, counters);
+    // lanes per position: the fewest of 8 / 16 / 32 whose vectors cover a row
+    const int vec = (dim & 3) == 0 ? 4 : 1;
+    const int lanes = dim <= 8 * vec ? 8 : dim <= 16 * vec ? 16 : 32;
+    long long hb = (n + 256 / lanes - 1) / (256 / lanes);
+    if (hb > kNumSMs * 16) hb = kNumSMs * 16;
+#define TFG_HEADS(V, LN)                                                                                          \
+  scatter_sub_heads_kernel<V, LN><<<(int)hb, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, n_live, sentinel, rows, scale, \
+                                                          runs, chunks, counters)
+    if (vec == 4) {
+      if (lanes == 8) TFG_HEADS(4, 8); else if (lanes == 16) TFG_HEADS(4, 16); else TFG_HEADS(4, 32);
       long_chunk_sum_kernel<4><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
       long_run_apply_kernel<4><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
     } else {
-      scatter_sub_heads_kernel<1><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel, rows,
-                                                              scale, runs, chunks, counters);
+      if (lanes == 8) TFG_HEADS(1, 8); else if (lanes == 16) TFG_HEADS(1, 16); else TFG_HEADS(1, 32);
       long_chunk_sum_kernel<1><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
       long_run_apply_kernel<1><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
     }
+#undef TFG_HEADS
   } else if ((dim & 3) == 0)
-    scatter_sub_runs_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel,
+    scatter_sub_runs_kernel<4><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, n_live, sentinel,
                                                            rows, scale);
   else
-    scatter_sub_runs_kernel<1><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, sentinel,
+    scatter_sub_runs_kernel<1><<<(int)blocks, 256, 0, s>>>(table, dim, keys[cur], vals[cur], n, n_live, sentinel,
                                                            rows, scale);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(nullptr, e, "sparse scatter_sub kernels");

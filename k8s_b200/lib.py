@@ -21,7 +21,7 @@ PART_MOD, PART_DIV = 0, 1
 DT_F32, DT_I64 = 0, 1
 BUF_PARAMS, BUF_GRADS, BUF_ACCUM, BUF_LOSS, BUF_FLAGS = 0, 1, 2, 3, 4
 MAX_REPLICAS, MAX_GPUS, IPC_HANDLE_BYTES = 64, 16, 64
-SPARSE_STATIC_MAX_IDS, SPARSE_STATIC_SCRATCH_BYTES = 65536, 1081600
+SPARSE_STATIC_MAX_IDS, SPARSE_STATIC_SCRATCH_BYTES = 65536, 1204480
 OPT_KINDS = {"sgd": OPT_SGD, "momentum": OPT_MOMENTUM, "nesterov": OPT_NESTEROV}
 MATH_MODES = {"fp32": MATH_FP32, "bf16": MATH_BF16, "tf32": MATH_TF32, "tf32x3": MATH_TF32X3}
 LAYOUTS = {"logical": LAYOUT_LOGICAL, "balanced": LAYOUT_BALANCED}

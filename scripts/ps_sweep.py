@@ -38,13 +38,15 @@ def timed(fn, stream, reps=10, warm=3):
 
 def main():
     quick = "--quick" in sys.argv
+    sparse_only = "--sparse-only" in sys.argv      # skip the dense sweep
+    one = "--one" in sys.argv                      # sparse: V = 1 M, D = 128, 1 M uniform ids only (for ncu)
     lib = L.load()
     peak = bench.measured_peaks()["hbm_gbs"]
     stream = torch.cuda.Stream()
     out = []
     # ---- dense ---------------------------------------------------------------------------
     sizes = [1 << 20, 1 << 22, 1 << 24, 1 << 26, 1 << 28] + ([] if quick else [1 << 30])
-    for P in sizes:
+    for P in ([] if sparse_only or one else sizes):
         for S in ([1, 8] if quick else [1, 2, 4, 8, 16]):
             for opt in ("sgd", "momentum"):
                 cfg = json.dumps({"cluster": {"master": ["m:1"], "ps": ["p%d:1" % i for i in range(S)]}})
@@ -71,10 +73,10 @@ def main():
                 torch.cuda.empty_cache()
     # ---- sparse --------------------------------------------------------------------------
     rng = np.random.default_rng(0)
-    for V, D in ([(1 << 20, 128)] if quick else [(1 << 20, 64), (1 << 20, 128), (1 << 23, 64), (1 << 23, 128)]):
+    for V, D in ([(1 << 20, 128)] if quick or one else [(1 << 20, 64), (1 << 20, 128), (1 << 23, 64), (1 << 23, 128)]):
         table = torch.randn(V, D, device="cuda")
-        for B in ([1 << 16] if quick else [1 << 16, 1 << 20]):
-            for dist in ("uniform", "zipf"):
+        for B in ([1 << 20] if one else [1 << 16] if quick else [1 << 16, 1 << 20]):
+            for dist in (("uniform",) if one else ("uniform", "zipf")):
                 ids_np = (rng.integers(0, V, size=B) if dist == "uniform"
                           else np.minimum(rng.zipf(1.05, size=B) - 1, V - 1)).astype(np.int64)
                 ids = torch.from_numpy(ids_np).cuda()
