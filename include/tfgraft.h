@@ -220,8 +220,9 @@ int tfg_sparse_gather(const float* table_dev, int64_t vocab, int dim, int n_shar
  * CPU loop).  Needs scratch_dev of at least tfg_sparse_scratch_bytes(n) bytes.
  * With tfg_sparse_scratch_bytes_fast(n, dim) bytes or more, rows hit by more than 64 ids
  * (heavy-tailed id distributions) are handled chunk-parallel instead of by one warp: their
- * updates are summed in blocks of 128 ids, in order, and the block sums subtracted in order --
- * deterministic, as accurate as the one-by-one loop, but not bit-identical to it.  Rows hit
+ * updates are summed in blocks of 128 ids, in order, the block sums in 16 contiguous segments, in order,
+ * and the segment sums subtracted in order -- deterministic, as accurate as the one-by-one loop, but not
+ * bit-identical to it.  Rows hit
  * by at most 64 ids are bit-exact either way. */
 size_t tfg_sparse_scratch_bytes(int64_t n);
 size_t tfg_sparse_scratch_bytes_fast(int64_t n, int dim);

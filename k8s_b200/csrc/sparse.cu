@@ -563,34 +563,54 @@ long_chunk_sum_kernel(int dim, const uint32_t* __restrict__ vals, const __grid_c
   }
 }
 
+// One block per long run.  Its warps sum contiguous segments of the run's chunk sums (in chunk order,
+// 8 loads in flight), then warp 0 subtracts the segment sums from the table row in segment order: the
+// row hit by half of a Zipf batch has thousands of chunks, which one warp alone walked for 0.3 ms.
+constexpr int kApplyWarps = 16;
+
 template <int VEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kApplyWarps * 32)
 long_run_apply_kernel(float* __restrict__ table, int dim, const LongRun* __restrict__ runs,
                       const uint32_t* __restrict__ counters, const float* __restrict__ carry) {
-  const int lane = threadIdx.x & 31;
+  __shared__ float seg[kApplyWarps][32 * VEC];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t n_runs = counters[0];
-  const uint32_t warps = gridDim.x * (blockDim.x >> 5);
-  for (uint32_t r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_runs; r += warps) {
+  for (uint32_t r = blockIdx.x; r < n_runs; r += gridDim.x) {
     const LongRun run = runs[r];
     const uint32_t nch = (run.len + kRunChunk - 1) / kRunChunk;
+    const uint32_t per = (nch + kApplyWarps - 1) / kApplyWarps;
+    const uint32_t j_begin = min(nch, w * per), j_end = min(nch, j_begin + per);
     float* trow = table + (long long)run.key * dim;
     for (int c0 = 0; c0 < dim; c0 += 32 * VEC) {
       const int c = c0 + lane * VEC;
-      float acc[VEC];
-      if (c < dim) load_vec<VEC>(trow + c, acc);
-      for (uint32_t j0 = 0; j0 < nch; j0 += 8) {
+      float sum[VEC];
+#pragma unroll
+      for (int u = 0; u < VEC; ++u) sum[u] = 0.f;
+      for (uint32_t j0 = j_begin; j0 < j_end; j0 += 8) {
         float cv[8][VEC];
 #pragma unroll
         for (int t = 0; t < 8; ++t)
-          if (j0 + t < nch && c < dim) load_vec<VEC>(carry + (long long)(run.chunk_base + j0 + t) * dim + c, cv[t]);
+          if (j0 + t < j_end && c < dim) load_vec<VEC>(carry + (long long)(run.chunk_base + j0 + t) * dim + c, cv[t]);
 #pragma unroll
         for (int t = 0; t < 8; ++t)
-          if (j0 + t < nch && c < dim) {
+          if (j0 + t < j_end && c < dim) {
 #pragma unroll
-            for (int u = 0; u < VEC; ++u) acc[u] = __fsub_rn(acc[u], cv[t][u]);
+            for (int u = 0; u < VEC; ++u) sum[u] = __fadd_rn(sum[u], cv[t][u]);
           }
       }
-      if (c < dim) store_vec<VEC>(trow + c, acc);
+#pragma unroll
+      for (int u = 0; u < VEC; ++u) seg[w][lane * VEC + u] = sum[u];
+      __syncthreads();
+      if (w == 0 && c < dim) {
+        float acc[VEC];
+        load_vec<VEC>(trow + c, acc);
+        for (int x = 0; x < kApplyWarps; ++x) {
+#pragma unroll
+          for (int u = 0; u < VEC; ++u) acc[u] = __fsub_rn(acc[u], seg[x][lane * VEC + u]);
+        }
+        store_vec<VEC>(trow + c, acc);
+      }
+      __syncthreads();
     }
   }
 }
@@ -754,11 +774,11 @@ static int scatter_sub_impl(float* table, int64_t vocab, int dim, int n_shards, 
     if (vec == 4) {
       if (lanes == 8) TFG_HEADS(4, 8); else if (lanes == 16) TFG_HEADS(4, 16); else TFG_HEADS(4, 32);
       long_chunk_sum_kernel<4><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
-      long_run_apply_kernel<4><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
+      long_run_apply_kernel<4><<<gl, kApplyWarps * 32, 0, s>>>(table, dim, runs, counters, carry);
     } else {
       if (lanes == 8) TFG_HEADS(1, 8); else if (lanes == 16) TFG_HEADS(1, 16); else TFG_HEADS(1, 32);
       long_chunk_sum_kernel<1><<<gl, 256, 0, s>>>(dim, vals[cur], rows, scale, chunks, counters, carry);
-      long_run_apply_kernel<1><<<gl, 256, 0, s>>>(table, dim, runs, counters, carry);
+      long_run_apply_kernel<1><<<gl, kApplyWarps * 32, 0, s>>>(table, dim, runs, counters, carry);
     }
 #undef TFG_HEADS
   } else if ((dim & 3) == 0)

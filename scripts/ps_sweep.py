@@ -39,7 +39,7 @@ def timed(fn, stream, reps=10, warm=3):
 def main():
     quick = "--quick" in sys.argv
     sparse_only = "--sparse-only" in sys.argv      # skip the dense sweep
-    one = "--one" in sys.argv                      # sparse: V = 1 M, D = 128, 1 M uniform ids only (for ncu)
+    one = "--one" in sys.argv or "--one-zipf" in sys.argv   # sparse: V = 1 M, D = 128, 1 M ids of one distribution (for ncu)
     lib = L.load()
     peak = bench.measured_peaks()["hbm_gbs"]
     stream = torch.cuda.Stream()
@@ -76,7 +76,7 @@ def main():
     for V, D in ([(1 << 20, 128)] if quick or one else [(1 << 20, 64), (1 << 20, 128), (1 << 23, 64), (1 << 23, 128)]):
         table = torch.randn(V, D, device="cuda")
         for B in ([1 << 20] if one else [1 << 16] if quick else [1 << 16, 1 << 20]):
-            for dist in (("uniform",) if one else ("uniform", "zipf")):
+            for dist in (("zipf",) if "--one-zipf" in sys.argv else ("uniform",) if one else ("uniform", "zipf")):
                 ids_np = (rng.integers(0, V, size=B) if dist == "uniform"
                           else np.minimum(rng.zipf(1.05, size=B) - 1, V - 1)).astype(np.int64)
                 ids = torch.from_numpy(ids_np).cuda()
