@@ -89,12 +89,29 @@ static long long shard_rows(int64_t vocab, int n_shards, int shard, int strategy
 }
 
 // ---- gather ------------------------------------------------------------------------------
+// LANES threads per id: a whole warp for rows of more than 64 floats, 16 or 8 lanes for narrower rows
+template <int LANES>
+__device__ __forceinline__ void copy_row(const float* __restrict__ src, float* __restrict__ dst, int dim, int lane) {
+  if ((dim & 3) == 0) {
+    for (int c = lane * 4; c < dim; c += LANES * 4)
+      *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+  } else {
+    for (int c = lane; c < dim; c += LANES) dst[c] = src[c];
+  }
+}
+
+static int gather_lanes(int dim) {
+  const int per = (dim & 3) == 0 ? 4 : 1;
+  return dim <= 8 * per ? 8 : dim <= 16 * per ? 16 : 32;
+}
+
+template <int LANES>
 __global__ void __launch_bounds__(256)
 gather_kernel(const float* __restrict__ table, Part pt, const long long* __restrict__ ids,
               long long n, int dim, float* __restrict__ out, int* bad) {
-  const int lane = threadIdx.x & 31;
-  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
-  for (long long i = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+  const int lane = threadIdx.x % LANES;
+  const long long groups = (long long)gridDim.x * (blockDim.x / LANES);
+  for (long long i = blockIdx.x * (long long)(blockDim.x / LANES) + threadIdx.x / LANES; i < n; i += groups) {
     long long id = ids[i];
     if (id < 0 || id >= pt.vocab) {
       if (lane == 0 && bad) atomicAdd(bad, 1);
@@ -104,25 +121,19 @@ gather_kernel(const float* __restrict__ table, Part pt, const long long* __restr
     long long row;
     locate(pt, id, &sh, &row);
     if (sh != pt.shard) continue;
-    const float* src = table + row * (long long)dim;
-    float* dst = out + i * (long long)dim;
-    if ((dim & 3) == 0) {
-      for (int c = lane * 4; c < dim; c += 128)
-        *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
-    } else {
-      for (int c = lane; c < dim; c += 32) dst[c] = src[c];
-    }
+    copy_row<LANES>(table + row * (long long)dim, out + i * (long long)dim, dim, lane);
   }
 }
 
 // the same with every shard of the table addressable from this GPU (own shards local, the others
 // peer-mapped): a worker fetches the rows of all its ids in one launch, straight from their owners
+template <int LANES>
 __global__ void __launch_bounds__(256)
 gather_multi_kernel(const __grid_constant__ TableSrc tables, Part pt, const long long* __restrict__ ids,
                     long long n, int dim, float* __restrict__ out, int* bad) {
-  const int lane = threadIdx.x & 31;
-  const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
-  for (long long i = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+  const int lane = threadIdx.x % LANES;
+  const long long groups = (long long)gridDim.x * (blockDim.x / LANES);
+  for (long long i = blockIdx.x * (long long)(blockDim.x / LANES) + threadIdx.x / LANES; i < n; i += groups) {
     long long id = ids[i];
     if (id < 0 || id >= pt.vocab) {
       if (lane == 0 && bad) atomicAdd(bad, 1);
@@ -131,14 +142,7 @@ gather_multi_kernel(const __grid_constant__ TableSrc tables, Part pt, const long
     int sh;
     long long row;
     locate(pt, id, &sh, &row);
-    const float* src = tables.base[sh] + row * (long long)dim;
-    float* dst = out + i * (long long)dim;
-    if ((dim & 3) == 0) {
-      for (int c = lane * 4; c < dim; c += 128)
-        *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
-    } else {
-      for (int c = lane; c < dim; c += 32) dst[c] = src[c];
-    }
+    copy_row<LANES>(tables.base[sh] + row * (long long)dim, out + i * (long long)dim, dim, lane);
   }
 }
 
@@ -649,10 +653,14 @@ int tfg_sparse_gather(const float* table, int64_t vocab, int dim, int n_shards, 
   if (n == 0) return TFG_OK;
   if (!table || !ids || !out) return fail(nullptr, TFG_EINVAL, "NULL argument");
   Part pt = make_part(vocab, n_shards, shard, strategy);
-  long long blocks = (n + 7) / 8;
+  const int lanes = gather_lanes(dim), per_block = 256 / lanes;
+  long long blocks = (n + per_block - 1) / per_block;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  gather_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, pt, (const long long*)ids, n, dim,
-                                                               out, bad);
+  const long long* idp = (const long long*)ids;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (lanes == 8) gather_kernel<8><<<(int)blocks, 256, 0, st>>>(table, pt, idp, n, dim, out, bad);
+  else if (lanes == 16) gather_kernel<16><<<(int)blocks, 256, 0, st>>>(table, pt, idp, n, dim, out, bad);
+  else gather_kernel<32><<<(int)blocks, 256, 0, st>>>(table, pt, idp, n, dim, out, bad);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(nullptr, e, "gather_kernel");
   return TFG_OK;
@@ -835,9 +843,14 @@ int tfg_sparse_gather_multi(const float* const* table_shards, int64_t vocab, int
     ts.base[k] = table_shards[k];
   }
   Part pt = make_part(vocab, n_shards, 0, strategy);
-  long long blocks = (n + 7) / 8;
+  const int lanes = gather_lanes(dim), per_block = 256 / lanes;
+  long long blocks = (n + per_block - 1) / per_block;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  gather_multi_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(ts, pt, (const long long*)ids, n, dim, out, bad);
+  const long long* idp = (const long long*)ids;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (lanes == 8) gather_multi_kernel<8><<<(int)blocks, 256, 0, st>>>(ts, pt, idp, n, dim, out, bad);
+  else if (lanes == 16) gather_multi_kernel<16><<<(int)blocks, 256, 0, st>>>(ts, pt, idp, n, dim, out, bad);
+  else gather_multi_kernel<32><<<(int)blocks, 256, 0, st>>>(ts, pt, idp, n, dim, out, bad);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_cuda(nullptr, e, "gather_multi_kernel");
   return TFG_OK;
