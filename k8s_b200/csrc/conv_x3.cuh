@@ -36,6 +36,23 @@ constexpr int kC2SlabLines = 336;                          // >= 255 + 4 * 18 + 
 constexpr int kC2SlabBytes = kC2SlabLines * 128;           // 43008 = 42 * 1024: every slab stays 1024-B aligned
 constexpr int kC2Threads = 64 + 256;                       // TMA warp, MMA warp, eight accumulate/epilogue warps
 
+// Development aid (make EXTRA=-DTFG_TRACE, scripts/conv_trace.py): cycles each role of a CTA spends waiting
+// on each barrier, read back with tfg_debug_c2_trace.  Not part of the shipped build.
+#ifdef TFG_TRACE
+__device__ long long g_c2_trace[2][160][16];
+#define C2T_DECL(...) long long __VA_ARGS__
+#define C2T_NOW() clock64()
+#define C2T_SET(v) v = clock64()
+#define C2T_ADD(acc, t0) acc += clock64() - (t0)
+#define C2T_PUT(slot, v) do { if (lane == 0) g_c2_trace[DGRAD ? 1 : 0][blockIdx.x][slot] = (v); } while (0)
+#else
+#define C2T_DECL(...)
+#define C2T_NOW() 0
+#define C2T_SET(v)
+#define C2T_ADD(acc, t0)
+#define C2T_PUT(slot, v)
+#endif
+
 // ---- forward (DGRAD = false) and data gradient (DGRAD = true) -----------------------------------------
 //   N_OUT   = output channels of the GEMM: 64 (forward) / 32 (data gradient)
 //   CBLOCKS = 32-channel blocks of the gathered tensor: 1 (x has 32 channels) / 2 (dy has 64)
@@ -85,6 +102,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chunks_per_tile = (25 + chunk_taps - 1) / chunk_taps;
+  C2T_DECL(t_entry = C2T_NOW(), tw0 = 0, tw1 = 0, tw2 = 0, tq = 0);
 
   // lines 324..335 of every slab are read by the last taps of rows that are not outputs; the TMA
   // box never writes them, so they are zeroed once (any finite value would do)
@@ -122,7 +140,9 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     if (lane == 0) {
       uint32_t tile = 0, bit = 0;
       for (int img = blockIdx.x; img < Nimg; img += gridDim.x, ++tile) {
+        C2T_SET(tq);
         mbar_wait(slab_empty, (tile & 1) ^ 1);
+        C2T_ADD(tw0, tq);
         mbar_expect_tx(slab_full, c2_slabs<DGRAD>() * 324 * 128);
 #pragma unroll
         for (int pl = 0; pl < 2; ++pl)
@@ -131,7 +151,9 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
             tma_load_4d(slab + (pl * CBLOCKS + cb) * kC2SlabBytes, pl ? &map_x_lo : &map_x, slab_full, cb * 32, -2, -2, img);
         for (int tap = 0; tap < 25; ++tap, ++bit) {
           const int s = bit % kBStages;
+          C2T_SET(tq);
           mbar_wait(&b_empty[s], ((bit / kBStages) & 1) ^ 1);
+          C2T_ADD(tw1, tq);
           mbar_expect_tx(&b_full[s], kBStage);
 #pragma unroll
           for (int pl = 0; pl < 2; ++pl) {
@@ -147,6 +169,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
           }
         }
       }
+      C2T_PUT(0, tw0); C2T_PUT(1, tw1); C2T_PUT(2, C2T_NOW() - t_entry);
     }
   } else if (warp == 1) {
     // ===== MMA issuer (converged warp, one elected lane) =====
@@ -159,16 +182,23 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     const uint32_t slab_full0 = smem_u32(slab_full), slab_empty0 = smem_u32(slab_empty);
     uint32_t bs = 0, bph = 0, tile = 0, chunk = 0;
     for (int img = blockIdx.x; img < Nimg; img += gridDim.x, ++tile) {
+      C2T_SET(tq);
+      C2T_PUT(3, tq - t_entry);                              // prologue: entry -> ready to wait for the slab
       mbar_wait_addr(slab_full0, tile & 1);
+      C2T_ADD(tw0, tq);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       for (int tap = 0; tap < 25; ++tap) {
         const bool chunk_start = tap % chunk_taps == 0;
         const uint32_t acc = chunk & 1;
         if (chunk_start) {
+          C2T_SET(tq);
           mbar_wait_addr(tmem_empty0 + acc * 8, ((chunk >> 1) & 1) ^ 1);
+          C2T_ADD(tw1, tq);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
+        C2T_SET(tq);
         mbar_wait_addr(b_full0 + bs * 8, bph);
+        C2T_ADD(tw2, tq);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int r = tap / 5, sx = tap - r * 5;
         const uint32_t shift = static_cast<uint32_t>(DGRAD ? (4 - r) * kC2PW + (4 - sx) : r * kC2PW + sx) * 8u;   // 16-B units
@@ -205,6 +235,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         }
       }
     }
+    C2T_PUT(4, tw0); C2T_PUT(5, tw1); C2T_PUT(6, tw2); C2T_PUT(7, C2T_NOW() - t_entry);
   } else {
     // ===== accumulate in registers + epilogue: warp = (TMEM lane quarter q, M tile h), thread = one grid position =====
     const int q = warp & 3, h = (warp - 2) >> 2;
@@ -220,7 +251,11 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
       for (int u = 0; u < N_OUT; ++u) sum[u] = 0.f;
       for (int c = 0; c < chunks_per_tile; ++c, ++chunk) {
         const uint32_t acc = chunk & 1;
+        C2T_SET(tq);
         mbar_wait(&tmem_full[acc], (chunk >> 1) & 1);
+        C2T_ADD(tw0, tq);
+        if (c == chunks_per_tile - 1) { C2T_SET(tw2); }         // last chunk of the image complete
+        C2T_SET(tq);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
         for (int c0 = 0; c0 < 2 * N_OUT; c0 += 32) {           // main columns, then the small ones
@@ -232,12 +267,14 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        C2T_ADD(tw1, tq);
       }
       if (valid) {
         const size_t row = (static_cast<size_t>(img) * kC2H + oh) * kC2W + ow;
         store_row_regs<N_OUT>(sum, out + row * N_OUT, mask ? mask + row * N_OUT : nullptr, 0, N_OUT, true, epi);
       }
     }
+    if (warp == 2) { C2T_PUT(8, tw0); C2T_PUT(9, tw1); C2T_PUT(10, tw2 - t_entry); C2T_PUT(11, C2T_NOW() - t_entry); }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -245,6 +282,7 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(kTmemCols) : "memory");
   }
+  if (threadIdx.x == 0) C2T_PUT(12, C2T_NOW() - t_entry);
 }
 
 // ---- weight gradient ---------------------------------------------------------------------------------

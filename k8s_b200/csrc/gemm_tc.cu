@@ -634,18 +634,24 @@ static int tc_backward_t(tfg_job* j, int slot) {
   const int B = m->B;
   int rc;
   const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
-  if ((rc = launch_tc(j, t->fc1_wgrad, kind, st))) return rc;   // dh1 (bf16 / low-order plane) came from fc2_bwd_kernel
+  const bool x3 = m->math == TFG_MATH_TF32X3;
+  // Weight gradients are leaves of the step.  In the 3xTF32 path they run on the side branch (joined at the
+  // end of mnist_forward_backward) while the data-gradient chain goes on: their CTAs fill the SMs the
+  // chain's one-wave kernels leave idle and their heads and tails overlap the chain's.
+  cudaStream_t leaf = x3 ? side_fork(j) : st;                   // ordered after fc2_bwd_kernel (dh1)
+  if ((rc = launch_tc(j, t->fc1_wgrad, kind, leaf))) return rc;   // dh1 (bf16 / low-order plane) came from fc2_bwd_kernel
   if ((rc = launch_tc(j, t->fc1_dgrad, kind, st))) return rc;
-  if (m->math == TFG_MATH_TF32X3) {
+  if (x3) {
     unpool_x3_kernel<<<kUnpoolBlocks, 256, 0, st>>>(s.da2, s.a2, s.idx2, (float*)t->dy2_lp, t->dy2_lo, t->partial, B);
     TC_LAUNCH_OK(j, "unpool_x3_kernel");
-    if ((rc = mnist_reduce_rows(j, t->partial, kUnpoolBlocks, 64, j->grads[slot] + j->vars[m->var[3]].offset))) return rc;   // db2
+    leaf = side_fork(j);                                        // ordered after the un-pooling (dy2 and its bias partials)
+    if ((rc = mnist_reduce_rows(j, t->partial, kUnpoolBlocks, 64, j->grads[slot] + j->vars[m->var[3]].offset, leaf))) return rc;   // db2
   } else {
     unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
     TC_LAUNCH_OK(j, "unpool_lp_kernel");
   }
-  if (m->math == TFG_MATH_TF32X3) {
-    if ((rc = launch_conv2_wgrad_x3(j, t, j->grads[slot] + j->vars[m->var[2]].offset, B, st))) return rc;
+  if (x3) {
+    if ((rc = launch_conv2_wgrad_x3(j, t, j->grads[slot] + j->vars[m->var[2]].offset, B, leaf))) return rc;
     // dx straight into g1m, masked by a1 > 0: no dcol, no col2im
     return launch_conv2_x3<true>(j, "conv2 dgrad x3", t->c2d_x, t->c2d_x_lo, t->c2d_w, t->c2d_w_lo, s.g1m, nullptr, s.a1, B, st);
   }
@@ -719,3 +725,13 @@ extern "C" int tfg_tf32_split_lo(const float* src_dev, float* lo_dev, int64_t n,
   if (!src_dev || !lo_dev || n < 0) return fail(nullptr, TFG_EINVAL, "bad argument");
   return launch_cast_lp(src_dev, lo_dev, n, 2, (cudaStream_t)stream) ? fail(nullptr, TFG_ECUDA, "split kernel launch failed") : TFG_OK;
 }
+
+#ifdef TFG_TRACE
+// development aid: the per-CTA wait counters of the conv2 forward (which = 0) / data gradient (1) kernel
+extern "C" int tfg_debug_c2_trace(int which, long long* out /* [160][16] */) {
+  using namespace tfg;
+  cudaError_t e = cudaMemcpyFromSymbol(out, tc::g_c2_trace, sizeof(long long) * 160 * 16,
+                                       (size_t)which * 160 * 16 * sizeof(long long));
+  return e == cudaSuccess ? TFG_OK : fail_cuda(nullptr, e, "cudaMemcpyFromSymbol(trace)");
+}
+#endif

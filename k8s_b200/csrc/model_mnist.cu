@@ -649,6 +649,7 @@ int mnist_build(tfg_job* j, int batch, int math) {
                                   ((B * 49 + 63) / 64) * 1024, (size_t)3136 * 1024});
     sl.scratch_floats = sc;
     A_(scratch, sc, float);
+    A_(scratch_c1, (size_t)kConv1Split * B * 832, float);
 #undef A_
   }
   if (e != cudaSuccess) {
@@ -671,7 +672,7 @@ void mnist_destroy(tfg_job* j) {
   for (auto& sl : m->slots) {
     void* ps[] = {sl.head_done, sl.x_stage, sl.lab_stage, sl.a1, sl.idx1, sl.col, sl.y2, sl.a2, sl.idx2, sl.h1,
                   sl.logits, sl.dlogits, sl.loss_vec, sl.dh1, sl.da2, sl.da2m, sl.dy2, sl.dcol,
-                  sl.g1m, sl.scratch};
+                  sl.g1m, sl.scratch, sl.scratch_c1};
     for (void* p : ps) cudaFree(p);
   }
   delete m;
@@ -691,8 +692,8 @@ int mnist_logits(tfg_job* j, int slot, float* host, size_t bytes) {
   return TFG_OK;
 }
 
-int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out) {
-  reduce_rows_kernel<<<(C + 31) / 32, 1024, 0, j->stream>>>(in, R, C, C, out, C, nullptr);
+int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out, cudaStream_t st) {
+  reduce_rows_kernel<<<(C + 31) / 32, 1024, 0, st>>>(in, R, C, C, out, C, nullptr);
   LAUNCH_OK(j, "reduce_rows_kernel");
   return TFG_OK;
 }
@@ -752,8 +753,9 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                                                              static_cast<__nv_bfloat16*>(mnist_tc_dh1_bf16(j, slot)),
                                                              mnist_tc_dh1_lo(j, slot), B);
     LAUNCH_OK(j, "fc2_bwd_kernel");
-    fc2_bwd_reduce_kernel<<<(kFc2PartialStride + 10 + 255) / 256, 256, 0, st>>>(s.scratch, s.dlogits, grd(6), grd(5),
-                                                                               grd(7), chunks, B);
+    // the gradients of W4, b3 and b4 are leaves of the step: side branch (joined before the function returns)
+    fc2_bwd_reduce_kernel<<<(kFc2PartialStride + 10 + 255) / 256, 256, 0, side_fork(j)>>>(s.scratch, s.dlogits, grd(6), grd(5),
+                                                                                         grd(7), chunks, B);
     LAUNCH_OK(j, "fc2_bwd_reduce_kernel");
   }
   if (tc) {
@@ -787,11 +789,13 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
     col2im_mask_kernel<float><<<blocks_for((long long)B * 196 * 8), 256, 0, st>>>(s.dcol, s.a1, s.g1m, B);
     LAUNCH_OK(j, "col2im_mask_kernel");
   }
-  conv1_bwd_kernel<<<kConv1Split * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch);
+  // own scratch: s.scratch may still be read by the side branch (fc2_bwd_reduce_kernel)
+  conv1_bwd_kernel<<<kConv1Split * B, 256, 0, st>>>(x, s.g1m, s.idx1, s.scratch_c1);
   LAUNCH_OK(j, "conv1_bwd_kernel");
   // [B][832] per-image partials -> dW1 (first 800 columns) and db1 (last 32), image order
-  reduce_rows_kernel<<<(832 + 31) / 32, 1024, 0, st>>>(s.scratch, kConv1Split * B, 832, 832, grd(0), 800, grd(1));
+  reduce_rows_kernel<<<(832 + 31) / 32, 1024, 0, st>>>(s.scratch_c1, kConv1Split * B, 832, 832, grd(0), 800, grd(1));
   LAUNCH_OK(j, "reduce_rows_kernel");
+  side_join(j);
   return TFG_OK;
 }
 

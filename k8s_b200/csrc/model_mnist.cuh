@@ -46,6 +46,7 @@ struct MnistSlot {       // activations of one local replica
   float* dcol = nullptr;         // [B*196, 800]
   float* g1m = nullptr;          // [B,14,14,32]
   float* scratch = nullptr;
+  float* scratch_c1 = nullptr;           // per-image partials of the conv1 gradients
   size_t scratch_floats = 0;
   void* tc = nullptr;            // tensor-path buffers (gemm_tc.cu)
 };
@@ -61,7 +62,7 @@ struct MnistModel {
 // model_mnist.cu: y2 -> a2, idx2 (shared by both math paths)
 int mnist_pool2(tfg_job* j, int slot, void* a2_bf16, float* a2_lo);
 // out[c] = sum over the R rows of in[R, C], rows added in a fixed order (reduce_rows_kernel)
-int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out);
+int mnist_reduce_rows(tfg_job* j, const float* in, int R, int C, float* out, cudaStream_t st);
 
 // gemm_tc.cu
 int mnist_tc_build(tfg_job* j);
