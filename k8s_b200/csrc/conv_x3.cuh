@@ -110,13 +110,34 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     const int sl = i / ((kC2SlabLines - 324) * 32), w = i % ((kC2SlabLines - 324) * 32);
     reinterpret_cast<float*>(slab + sl * kC2SlabBytes + 324 * 128)[w] = 0.f;
   }
-  if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_x_lo)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_w)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_w_lo)) : "memory");
-  }
-  if (warp == 1) {
+  // loads of one weight stage (tap) into ring slot s
+  auto load_tap = [&](int tap, int s) {
+    mbar_expect_tx(&b_full[s], kBStage);
+#pragma unroll
+    for (int pl = 0; pl < 2; ++pl) {
+      const CUtensorMap* mw = pl ? &map_w_lo : &map_w;
+      uint8_t* dst = smem_b + s * kBStage;
+      if (!DGRAD) {            // rows = K (the tap's 32 input channels), columns = n: two MN-major boxes of 32 n per plane
+        tma_load_2d(dst + pl * 8192, mw, &b_full[s], 0, tap * 32);
+        tma_load_2d(dst + pl * 8192 + 4096, mw, &b_full[s], 32, tap * 32);
+      } else {                 // rows = the tap's 32 input channels (N of this GEMM), columns = K: per K block [W | W_lo]
+        tma_load_2d(dst + pl * 4096, mw, &b_full[s], 0, tap * 32);
+        tma_load_2d(dst + 8192 + pl * 4096, mw, &b_full[s], 32, tap * 32);
+      }
+    }
+  };
+  auto load_slabs = [&](int img) {
+    mbar_expect_tx(slab_full, c2_slabs<DGRAD>() * 324 * 128);
+#pragma unroll
+    for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+      for (int cb = 0; cb < CBLOCKS; ++cb)
+        tma_load_4d(slab + (pl * CBLOCKS + cb) * kC2SlabBytes, pl ? &map_x_lo : &map_x, slab_full, cb * 32, -2, -2, img);
+  };
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the zeroed lines, before any MMA reads them
+  if (warp == 0) {
+    // The producer warp sets up the barriers and only ARRIVES at the block's start barrier: its loads are
+    // under way while the TMEM allocation and everybody else's wait are still going on.
     if (lane == 0) {
       mbar_init(slab_full, 1); mbar_init(slab_empty, 1);
       for (int s = 0; s < kBStages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
@@ -124,14 +145,17 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                 :: "r"(smem_u32(tmem_slot)), "n"(kTmemCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    asm volatile("bar.arrive 1, %0;" :: "n"(kC2Threads) : "memory");
+  } else {
+    if (warp == 1) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                   :: "r"(smem_u32(tmem_slot)), "n"(kTmemCols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" :: "n"(kC2Threads) : "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the zeroed lines, before any MMA reads them
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
   // TMEM columns: chunk accumulator a, M tile h at a * kAccCols + h * 2 * N_OUT: [main N_OUT | small N_OUT]
 
@@ -143,30 +167,13 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         C2T_SET(tq);
         mbar_wait(slab_empty, (tile & 1) ^ 1);
         C2T_ADD(tw0, tq);
-        mbar_expect_tx(slab_full, c2_slabs<DGRAD>() * 324 * 128);
-#pragma unroll
-        for (int pl = 0; pl < 2; ++pl)
-#pragma unroll
-          for (int cb = 0; cb < CBLOCKS; ++cb)
-            tma_load_4d(slab + (pl * CBLOCKS + cb) * kC2SlabBytes, pl ? &map_x_lo : &map_x, slab_full, cb * 32, -2, -2, img);
+        load_slabs(img);
         for (int tap = 0; tap < 25; ++tap, ++bit) {
           const int s = bit % kBStages;
           C2T_SET(tq);
           mbar_wait(&b_empty[s], ((bit / kBStages) & 1) ^ 1);
           C2T_ADD(tw1, tq);
-          mbar_expect_tx(&b_full[s], kBStage);
-#pragma unroll
-          for (int pl = 0; pl < 2; ++pl) {
-            const CUtensorMap* mw = pl ? &map_w_lo : &map_w;
-            uint8_t* dst = smem_b + s * kBStage;
-            if (!DGRAD) {            // rows = K (the tap's 32 input channels), columns = n: two MN-major boxes of 32 n per plane
-              tma_load_2d(dst + pl * 8192, mw, &b_full[s], 0, tap * 32);
-              tma_load_2d(dst + pl * 8192 + 4096, mw, &b_full[s], 32, tap * 32);
-            } else {                 // rows = the tap's 32 input channels (N of this GEMM), columns = K: per K block [W | W_lo]
-              tma_load_2d(dst + pl * 4096, mw, &b_full[s], 0, tap * 32);
-              tma_load_2d(dst + 8192 + pl * 4096, mw, &b_full[s], 32, tap * 32);
-            }
-          }
+          load_tap(tap, s);
         }
       }
       C2T_PUT(0, tw0); C2T_PUT(1, tw1); C2T_PUT(2, C2T_NOW() - t_entry);
@@ -243,12 +250,23 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
     const int m = h * 128 + q * 32 + lane;
     const int oh = m / kC2PW, ow = m - oh * kC2PW;
     const bool valid = oh < kC2H && ow < kC2W;
-    Epilogue epi = {bias, nullptr, 0, nullptr, 1, 0, nullptr};
     uint32_t chunk = 0;
     for (int img = blockIdx.x; img < Nimg; img += gridDim.x) {
+      // Nothing but stores is left for after the last chunk: the running sum starts at the bias, and the
+      // mask (data gradient: input activation > 0) is fetched now, as one bit per channel.
+      const size_t row = valid ? (static_cast<size_t>(img) * kC2H + oh) * kC2W + ow : 0;
       float sum[N_OUT];
 #pragma unroll
-      for (int u = 0; u < N_OUT; ++u) sum[u] = 0.f;
+      for (int u = 0; u < N_OUT; ++u) sum[u] = bias ? __ldg(bias + u) : 0.f;
+      uint32_t keep = 0xffffffffu;
+      if (DGRAD && mask && valid) {
+        keep = 0;
+#pragma unroll
+        for (int u = 0; u < N_OUT && u < 32; u += 4) {
+          const float4 k4 = *reinterpret_cast<const float4*>(mask + row * N_OUT + u);
+          keep |= (k4.x > 0.f ? 1u : 0u) << u | (k4.y > 0.f ? 2u : 0u) << u | (k4.z > 0.f ? 4u : 0u) << u | (k4.w > 0.f ? 8u : 0u) << u;
+        }
+      }
       for (int c = 0; c < chunks_per_tile; ++c, ++chunk) {
         const uint32_t acc = chunk & 1;
         C2T_SET(tq);
@@ -270,8 +288,16 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         C2T_ADD(tw1, tq);
       }
       if (valid) {
-        const size_t row = (static_cast<size_t>(img) * kC2H + oh) * kC2W + ow;
-        store_row_regs<N_OUT>(sum, out + row * N_OUT, mask ? mask + row * N_OUT : nullptr, 0, N_OUT, true, epi);
+        float* orow = out + row * N_OUT;
+#pragma unroll
+        for (int u = 0; u < N_OUT; u += 4) {
+          float4 o = make_float4(sum[u], sum[u + 1], sum[u + 2], sum[u + 3]);
+          if (DGRAD) {
+            o.x = (keep >> (u & 31)) & 1u ? o.x : 0.f; o.y = (keep >> ((u + 1) & 31)) & 1u ? o.y : 0.f;
+            o.z = (keep >> ((u + 2) & 31)) & 1u ? o.z : 0.f; o.w = (keep >> ((u + 3) & 31)) & 1u ? o.w : 0.f;
+          }
+          *reinterpret_cast<float4*>(orow + u) = o;
+        }
       }
     }
     if (warp == 2) { C2T_PUT(8, tw0); C2T_PUT(9, tw1); C2T_PUT(10, tw2 - t_entry); C2T_PUT(11, C2T_NOW() - t_entry); }
