@@ -225,7 +225,7 @@ int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
                         : launch_major<128, 1>(g, dst, ldc, k_blocks, kps, splits, epi, s);
   if (j) prof_mark(j, g.name);
   if (e != cudaSuccess) return fail_cuda(j, e, g.name);
-  if (splits > 1) {
+  if (splits > 1 && !g.reduce_later) {
     const long long mn = (long long)g.M * g.N;
     if (g.epi.mask) return fail(j, TFG_EINVAL, "split-K cannot apply a mask epilogue");
     splitk_reduce_kernel<<<(int)((mn + 255) / 256), 256, 0, s>>>(g.partial, g.C, splits, mn, g.epi.bias, g.N,
@@ -234,6 +234,14 @@ int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s) {
     if ((e = cudaGetLastError()) != cudaSuccess) return fail_cuda(j, e, "splitk_reduce_kernel");
   }
   return TFG_OK;
+}
+
+int tc_splits(const TcGemm& g, int kind) {
+  const int block_k = tc::kBlockKBytes / (kind == TFG_MATH_BF16 ? 2 : 4);
+  const int k_blocks = (g.K + block_k - 1) / block_k;
+  const int splits = std::max(1, std::min(g.splits, k_blocks));
+  const int kps = (k_blocks + splits - 1) / splits;
+  return (k_blocks + kps - 1) / kps;
 }
 
 // ---- operand preparation ---------------------------------------------------------------------
@@ -328,13 +336,14 @@ pool_relu_x3_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t*
 }
 
 // Gradient of the above: gp[B,7,7,64] (gradient at the pooled, post-relu map) -> the dense gradient
+// (gp = the pooled gradient da2[B,7,7,64], here still in split-K partial sums)
 // gy[B,14,14,64] at the convolution output (+ low-order plane): the masked value at the argmax position, 0 at
 // the other three.  The masked pooled gradient is also what the bias gradient sums: every thread keeps the sum
 // of its four channels over its positions, a block adds its 16 position lanes in lane order, and
 // bias_partial[block][64] goes to reduce_rows_kernel -- the separate column-sum pass over da2 is gone.
 constexpr int kUnpoolBlocks = 2 * kNumSMs;
 __global__ void __launch_bounds__(256)
-unpool_x3_kernel(const float* __restrict__ gp, const float* __restrict__ a, const uint8_t* __restrict__ idx,
+unpool_x3_kernel(const float* __restrict__ gp_partial, int splits, const float* __restrict__ a, const uint8_t* __restrict__ idx,
                  float* __restrict__ gy, float* __restrict__ gy_lo, float* __restrict__ bias_partial, int B) {
   __shared__ float4 red[16][16];
   const long long total = (long long)B * 49 * 16;
@@ -344,7 +353,13 @@ unpool_x3_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
     const long long pos = i >> 4;
     const int pw = (int)(pos % 7), ph = (int)((pos / 7) % 7);
     const long long b = pos / 49;
-    const float4 g4 = *reinterpret_cast<const float4*>(gp + i * 4), a4 = *reinterpret_cast<const float4*>(a + i * 4);
+    // the pooled gradient arrives as the K-split partial sums of the fc1 data-gradient GEMM: added here, in split order
+    float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z = 0; z < splits; ++z) {
+      const float4 p4 = *reinterpret_cast<const float4*>(gp_partial + (z * total + i) * 4);
+      g4.x += p4.x; g4.y += p4.y; g4.z += p4.z; g4.w += p4.w;
+    }
+    const float4 a4 = *reinterpret_cast<const float4*>(a + i * 4);
     const uchar4 k4 = *reinterpret_cast<const uchar4*>(idx + i * 4);
     const float g[4] = {a4.x > 0.f ? g4.x : 0.f, a4.y > 0.f ? g4.y : 0.f, a4.z > 0.f ? g4.z : 0.f, a4.w > 0.f ? g4.w : 0.f};
     const int k[4] = {k4.x, k4.y, k4.z, k4.w};
@@ -547,6 +562,10 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
                x3 ? 64 : 128, 1, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->a2_lo, t->dh1_lo))) return rc;
   if ((rc = mk(t->fc1_dgrad, "tc gemm fc1 dgrad", B, 3136, 1024, dh1, 1024, false, w3, 1024, false, s.da2,
                64, kSplitFc1Dgrad, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}, t->dh1_lo, w3l))) return rc;
+  if (x3) {   // their consumers (head_fwd_kernel, unpool_x3_kernel) add the K-split partial sums themselves
+    t->fc1_fwd.reduce_later = true;
+    t->fc1_dgrad.reduce_later = true;
+  }
   if (!x3) {
     if ((rc = mk(t->conv2_wgrad, "tc gemm conv2 wgrad", 800, 64, M2, t->col_lp, 800, true, t->dy2_lp, 64, true, grd(2),
                  64, kSplitW2Tc, tc::Epilogue{nullptr, nullptr, 0, nullptr, 0}))) return rc;
@@ -642,10 +661,13 @@ static int tc_backward_t(tfg_job* j, int slot) {
   if ((rc = launch_tc(j, t->fc1_wgrad, kind, leaf))) return rc;   // dh1 (bf16 / low-order plane) came from fc2_bwd_kernel
   if ((rc = launch_tc(j, t->fc1_dgrad, kind, st))) return rc;
   if (x3) {
-    unpool_x3_kernel<<<kUnpoolBlocks, 256, 0, st>>>(s.da2, s.a2, s.idx2, (float*)t->dy2_lp, t->dy2_lo, t->partial, B);
+    // fc1_dgrad left its K-split partial sums in t->partial (reduce_later); the bias partials go to the da2 buffer,
+    // which nothing else uses in this path
+    unpool_x3_kernel<<<kUnpoolBlocks, 256, 0, st>>>(t->partial, tc_splits(t->fc1_dgrad, kind), s.a2, s.idx2, (float*)t->dy2_lp,
+                                                    t->dy2_lo, s.da2, B);
     TC_LAUNCH_OK(j, "unpool_x3_kernel");
     leaf = side_fork(j);                                        // ordered after the un-pooling (dy2 and its bias partials)
-    if ((rc = mnist_reduce_rows(j, t->partial, kUnpoolBlocks, 64, j->grads[slot] + j->vars[m->var[3]].offset, leaf))) return rc;   // db2
+    if ((rc = mnist_reduce_rows(j, s.da2, kUnpoolBlocks, 64, j->grads[slot] + j->vars[m->var[3]].offset, leaf))) return rc;   // db2
   } else {
     unpool_lp_kernel<T><<<blocks_for((long long)B * 3136), 256, 0, st>>>(s.da2, s.a2, s.idx2, (T*)t->dy2_lp, t->dy2_lo, B, 7, 64);
     TC_LAUNCH_OK(j, "unpool_lp_kernel");
@@ -657,6 +679,14 @@ static int tc_backward_t(tfg_job* j, int slot) {
   }
   if ((rc = launch_tc(j, t->conv2_wgrad, kind, st))) return rc;
   return launch_tc(j, t->conv2_dgrad, kind, st);
+}
+
+const float* mnist_tc_fc1_partial(tfg_job* j, int slot, int* splits) {
+  MnistModel* m = j->model;
+  if (!m || m->math != TFG_MATH_TF32X3 || !m->slots[slot].tc) return nullptr;
+  TcSlot* t = static_cast<TcSlot*>(m->slots[slot].tc);
+  *splits = tc_splits(t->fc1_fwd, TFG_MATH_TF32);
+  return *splits > 1 ? t->partial : nullptr;
 }
 
 float* mnist_tc_a1_lo(tfg_job* j, int slot) {

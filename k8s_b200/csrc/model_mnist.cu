@@ -371,7 +371,8 @@ softmax_xent_kernel(const float* __restrict__ logits, const int32_t* __restrict_
 // One block of 8 warps per example: warp w covers k in [128w, 128w+128), partial sums are
 // combined by xor-shuffles and a fixed-order pass over the 8 warps.
 __global__ void __launch_bounds__(256)
-head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, const float* __restrict__ b4,
+head_fwd_kernel(float* __restrict__ h1, const float* __restrict__ h1_partial, int splits, const float* __restrict__ b3,
+                const float* __restrict__ w4, const float* __restrict__ b4,
                 const int32_t* __restrict__ labels, float* __restrict__ logits, float* __restrict__ dlogits,
                 float* __restrict__ loss_vec, int B, unsigned int* __restrict__ done, float* __restrict__ loss_out) {
   __shared__ float part[8][10];
@@ -380,11 +381,19 @@ head_fwd_kernel(const float* __restrict__ h1, const float* __restrict__ w4, cons
   float acc[10];
 #pragma unroll
   for (int n = 0; n < 10; ++n) acc[n] = 0.f;
-  const float* h = h1 + (size_t)ex * 1024;
+  float* h = h1 + (size_t)ex * 1024;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int k = w * 128 + i * 32 + lane;
-    const float hv = h[k];
+    float hv;
+    if (h1_partial) {   // h1 = relu(b3 + sum of fc1's K-split partial sums), added here in split order and kept for the backward pass
+      hv = 0.f;
+      for (int z = 0; z < splits; ++z) hv += h1_partial[((size_t)z * B + ex) * 1024 + k];
+      hv = fmaxf(hv + b3[k], 0.f);
+      h[k] = hv;
+    } else {
+      hv = h[k];
+    }
     const float2* wr = reinterpret_cast<const float2*>(w4 + k * 10);   // rows are 40 B: 8-B aligned
 #pragma unroll
     for (int n2 = 0; n2 < 5; ++n2) {
@@ -739,8 +748,10 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
                     GemmEpi{par(5), nullptr, 1}, 1, nullptr))) return rc;
   }
   // logits = h1 * W4 + b4, softmax cross-entropy and dlogits in one warp-shuffle kernel
-  head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, par(6), par(7), labels, s.logits, s.dlogits, s.loss_vec, B, s.head_done,
-                                     j->loss + j->local_replicas[slot]);
+  int fc1_splits = 1;
+  const float* fc1_partial = tc ? mnist_tc_fc1_partial(j, slot, &fc1_splits) : nullptr;
+  head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, fc1_partial, fc1_splits, par(5), par(6), par(7), labels, s.logits, s.dlogits,
+                                     s.loss_vec, B, s.head_done, j->loss + j->local_replicas[slot]);
   LAUNCH_OK(j, "head_fwd_kernel");
 
   }

@@ -71,6 +71,8 @@ int mnist_tc_forward(tfg_job* j, int slot);    // a1 -> y2/a2/idx2 -> h1
 int mnist_tc_backward(tfg_job* j, int slot);   // dh1 -> dW3, da2, dy2, dW2, dcol
 void* mnist_tc_dh1_bf16(tfg_job* j, int slot); // where fc2_bwd drops its bf16 copy of dh1 (NULL unless bf16 math)
 float* mnist_tc_dh1_lo(tfg_job* j, int slot);
+// 3xTF32: fc1's K-split partial sums [splits][B][1024], which head_fwd_kernel adds (NULL otherwise: h1 is complete)
+const float* mnist_tc_fc1_partial(tfg_job* j, int slot, int* splits);
 float* mnist_tc_a1_lo(tfg_job* j, int slot);   // where conv1 drops the low-order plane of a1 (NULL unless 3xTF32 math)  // ... and the low-order plane of dh1 (NULL unless 3xTF32 math)
 
 }  // namespace tfg

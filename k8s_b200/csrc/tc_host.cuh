@@ -16,6 +16,7 @@ struct TcGemm {
   float* partial = nullptr;    // [splits][M][N] when splits > 1
   int M = 0, N = 0, K = 0, ldc = 0, block_n = 128, splits = 1;
   bool a_mn = false, b_mn = false;
+  bool reduce_later = false;   // splits > 1: leave the partial sums [splits][M][N] for the consumer kernel to add (tc_splits() of them)
   tc::Epilogue epi = {nullptr, nullptr, 0, nullptr, 0, 0};
   const char* name = "gemm";
 };
@@ -27,5 +28,7 @@ int make_map(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t 
              bool mn_major = false);
 // j may be NULL (stateless entry point).  Launches the GEMM (and the split-K reduce when needed).
 int launch_tc(tfg_job* j, const TcGemm& g, int kind, cudaStream_t s);
+// number of K splits launch_tc really uses for g (no split is left empty)
+int tc_splits(const TcGemm& g, int kind);
 
 }  // namespace tfg
