@@ -480,7 +480,7 @@ int launch_job_apply(tfg_job* j, bool summed_local, int n_summed, bool whole, bo
     a.n_pull = 0;
     for (int g = 0; g < j->n_gpus; ++g)
       if (g != j->gpu_rank) a.pull[a.n_pull++] = j->peer_params[g];
-    if (j->params_lp)
+    if (j->params_lp && !lp_derived_per_step(j))
       for (int g = 0; g < j->n_gpus; ++g) a.lp[a.n_lp++] = j->peer_params_lp[g];
     a.n_loss = (j->model || j->resnet) ? j->n_replicas : 0;
     for (int r = 0; r < a.n_loss; ++r) a.loss_src[r] = j->peer_loss[r % j->n_gpus] + r;
@@ -594,8 +594,23 @@ cast_lp_kernel(const float* __restrict__ src, void* __restrict__ dst, long long 
   }
 }
 
+// the low-order plane, four values per thread (16-byte aligned buffers, n a multiple of 4)
+__global__ void __launch_bounds__(256)
+split_lo4_kernel(const float4* __restrict__ src, float4* __restrict__ dst, long long n4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = src[i];
+    dst[i] = make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w));
+  }
+}
+
 int launch_cast_lp(const float* src, void* dst, long long n, int lp_mode, cudaStream_t s) {
   if (n <= 0) return TFG_OK;
+  if (lp_mode == 2 && (n & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+    long long blocks = (n / 4 + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    split_lo4_kernel<<<(int)blocks, 256, 0, s>>>(reinterpret_cast<const float4*>(src), static_cast<float4*>(dst), n / 4);
+    return cudaGetLastError() == cudaSuccess ? TFG_OK : TFG_ECUDA;
+  }
   long long blocks = (n + 255) / 256;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
   cast_lp_kernel<<<(int)blocks, 256, 0, s>>>(src, dst, n, lp_mode);

@@ -732,8 +732,15 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   // ---------------- forward ----------------
   {
   NvtxRange nvtx_fwd("mnist forward");
+  const bool derive_lo = lp_derived_per_step(j);
+  if (derive_lo) {   // low-order plane of the weights from this rank's fp32 copy, beside conv1 (which does not read it)
+    if (launch_cast_lp(j->params, j->params_lp, j->flat_count, j->lp_mode, side_fork(j)))
+      return fail(j, TFG_ECUDA, "split_lo4_kernel launch failed");
+    prof_mark(j, "weights low-order plane");
+  }
   conv1_pool_relu_kernel<<<B * kConv1Split, 256, 0, st>>>(x, par(0), par(1), s.a1, s.idx1, mnist_tc_a1_lo(j, slot));
   LAUNCH_OK(j, "conv1_pool_relu_kernel");
+  if (derive_lo) side_join(j);
   if (tc) {
     if ((rc = mnist_tc_forward(j, slot))) return rc;   // conv2 + fc1 on the tensor path
   } else {
