@@ -20,6 +20,7 @@ SHAPES = [
     (800, 64, 1568, 64, 5), (800, 64, 25088, 64, 21),        # conv2 wgrad: split-K
     (3136, 1024, 128, 128, 1), (128, 3136, 1024, 64, 1),     # fc1 wgrad / dgrad at B = 128
     (130, 200, 72, 128, 3),
+    (128, 1024, 3136, 128, 17), (128, 3136, 1024, 128, 5),   # fc1 fwd / dgrad in 128-wide tiles, deep split-K, ragged last N tile
 ]
 
 

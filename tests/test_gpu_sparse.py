@@ -57,6 +57,36 @@ def test_gather_and_scatter_sub_bit_exact(lib, strategy, vocab, dim, n_shards, n
     assert not np.isnan(out_cpu).any() and int(bad.item()) == 0
 
 
+@pytest.mark.parametrize("vocab,n_shards,shard,ids_kind", [
+    ((1 << 23) + 5, 1, 0, "clustered"),      # 24-bit row keys: three radix passes of 8 bits
+    ((1 << 22) + 3, 1, 0, "clustered"),      # 23 bits: three passes
+    ((1 << 21) - 7, 1, 0, "clustered"),      # 21 bits: two passes of 11 bits (2048 bins, 64 KB of shared memory)
+    (3 * (1 << 21), 3, 1, "clustered"),      # owned-id compaction in front of a two-pass sort
+    (2000, 1, 0, "clustered"),               # one pass
+])
+def test_scatter_sub_key_widths(lib, vocab, n_shards, shard, ids_kind):
+    """Every digit plan of the radix sort (sparse.cu: passes of at most 11 bits chosen from the shard's row count),
+    with duplicates that differ only in their high key bits and out-of-range ids mixed in: bit-exact."""
+    rng = np.random.default_rng(vocab)
+    dim, n = 4, 30000
+    base = rng.integers(0, vocab, size=40).astype(np.int64)
+    ids = np.concatenate([base[rng.integers(0, 40, size=n // 2)],                       # heavy duplicates
+                          (rng.integers(0, 8, size=n // 4) * (vocab // 8)).astype(np.int64),   # differ in the top bits only
+                          rng.integers(0, vocab, size=n - n // 2 - n // 4).astype(np.int64)])
+    ids[::997] = vocab + 3                                                              # out of range: skipped
+    rng.shuffle(ids)
+    grads = rng.standard_normal((n, dim)).astype(np.float32)
+    rows = lib.sparse_shard_rows(vocab, n_shards, shard, L.PART_MOD)
+    table = rng.standard_normal((rows, dim)).astype(np.float32)
+    d_table, d_ids, d_grads = dev(table), dev(ids), dev(grads)
+    scratch = torch.empty(lib.sparse_scratch_bytes(n), dtype=torch.uint8, device="cuda")
+    lib.check(lib.sparse_scatter_sub(d_table.data_ptr(), vocab, dim, n_shards, shard, L.PART_MOD, d_ids.data_ptr(), n,
+                                     d_grads.data_ptr(), 0.05, scratch.data_ptr(), scratch.numel(), 0))
+    torch.cuda.synchronize()
+    O.sparse_scatter_sub(table, vocab, n_shards, shard, L.PART_MOD, ids, grads, 0.05)
+    np.testing.assert_array_equal(d_table.cpu().numpy().view(np.uint32), table.view(np.uint32))
+
+
 @pytest.mark.parametrize("vocab,dim,n,dist", [(1000, 64, 20000, "zipf"), (300, 33, 5000, "one"), (5000, 128, 65536, "zipf"),
                                               (100000, 128, 200000, "uniform")])
 def test_scatter_sub_chunk_parallel_long_runs(lib, vocab, dim, n, dist):
