@@ -1,14 +1,17 @@
 #!/bin/bash
 # Everything that needs N > 1 GPUs in one call (N = $1): parity checks over real peers, the bench line,
 # the dense exchange sweep (fused kernel and NCCL arm) and the sparse exchange.  Output: gpurun_out/r2_n$N_*.
+# $2: --quick (short sweep) | --no-sweep (no dense exchange sweep);  $3: extra bench.py flags (e.g. --no-resnet)
 N=$1
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 O=gpurun_out
 $TR --master-port 29601 scripts/mgpu_check.py balanced tf32x3 2>&1 | grep "MGPU_CHECK\|step" > $O/r2_n${N}_mgpu_check.log
 $TR --master-port 29602 scripts/mgpu_check.py logical tf32x3 2>&1 | grep "MGPU_CHECK\|step" >> $O/r2_n${N}_mgpu_check.log
 $TR --master-port 29603 scripts/mgpu_sparse_check.py --bench 2>&1 | grep "^{\|MGPU\|sparse" > $O/r2_n${N}_sparse.log
-$TR --master-port 29604 bench.py --gpus $N --steps 30 --warmup 5 2>$O/r2_n${N}_bench.err | grep "^{" > $O/r2_n${N}_bench.json
-$TR --master-port 29606 scripts/ps_exchange_sweep.py $2 --out $O/r2_n${N}_ps_exchange.jsonl > /dev/null 2>&1
+$TR --master-port 29604 bench.py --gpus $N --steps 30 --warmup 5 $3 2>$O/r2_n${N}_bench.err | grep "^{" > $O/r2_n${N}_bench.json
+if [ "$2" != "--no-sweep" ]; then
+  $TR --master-port 29606 scripts/ps_exchange_sweep.py $2 --out $O/r2_n${N}_ps_exchange.jsonl > /dev/null 2>&1
+fi
 cat $O/r2_n${N}_mgpu_check.log; grep MGPU $O/r2_n${N}_sparse.log
 python - <<PY
 import json
