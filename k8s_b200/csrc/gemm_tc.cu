@@ -342,6 +342,7 @@ pool_relu_x3_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t*
 // of its four channels over its positions, a block adds its 16 position lanes in lane order, and
 // bias_partial[block][64] goes to reduce_rows_kernel -- the separate column-sum pass over da2 is gone.
 constexpr int kUnpoolBlocks = 2 * kNumSMs;
+constexpr int kMaxUnpoolSplits = 4;   // K splits of the fc1 data gradient that unpool_x3_kernel adds itself (it uses 3)
 __global__ void __launch_bounds__(256)
 unpool_x3_kernel(const float* __restrict__ gp_partial, int splits, const float* __restrict__ a, const uint8_t* __restrict__ idx,
                  float* __restrict__ gy, float* __restrict__ gy_lo, float* __restrict__ bias_partial, int B) {
@@ -354,11 +355,14 @@ unpool_x3_kernel(const float* __restrict__ gp_partial, int splits, const float* 
     const int pw = (int)(pos % 7), ph = (int)((pos / 7) % 7);
     const long long b = pos / 49;
     // the pooled gradient arrives as the K-split partial sums of the fc1 data-gradient GEMM: added here, in split order
+    float4 pv[kMaxUnpoolSplits];
+#pragma unroll
+    for (int z = 0; z < kMaxUnpoolSplits; ++z)       // all loads first, then the sum in split order
+      if (z < splits) pv[z] = *reinterpret_cast<const float4*>(gp_partial + (z * total + i) * 4);
     float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z = 0; z < splits; ++z) {
-      const float4 p4 = *reinterpret_cast<const float4*>(gp_partial + (z * total + i) * 4);
-      g4.x += p4.x; g4.y += p4.y; g4.z += p4.z; g4.w += p4.w;
-    }
+#pragma unroll
+    for (int z = 0; z < kMaxUnpoolSplits; ++z)
+      if (z < splits) { g4.x += pv[z].x; g4.y += pv[z].y; g4.z += pv[z].z; g4.w += pv[z].w; }
     const float4 a4 = *reinterpret_cast<const float4*>(a + i * 4);
     const uchar4 k4 = *reinterpret_cast<const uchar4*>(idx + i * 4);
     const float g[4] = {a4.x > 0.f ? g4.x : 0.f, a4.y > 0.f ? g4.y : 0.f, a4.z > 0.f ? g4.z : 0.f, a4.w > 0.f ? g4.w : 0.f};
@@ -663,6 +667,7 @@ static int tc_backward_t(tfg_job* j, int slot) {
   if (x3) {
     // fc1_dgrad left its K-split partial sums in t->partial (reduce_later); the bias partials go to the da2 buffer,
     // which nothing else uses in this path
+    if (tc_splits(t->fc1_dgrad, kind) > kMaxUnpoolSplits) return fail(j, TFG_ESTATE, "fc1 data gradient uses more K splits than unpool_x3_kernel adds");
     unpool_x3_kernel<<<kUnpoolBlocks, 256, 0, st>>>(t->partial, tc_splits(t->fc1_dgrad, kind), s.a2, s.idx2, (float*)t->dy2_lp,
                                                     t->dy2_lo, s.da2, B);
     TC_LAUNCH_OK(j, "unpool_x3_kernel");

@@ -370,6 +370,8 @@ softmax_xent_kernel(const float* __restrict__ logits, const int32_t* __restrict_
 // ===== classifier head, forward: logits = h1 * W4 + b4, softmax cross-entropy, dlogits ======
 // One block of 8 warps per example: warp w covers k in [128w, 128w+128), partial sums are
 // combined by xor-shuffles and a fixed-order pass over the 8 warps.
+constexpr int kMaxFusedSplits = 12;   // K splits whose partial sums head_fwd_kernel can add itself (fc1 forward uses 9)
+
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(float* __restrict__ h1, const float* __restrict__ h1_partial, int splits, const float* __restrict__ b3,
                 const float* __restrict__ w4, const float* __restrict__ b4,
@@ -387,8 +389,14 @@ head_fwd_kernel(float* __restrict__ h1, const float* __restrict__ h1_partial, in
     const int k = w * 128 + i * 32 + lane;
     float hv;
     if (h1_partial) {   // h1 = relu(b3 + sum of fc1's K-split partial sums), added here in split order and kept for the backward pass
+      float pv[kMaxFusedSplits];
+#pragma unroll
+      for (int z = 0; z < kMaxFusedSplits; ++z)      // all loads first, then the sum in split order
+        if (z < splits) pv[z] = h1_partial[((size_t)z * B + ex) * 1024 + k];
       hv = 0.f;
-      for (int z = 0; z < splits; ++z) hv += h1_partial[((size_t)z * B + ex) * 1024 + k];
+#pragma unroll
+      for (int z = 0; z < kMaxFusedSplits; ++z)
+        if (z < splits) hv += pv[z];
       hv = fmaxf(hv + b3[k], 0.f);
       h[k] = hv;
     } else {
@@ -757,6 +765,7 @@ int mnist_forward_backward(tfg_job* j, int slot, const float* x, const int32_t* 
   // logits = h1 * W4 + b4, softmax cross-entropy and dlogits in one warp-shuffle kernel
   int fc1_splits = 1;
   const float* fc1_partial = tc ? mnist_tc_fc1_partial(j, slot, &fc1_splits) : nullptr;
+  if (fc1_partial && fc1_splits > kMaxFusedSplits) return fail(j, TFG_ESTATE, "fc1 forward uses more K splits than head_fwd_kernel adds");
   head_fwd_kernel<<<B, 256, 0, st>>>(s.h1, fc1_partial, fc1_splits, par(5), par(6), par(7), labels, s.logits, s.dlogits,
                                      s.loss_vec, B, s.head_done, j->loss + j->local_replicas[slot]);
   LAUNCH_OK(j, "head_fwd_kernel");
