@@ -478,9 +478,14 @@ fc2_bwd_kernel(const float* __restrict__ h1, const float* __restrict__ dlogits, 
   for (int n = 0; n < 10; ++n) { w[n] = w4[k * 10 + n]; dw[n] = 0.f; }
   __syncthreads();
   float bsum = 0.f;
-#pragma unroll 4
-  for (int b = 0; b < nb; ++b) {
-    const float hv = h1[(size_t)(b0 + b) * 1024 + k];
+  float hvs[kFc2Chunk];
+#pragma unroll
+  for (int b = 0; b < kFc2Chunk; ++b)            // the chunk's activations in flight together
+    if (b < nb) hvs[b] = h1[(size_t)(b0 + b) * 1024 + k];
+#pragma unroll
+  for (int b = 0; b < kFc2Chunk; ++b) {
+    if (b >= nb) break;
+    const float hv = hvs[b];
     float v = 0.f;
 #pragma unroll
     for (int n = 0; n < 10; ++n) {
