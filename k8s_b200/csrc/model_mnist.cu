@@ -81,6 +81,20 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
   __shared__ float xs[32][33];
   __shared__ float red[8][26][32];
   const int b = blockIdx.x / kConv1Split, part = blockIdx.x % kConv1Split, t = threadIdx.x, w = t >> 5, c = t & 31;
+  // this thread's gradients and arg-max codes, fetched while the image is staged (the loop below
+  // used to pay one global-load latency per output)
+  constexpr int kIters = (kConv1Part + 255) / 256;
+  float gs[kIters];
+  int as[kIters];
+#pragma unroll
+  for (int u = 0; u < kIters; ++u) {
+    const int o = part * kConv1Part + t + 256 * u;
+    if (o < (part + 1) * kConv1Part) {
+      const size_t oi = (size_t)b * (14 * 14 * 32) + o;
+      gs[u] = g1m[oi];
+      as[u] = idx1[oi];
+    }
+  }
   for (int i = t; i < 32 * 32; i += 256) {
     int r = i >> 5, q = i & 31;
     int ir = r - 2, ic = q - 2;
@@ -92,11 +106,13 @@ conv1_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g1m,
 #pragma unroll
   for (int k = 0; k < 25; ++k) acc[k] = 0.f;
   // this block's quarter of the pooled map
-  for (int o = part * kConv1Part + t; o < (part + 1) * kConv1Part; o += 256) {   // o & 31 == c
+#pragma unroll
+  for (int u = 0; u < kIters; ++u) {
+    const int o = part * kConv1Part + t + 256 * u;   // o & 31 == c
+    if (o >= (part + 1) * kConv1Part) break;
     const int pw = (o >> 5) % 14, ph = (o >> 5) / 14;
-    const size_t oi = (size_t)b * (14 * 14 * 32) + o;
-    const float g = g1m[oi];
-    const int a = idx1[oi];
+    const float g = gs[u];
+    const int a = as[u];
     const int r0 = 2 * ph + (a >> 1), c0 = 2 * pw + (a & 1);
     accb += g;
 #pragma unroll
