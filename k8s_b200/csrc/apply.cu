@@ -263,6 +263,20 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint
                :: "r"(tc::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
 }
 
+// Development aid (make EXTRA=-DTFG_TRACE, scripts/exchange_trace.py): %globaltimer stamps (ns) of the phases
+// of the last launch, from CTA 0 and from the CTA that finished last.  Not part of the shipped build.
+#ifdef TFG_TRACE
+__device__ unsigned long long g_xchg_trace[8];
+__device__ __forceinline__ void xchg_stamp(int slot) {
+  unsigned long long v;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v));
+  g_xchg_trace[slot] = v;
+}
+#define XCHG_STAMP(cond, slot) do { if (cond) xchg_stamp(slot); } while (0)
+#else
+#define XCHG_STAMP(cond, slot)
+#endif
+
 template <int KIND, bool SYNC>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 push_apply_pull_tma_kernel(const __grid_constant__ ApplyArgs a, int stages) {
@@ -274,6 +288,7 @@ push_apply_pull_tma_kernel(const __grid_constant__ ApplyArgs a, int stages) {
   uint64_t* empty = full + stages;
   const int t = threadIdx.x;
   uint32_t epoch = 0;
+  XCHG_STAMP(blockIdx.x == 0 && t == 0, 0);                      // kernel entry
   if (t == 0) {
     for (int s = 0; s < stages; ++s) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], kApplyThreads / 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -290,6 +305,7 @@ push_apply_pull_tma_kernel(const __grid_constant__ ApplyArgs a, int stages) {
     if (!wait_peers(a, kFlagsReady, epoch, t)) { peers_ok = 0; atomicExch(a.err_out, 1); }
     __syncthreads();
     if (!peers_ok) return;
+    XCHG_STAMP(blockIdx.x == 0 && t == 0, 1);                    // every peer is ready
   } else {
     __syncthreads();
     if (a.err && *reinterpret_cast<const volatile int*>(a.err) != 0) return;
@@ -374,15 +390,19 @@ push_apply_pull_tma_kernel(const __grid_constant__ ApplyArgs a, int stages) {
   }
   if (SYNC) {
     __shared__ int last;
+    XCHG_STAMP(blockIdx.x == 0 && t == 0, 2);                    // CTA 0: its chunks are done
     __threadfence_system();
     __syncthreads();
+    XCHG_STAMP(blockIdx.x == 0 && t == 0, 3);                    // CTA 0: its stores have landed
     if (t == 0) last = atomicAdd(a.done, 1u) == gridDim.x - 1;
     __syncthreads();
     if (last) {
+      XCHG_STAMP(t == 0, 4);                                     // the last CTA is through
       __threadfence_system();
       signal_peers(a, kFlagsPulled, epoch, t);
       if (!wait_peers(a, kFlagsPulled, epoch, t)) atomicExch(a.err_out, 1);
       __syncthreads();
+      XCHG_STAMP(t == 0, 5);                                     // every peer's stores have landed here
       if (t == 0) { *a.done = 0u; *a.epoch = epoch; }
     }
   }
@@ -664,3 +684,10 @@ int launch_barrier(tfg_job* j) {
 }
 
 }  // namespace tfg
+
+#ifdef TFG_TRACE
+extern "C" int tfg_debug_xchg_trace(unsigned long long* out /* [8] */) {
+  cudaError_t e = cudaMemcpyFromSymbol(out, tfg::g_xchg_trace, sizeof(unsigned long long) * 8);
+  return e == cudaSuccess ? TFG_OK : tfg::fail_cuda(nullptr, e, "cudaMemcpyFromSymbol(trace)");
+}
+#endif
