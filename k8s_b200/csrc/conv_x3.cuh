@@ -64,12 +64,16 @@ __device__ long long g_c2_trace[2][160][16];
 //   forward  [W n 0..31 | W n 32..63 | W_lo n 0..31 | W_lo n 32..63], MN-major boxes of 4 KB (group stride 4 KB)
 //   dgrad    per K block (32 of the 64 dy channels): [W rows c 0..31 | W_lo rows c 0..31], K-major, 8 KB
 template <bool DGRAD> constexpr int c2_b_stage_bytes() { return 2 /*planes*/ * 64 * 32 * 4; }   // 16 KB: [W | W_lo] of one tap
-template <bool DGRAD> constexpr int c2_b_stages() { return DGRAD ? 3 : 6; }
+template <bool DGRAD> constexpr int c2_b_stages() { return DGRAD ? 3 : 4; }
+// forward only: the image's 14 x 14 x 64 outputs staged for the 2x2 max-pool of the epilogue, one position per
+// line of 64 + 4 floats (the pad spreads the row-per-thread stores over the banks)
+constexpr int kC2PoolPitch = 68;
+template <bool DGRAD> constexpr int c2_pool_bytes() { return DGRAD ? 0 : kC2H * kC2W * kC2PoolPitch * 4; }
 template <bool DGRAD> constexpr int c2_slabs() { return DGRAD ? 4 : 2; }                        // planes x channel blocks
 template <bool DGRAD>
 constexpr size_t smem_bytes_c2() {
   return 1024 + static_cast<size_t>(c2_slabs<DGRAD>()) * kC2SlabBytes + c2_b_stages<DGRAD>() * c2_b_stage_bytes<DGRAD>() +
-         (2 * c2_b_stages<DGRAD>() + 8) * sizeof(uint64_t) + 16;
+         c2_pool_bytes<DGRAD>() + (2 * c2_b_stages<DGRAD>() + 8) * sizeof(uint64_t) + 16;
 }
 static_assert(smem_bytes_c2<false>() <= 232448 && smem_bytes_c2<true>() <= 232448, "shared memory budget");
 
@@ -78,7 +82,7 @@ __global__ void __launch_bounds__(kC2Threads, 1)
 conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_x_lo,
                 const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_w_lo,
                 float* __restrict__ out, const float* __restrict__ bias, const float* __restrict__ mask, int Nimg,
-                int chunk_taps) {
+                int chunk_taps, float* __restrict__ pool_a, float* __restrict__ pool_lo, uint8_t* __restrict__ pool_idx) {
   constexpr int N_OUT = DGRAD ? 32 : 64;
   constexpr int CBLOCKS = DGRAD ? 2 : 1;
   constexpr int kBStages = c2_b_stages<DGRAD>();
@@ -92,7 +96,8 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* slab = smem;                                      // [plane][cblock] slabs
   uint8_t* smem_b = slab + c2_slabs<DGRAD>() * kC2SlabBytes;
-  uint64_t* slab_full = reinterpret_cast<uint64_t*>(smem_b + kBStages * kBStage);
+  float* pool_stage = reinterpret_cast<float*>(smem_b + kBStages * kBStage);          // forward only (c2_pool_bytes)
+  uint64_t* slab_full = reinterpret_cast<uint64_t*>(smem_b + kBStages * kBStage + c2_pool_bytes<DGRAD>());
   uint64_t* slab_empty = slab_full + 1;
   uint64_t* b_full = slab_empty + 1;
   uint64_t* b_empty = b_full + kBStages;
@@ -287,7 +292,42 @@ conv2_x3_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
         C2T_ADD(tw1, tq);
       }
-      if (valid) {
+      if (!DGRAD && pool_a) {
+        // Forward with the 2x2 max-pool + relu in the epilogue (a launch of its own until the end of round 2; same
+        // comparisons in the same order as pool_relu_kernel of the other math modes): the outputs go to shared memory, one line per position, and the eight
+        // epilogue warps then share out the 49 pooled positions x 16 channel quads.  The convolution output itself is
+        // never written: the backward pass needs the pooled activations and the arg-max codes only.
+        if (valid) {
+          float* line = pool_stage + (oh * kC2W + ow) * kC2PoolPitch;
+#pragma unroll
+          for (int u = 0; u < N_OUT; u += 4) *reinterpret_cast<float4*>(line + u) = make_float4(sum[u], sum[u + 1], sum[u + 2], sum[u + 3]);
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        for (int i = threadIdx.x - 64; i < 49 * 16; i += 256) {
+          const int q4 = i & 15, pos = i >> 4, ph = pos / 7, pw = pos - ph * 7;
+          float best[4];
+          int arg[4];
+#pragma unroll
+          for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+              const float4 v4 = *reinterpret_cast<const float4*>(pool_stage + ((2 * ph + dy) * kC2W + 2 * pw + dx) * kC2PoolPitch + q4 * 4);
+              const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                if ((dy | dx) == 0 || v[u] > best[u]) { best[u] = v[u]; arg[u] = dy * 2 + dx; }
+            }
+          float r[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) r[u] = fmaxf(best[u], 0.f);
+          const size_t o = (static_cast<size_t>(img) * 49 + pos) * 64 + q4 * 4;
+          *reinterpret_cast<float4*>(pool_a + o) = make_float4(r[0], r[1], r[2], r[3]);
+          *reinterpret_cast<float4*>(pool_lo + o) = make_float4(tf32_lo(r[0]), tf32_lo(r[1]), tf32_lo(r[2]), tf32_lo(r[3]));
+          *reinterpret_cast<uchar4*>(pool_idx + o) = make_uchar4((unsigned char)arg[0], (unsigned char)arg[1], (unsigned char)arg[2],
+                                                                (unsigned char)arg[3]);
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");     // the staging lines are free for the next image
+      } else if (valid) {
         float* orow = out + row * N_OUT;
 #pragma unroll
         for (int u = 0; u < N_OUT; u += 4) {

@@ -301,41 +301,9 @@ unpool_lp_kernel(const float* __restrict__ gp, const float* __restrict__ a, cons
   }
 }
 
-// ---- 3xTF32 path: 2x2 max-pool + relu and its gradient, four channels per thread ---------------------
-// y2[B,14,14,64] (bias included) -> a2[B,7,7,64] (+ low-order plane) and the 2-bit argmax.  16-byte loads
-// and stores; a thread owns one pooled position and four channels.
-__global__ void __launch_bounds__(256)
-pool_relu_x3_kernel(const float* __restrict__ y, float* __restrict__ a, uint8_t* __restrict__ idx,
-                    float* __restrict__ a_lo, int B) {
-  const long long total = (long long)B * 49 * 16;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int q = (int)(i & 15);
-    const long long pos = i >> 4;
-    const int pw = (int)(pos % 7), ph = (int)((pos / 7) % 7);
-    const long long b = pos / 49;
-    float best[4];
-    int arg[4];
-#pragma unroll
-    for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-      for (int dx = 0; dx < 2; ++dx) {
-        const float4 v4 = *reinterpret_cast<const float4*>(y + ((b * 14 + 2 * ph + dy) * 14 + 2 * pw + dx) * 64 + q * 4);
-        const float v[4] = {v4.x, v4.y, v4.z, v4.w};
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if ((dy | dx) == 0 || v[u] > best[u]) { best[u] = v[u]; arg[u] = dy * 2 + dx; }
-      }
-    float r[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) r[u] = fmaxf(best[u], 0.f);
-    *reinterpret_cast<float4*>(a + i * 4) = make_float4(r[0], r[1], r[2], r[3]);
-    *reinterpret_cast<float4*>(a_lo + i * 4) = make_float4(tc::tf32_lo(r[0]), tc::tf32_lo(r[1]), tc::tf32_lo(r[2]), tc::tf32_lo(r[3]));
-    *reinterpret_cast<uchar4*>(idx + i * 4) = make_uchar4((unsigned char)arg[0], (unsigned char)arg[1], (unsigned char)arg[2],
-                                                          (unsigned char)arg[3]);
-  }
-}
-
-// Gradient of the above: gp[B,7,7,64] (gradient at the pooled, post-relu map) -> the dense gradient
+// ---- 3xTF32 path: the gradient of the 2x2 max-pool + relu, four channels per thread -----------------------
+// (the forward pooling lives in the epilogue of the conv2 forward kernel, conv_x3.cuh)
+// gp[B,7,7,64] (gradient at the pooled, post-relu map) -> the dense gradient
 // (gp = the pooled gradient da2[B,7,7,64], here still in split-K partial sums)
 // gy[B,14,14,64] at the convolution output (+ low-order plane): the masked value at the argmax position, 0 at
 // the other three.  The masked pooled gradient is also what the bias gradient sums: every thread keeps the sum
@@ -586,7 +554,8 @@ static int mnist_tc_prepare(tfg_job* j, int slot) {
 
 template <bool DGRAD>
 static int launch_conv2_x3(tfg_job* j, const char* name, const CUtensorMap& x, const CUtensorMap& x_lo, const CUtensorMap& w,
-                           const CUtensorMap& w_lo, float* out, const float* bias, const float* mask, int B, cudaStream_t st) {
+                           const CUtensorMap& w_lo, float* out, const float* bias, const float* mask, int B, cudaStream_t st,
+                           float* pool_a = nullptr, float* pool_lo = nullptr, uint8_t* pool_idx = nullptr) {
   static bool attr_set = false;
   constexpr size_t smem = tc::smem_bytes_c2<DGRAD>();
   if (!attr_set) {
@@ -598,7 +567,7 @@ static int launch_conv2_x3(tfg_job* j, const char* name, const CUtensorMap& x, c
   // small] accumulator is twice as wide to read back, so the chunk is longer than the GEMM's), one tap of 64
   // channels backward (8)
   tc::conv2_x3_kernel<DGRAD><<<std::min(B, kNumSMs), tc::kC2Threads, smem, st>>>(x, x_lo, w, w_lo, out, bias, mask, B,
-                                                                                  DGRAD ? 1 : 3);
+                                                                                  DGRAD ? 1 : 3, pool_a, pool_lo, pool_idx);
   TC_LAUNCH_OK(j, name);
   return TFG_OK;
 }
@@ -631,7 +600,9 @@ static int tc_forward_t(tfg_job* j, int slot) {
   const int kind = sizeof(T) == 2 ? TFG_MATH_BF16 : TFG_MATH_TF32;
   if (m->math == TFG_MATH_TF32X3) {
     const float* b2 = j->params + j->vars[m->var[3]].offset;
-    if ((rc = launch_conv2_x3<false>(j, "conv2 fwd x3", t->c2f_x, t->c2f_x_lo, t->c2f_w, t->c2f_w_lo, s.y2, b2, nullptr, B, st)))
+    // with the 2x2 max-pool + relu in its epilogue: a2, its low-order plane and the arg-max codes; y2 is never written
+    if ((rc = launch_conv2_x3<false>(j, "conv2 fwd x3", t->c2f_x, t->c2f_x_lo, t->c2f_w, t->c2f_w_lo, nullptr, b2, nullptr, B, st,
+                                     s.a2, t->a2_lo, s.idx2)))
       return rc;
   } else {
     // conv2 as im2col GEMM
@@ -639,12 +610,7 @@ static int tc_forward_t(tfg_job* j, int slot) {
     TC_LAUNCH_OK(j, "im2col_lp_kernel");
     if ((rc = launch_tc(j, t->conv2_fwd, kind, st))) return rc;
   }
-  if (m->math == TFG_MATH_TF32X3) {
-    pool_relu_x3_kernel<<<blocks_for((long long)B * 49 * 16), 256, 0, st>>>(s.y2, s.a2, s.idx2, t->a2_lo, B);
-    TC_LAUNCH_OK(j, "pool_relu_x3_kernel");
-  } else if ((rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) {     // also drops the operand copy of a2
-    return rc;
-  }
+  if (m->math != TFG_MATH_TF32X3 && (rc = mnist_pool2(j, slot, t->a2_lp, t->a2_lo))) return rc;   // also drops the operand copy of a2
   return launch_tc(j, t->fc1_fwd, kind, st);
 }
 
