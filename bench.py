@@ -621,14 +621,13 @@ def measure(a, model: str, n: int, rank: int, local: int, lib, L, torch, dist, s
         if "barrier_kernel" in prof:
             roof["barrier_share_of_step"] = prof["barrier_kernel"]["ms"] / total
         if n > 1 and "push_apply_pull_kernel" in prof:
-            # bytes one GPU sends (and receives) per step over NVLink: its shard's gradient from the N-1 other
-            # replicas, the new values (and their operand shadow) to the N-1 other ranks
+            # bytes one GPU receives (and, mirrored, sends) per step over NVLink: its shard's gradient from the N-1
+            # other replicas and the new values (bf16 math: and their shadow) of the N-1 other shards
             n_params = 25557032 if resnet else 3274634
             # (3xTF32: fp32 values only; every rank derives the low-order plane itself at the next forward)
             shadow = 2 if math == "bf16" else 0
             roof["exchange"] = {"share_of_step_incl_wait": prof["push_apply_pull_kernel"]["ms"] / total,
-                                "nvlink_bytes_in_per_gpu": 4 * n_params * (n - 1) / n,
-                                "nvlink_bytes_out_per_gpu": (4 + shadow) * n_params * (n - 1) / n,
+                                "nvlink_bytes_per_gpu_per_direction": (8 + shadow) * n_params * (n - 1) / n,
                                 "note": "the kernel waits in-kernel for the slowest rank; see scripts/ps_exchange_sweep.py "
                                         "for its bandwidth against the measured link"}
         out["roofline"] = roof

@@ -168,8 +168,8 @@ int resnet_tensor_get(tfg_job* j, int slot, const char* name, float* host, size_
 int mnist_batch(const tfg_job* j);
 int mnist_math(const tfg_job* j);
 int launch_cast_lp(const float* src, void* dst, long long n, int lp_mode, cudaStream_t s);   // apply.cu
-// 3xTF32 on several GPUs: the exchange moves the fp32 parameters only (8 instead of 12 bytes per parameter
-// and peer over NVLink); every rank derives the low-order plane from its own copy at the start of the next
+// 3xTF32 on several GPUs: the exchange moves the fp32 parameters only (8 (N-1)/N instead of 12 (N-1)/N bytes per
+// parameter and NVLink direction); every rank derives the low-order plane from its own copy at the start of the next
 // forward, beside conv1, which does not read it (model_mnist.cu).
 inline bool lp_derived_per_step(const tfg_job* j) { return j->lp_mode == 2 && j->n_gpus > 1; }
 float* mnist_stage_images(tfg_job* j, int slot);
