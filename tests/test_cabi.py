@@ -2,6 +2,7 @@
 entry points (cluster, placement) are exercised without a GPU, compute ones are not."""
 import ctypes as C
 import json
+import os
 
 import numpy as np
 import pytest
@@ -87,6 +88,12 @@ def test_sparse_shard_rows_matches_oracle(lib):
                 assert sum(rows) == vocab
     assert lib.sparse_shard_rows(10, 0, 0, 0) == -1
     assert lib.sparse_scratch_bytes(0) >= 256 and lib.sparse_scratch_bytes(1 << 20) >= 16 << 20
+    # the array behind tfg_sparse_scatter_sub_static is exactly what the sort asks for at its id limit, and the
+    # Python mirror of the header constants agrees with the header
+    assert lib.sparse_scratch_bytes(L.SPARSE_STATIC_MAX_IDS) == L.SPARSE_STATIC_SCRATCH_BYTES
+    header = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "tfgraft.h")).read()
+    assert "#define TFG_SPARSE_STATIC_MAX_IDS %d" % L.SPARSE_STATIC_MAX_IDS in header
+    assert "#define TFG_SPARSE_STATIC_SCRATCH_BYTES %d" % L.SPARSE_STATIC_SCRATCH_BYTES in header
 
 
 def test_compute_entry_points_fail_loudly_without_gpu(lib):
